@@ -1,0 +1,318 @@
+#!/usr/bin/env python
+"""bench.py — pod x node Filter+Score+NormalizeScore evaluations per second.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One "step" = one pass of the hot path over one batch: 50 000 pending pods against 5 000
+nodes x 8 GPUs per rank (BASELINE.json configs[1]); with N ranks the nodes are sharded
+(5 000 per rank, weak scaling) and the per-pod extrema are all-reduced between the scoring
+and the normalise kernels (the path's one exchange step).
+
+Prints ONE JSON line (rank 0).  `value` = device-resident throughput (inputs in HBM when
+the timed region starts); `e2e` = the same metric through the host-buffer C-ABI call
+gs_score_batch, host<->device copies inside the timed region; `roofline` = the dominant
+kernel against the measured HBM bandwidth; `cpu_baseline` = the CPU oracle (a port of the
+reference's Go algorithm) on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+N_PODS, N_NODES, GPUS_PER_NODE, N_APPS = 50_000, 5_000, 8, 1024
+METRIC = "pod x node Filter+Score+NormalizeScore evals/sec (50k pods x 5k nodes x 8 GPUs/node per rank)"
+UNIT = "evals/s"
+
+
+def workload_name(n_ranks):
+    return (f"batched Filter+Score+NormalizeScore, {N_PODS} pods x {N_NODES} nodes x {GPUS_PER_NODE} GPUs/node per rank"
+            f" ({n_ranks} rank(s), nodes sharded)")
+
+
+def algorithmic_bytes(n_pods, n_nodes, n_res, n_apps, n_cols, gpn):
+    """2 B written per eval + every input table read once + 4 B/pod best node."""
+    return (2 * n_pods * n_nodes + 8 * n_pods + n_nodes * 2 + 4 * (n_nodes * gpn + 1) + 8 * n_res
+            + 4 * n_apps * n_cols + 8 * n_apps * n_apps + 4 * n_pods)
+
+
+def measured_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self._stop, self._t = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                                      str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.splitlines()[0].split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def __enter__(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=10)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in self.rows if len(r) > 3 + i)]
+        try:
+            mx = float(self.rows[0][1])
+        except Exception:
+            mx = None
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": reasons, "samples": len(self.rows)}
+
+
+def cpu_reference_leg(preds, cluster, pods, budget_evals_per_thread=1_500_000, steps=1, warmup=0):
+    """The CPU restatement of the reference algorithm on a bounded sample (first pods of the batch)."""
+    from oracle.score_oracle import Oracle, num_threads
+
+    threads = num_threads()
+    n_sample = max(8, min(pods.n_pods, int(budget_evals_per_thread * threads / max(1, cluster.n_nodes))))
+    sub = type(pods)(app=pods.app[:n_sample], slo=pods.slo[:n_sample])
+    ora = Oracle(preds, cluster)
+    for _ in range(warmup):
+        ora.score_batch(type(pods)(app=pods.app[:max(8, n_sample // 8)], slo=pods.slo[:max(8, n_sample // 8)]), threads=threads)
+    times = []
+    for _ in range(max(1, steps)):
+        t0 = time.perf_counter()
+        ora.score_batch(sub, normalize=True, threads=threads)
+        times.append(time.perf_counter() - t0)
+    evals = n_sample * cluster.n_nodes
+    return {"value": evals * len(times) / sum(times), "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"first {n_sample} of {pods.n_pods} pods x all {cluster.n_nodes} nodes ({evals} evals/step), "
+                      f"oracle/score_oracle.c -O2, OpenMP over pods"}, sum(times) / len(times)
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    import __graft_entry__ as entry
+
+    pkg = entry.load_package()
+    preds, cluster, pods = pkg.synth.make_workload(N_PODS, N_NODES, GPUS_PER_NODE, N_APPS)
+    cb, sec = cpu_reference_leg(preds, cluster, pods, steps=args.steps, warmup=min(args.warmup, 1))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32+f64", "data": "synthetic",
+        "config": {"workload": workload_name(world), "note": "CPU port of the reference's Go Logic/NormalizeScore "
+                   "(Go toolchain absent); each step is a bounded sample of the workload; the real reference also "
+                   "pays 2*G*(R+1) gRPC dials + Redis + API-server writes per Score, omitted here"},
+        "cpu_baseline": cb,
+        "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--pods", type=int, default=N_PODS)
+    ap.add_argument("--nodes", type=int, default=N_NODES)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+
+    import __graft_entry__ as entry
+
+    pkg = entry.load_package()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    P, NL = args.pods, args.nodes                   # nodes per rank (weak scaling)
+    preds = pkg.synth.make_predictions(N_APPS)
+    cluster_all = pkg.synth.make_cluster(NL * world, N_APPS, GPUS_PER_NODE)
+    cluster = cluster_all.shard(rank * NL, (rank + 1) * NL) if world > 1 else cluster_all
+    pods = pkg.synth.make_pods(P, N_APPS)
+
+    sch = pkg.Scheduler(local_rank)
+    sch.upload_predictions(preds)
+    sch.upload_cluster(cluster, node_base=rank * NL)
+    sch.set_profiling(True)
+
+    d_app = torch.from_numpy(pods.app.view(np.int32)).to(dev)
+    d_slo = torch.from_numpy(pods.slo).to(dev)
+    d_score = torch.empty((P, NL), dtype=torch.uint8, device=dev)
+    d_sel = torch.empty((P, NL), dtype=torch.uint8, device=dev)
+    d_ext = torch.zeros((2, P), dtype=torch.int64, device=dev)   # [hi_arg | neg_lo], one all-reduce(MAX)
+    d_best = torch.empty(P, dtype=torch.int32, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def step():
+        st = torch.cuda.current_stream().cuda_stream
+        sch.score_raw_dev(d_app, d_slo, P, d_score, d_sel, d_ext[0], d_ext[1], stream=st)
+        if world > 1:
+            dist.all_reduce(d_ext, op=dist.ReduceOp.MAX)
+        sch.normalize_dev(P, d_score, d_ext[0], d_ext[1], d_best, stream=st)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    kern_ms = []
+    with ClockSampler(local_rank) as clocks:
+        barrier()
+        t_wall0 = time.perf_counter()
+        for a, b in ev:
+            flush.zero_()          # evict L2 between timed iterations (not timed)
+            a.record()
+            step()
+            b.record()
+            kern_ms.append(None)
+        barrier()
+        t_wall = time.perf_counter() - t_wall0
+    step_ms = [a.elapsed_time(b) for a, b in ev]
+    # dominant-kernel duration, live, from the library's own event bracket on the same stream
+    kms = []
+    for _ in range(3):
+        flush.zero_()
+        step()
+        torch.cuda.synchronize()
+        kms.append(sch.last_score_kernel_ms())
+    total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+    total_ms = float(total_ms.item())
+    evals_per_step = P * NL * world
+    value = evals_per_step * args.steps / (total_ms * 1e-3)
+
+    # ---- e2e: host buffers through gs_score_batch (pinned), copies inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        h_score = torch.empty((P, NL), dtype=torch.uint8).pin_memory()
+        h_sel = torch.empty((P, NL), dtype=torch.uint8).pin_memory()
+        h_best = torch.empty(P, dtype=torch.int32).pin_memory()
+        h_app = torch.from_numpy(pods.app.view(np.int32)).pin_memory()
+        h_slo = torch.from_numpy(pods.slo).pin_memory()
+        hp = pkg.Pods(app=h_app.numpy().view(np.uint32), slo=h_slo.numpy())
+        out = (h_score.numpy(), h_sel.numpy(), h_best.numpy())
+        if world == 1:
+            for _ in range(2):
+                sch.score_batch(hp, normalize=True, out=out)
+            n_e2e = max(3, min(args.steps, 10))
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(n_e2e):
+                sch.score_batch(hp, normalize=True, out=out)
+            barrier()
+            dt = (time.perf_counter() - t0) / n_e2e
+            e2e = {"value": P * NL / dt, "unit": UNIT, "h2d_bytes_per_step": 8 * P,
+                   "d2h_bytes_per_step": 2 * P * NL + 4 * P, "ms_per_step": dt * 1e3,
+                   "api": "gs_score_batch (host buffers in, score+selection matrices and best node out)"}
+        else:
+            # N>1: device API + NCCL between the phases, host copies around it
+            def e2e_step():
+                st = torch.cuda.current_stream().cuda_stream
+                d_app.copy_(h_app, non_blocking=True)
+                d_slo.copy_(h_slo, non_blocking=True)
+                sch.score_raw_dev(d_app, d_slo, P, d_score, d_sel, d_ext[0], d_ext[1], stream=st)
+                dist.all_reduce(d_ext, op=dist.ReduceOp.MAX)
+                sch.normalize_dev(P, d_score, d_ext[0], d_ext[1], d_best, stream=st)
+                h_score.copy_(d_score, non_blocking=True)
+                h_sel.copy_(d_sel, non_blocking=True)
+                h_best.copy_(d_best, non_blocking=True)
+                torch.cuda.synchronize()
+            e2e_step()
+            n_e2e = max(3, min(args.steps, 10))
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(n_e2e):
+                e2e_step()
+            barrier()
+            dt = torch.tensor([(time.perf_counter() - t0) / n_e2e], dtype=torch.float64, device=dev)
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+            dt = float(dt.item())
+            e2e = {"value": evals_per_step / dt, "unit": UNIT, "h2d_bytes_per_step": 8 * P,
+                   "d2h_bytes_per_step": 2 * P * NL + 4 * P, "ms_per_step": dt * 1e3,
+                   "api": "gs_score_raw_dev + all_reduce(MAX) + gs_normalize_dev with pinned host copies, per rank"}
+
+    if rank == 0:
+        peak, peak_kind = measured_peak_gbs()
+        kernel_ms = float(np.median(kms))
+        abytes = algorithmic_bytes(P, NL, int(cluster.res_app.size), N_APPS, preds.conf.shape[1], GPUS_PER_NODE)
+        achieved = abytes / (kernel_ms * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32+f64", "data": "synthetic",
+            "config": {"workload": workload_name(world), "pods": P, "nodes_per_rank": NL, "gpus_per_node": GPUS_PER_NODE,
+                       "apps": N_APPS, "residents_rank0": int(cluster.res_app.size),
+                       "distinct_app_slo_classes": pkg.synth.distinct_classes(pods), "seed": hex(pkg.synth.SEED),
+                       "l2": "flushed between timed iterations (256 MB memset, untimed); outputs 500 MB > L2",
+                       "timing": "CUDA events per step on the launching stream, summed; max over ranks"},
+            "gpu_launches": 5 * args.steps,
+            "wall_ms_per_step_incl_flush": t_wall * 1e3 / args.steps,
+            "clocks": clocks.summary(),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_kind": peak_kind, "kernel": "score_fast_kernel",
+                         "kernel_ms": kernel_ms, "algorithmic_bytes": abytes,
+                         "note": "kernel is FP64/FP32-ALU bound, not HBM bound (see DESIGN.md)"},
+        }
+        if e2e:
+            line["e2e"] = e2e
+        if not args.no_cpu_baseline and world == 1:
+            line["cpu_baseline"], _ = cpu_reference_leg(preds, cluster, pods)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

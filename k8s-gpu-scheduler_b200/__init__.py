@@ -1,0 +1,204 @@
+"""k8s-gpu-scheduler_b200 — B200-native Score/NormalizeScore hot path of k8s-gpu-scheduler.
+
+Python here is a thin ctypes driver over ``libgpusched.so`` (the C ABI in
+``include/gpusched.h``), used by the tests and ``bench.py`` in this toolchain-less
+container; the production caller is the Go plugin over cgo.
+
+There is no CPU path: importing works anywhere (so that symbols can be checked), but any
+compute call needs a CUDA device and raises otherwise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import synth  # noqa: F401  (re-export)
+from .synth import APP_UNKNOWN, MODEL_A30, MODEL_NONE, MODEL_V100, Cluster, Pods, Predictions  # noqa: F401
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgpusched.so")
+
+GS_OK = 0
+SCORE_RAW, SCORE_NORMALIZE, SCORE_DIRECT = 0, 1, 2
+SEL_NONE = 31
+ERR_NAMES = {-1: "GS_ERR_INVALID", -2: "GS_ERR_CUDA", -3: "GS_ERR_STATE", -4: "GS_ERR_NOMEM",
+             -5: "GS_ERR_UNSUPPORTED", -6: "GS_ERR_NOCONV"}
+
+# every symbol include/gpusched.h declares
+EXPORTS = [
+    "gs_create", "gs_destroy", "gs_last_error", "gs_version", "gs_upload_cluster", "gs_upload_predictions",
+    "gs_score_batch", "gs_score_raw_dev", "gs_normalize_dev", "gs_normalize_scores", "gs_select_mig",
+    "gs_set_profiling", "gs_last_score_kernel_ms", "gs_complete_fit", "gs_complete_transform", "gs_model_info", "gs_model_step", "gs_model_destroy",
+]
+
+
+class GsError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"{ERR_NAMES.get(code, code)}: {msg}")
+        self.code = code
+
+
+class _GsCluster(C.Structure):
+    _fields_ = [("n_nodes", C.c_int32), ("max_gpus", C.c_int32), ("node_model", C.c_void_p),
+                ("node_ngpu", C.c_void_p), ("gpu_off", C.c_void_p), ("res_app", C.c_void_p),
+                ("res_slo", C.c_void_p), ("redis_reachable", C.c_int32)]
+
+
+class _GsPredictions(C.Structure):
+    _fields_ = [("n_apps", C.c_int32), ("n_cols", C.c_int32), ("conf", C.c_void_p), ("interf", C.c_void_p),
+                ("col_of", C.c_void_p)]
+
+
+_lib = None
+
+
+def load_library():
+    """dlopen libgpusched.so (built in-tree by build.py); fails loudly if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} not built: run `python k8s-gpu-scheduler_b200/build.py` "
+                          "(there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    vp, i32, u32 = C.c_void_p, C.c_int32, C.c_uint32
+    L.gs_create.argtypes = [C.c_int, C.POINTER(vp)]
+    L.gs_destroy.argtypes = [vp]
+    L.gs_destroy.restype = None
+    L.gs_last_error.argtypes = [vp]
+    L.gs_last_error.restype = C.c_char_p
+    L.gs_version.restype = C.c_char_p
+    L.gs_upload_cluster.argtypes = [vp, C.POINTER(_GsCluster), i32]
+    L.gs_upload_predictions.argtypes = [vp, C.POINTER(_GsPredictions)]
+    L.gs_score_batch.argtypes = [vp, vp, vp, vp, i32, u32, vp, vp, vp]
+    L.gs_score_raw_dev.argtypes = [vp, vp, vp, vp, i32, u32, vp, vp, vp, vp, vp]
+    L.gs_normalize_dev.argtypes = [vp, i32, vp, vp, vp, vp, vp]
+    L.gs_normalize_scores.argtypes = [vp, vp, i32]
+    L.gs_select_mig.argtypes = [vp, vp, vp, i32, vp]
+    L.gs_set_profiling.argtypes = [vp, C.c_int]
+    L.gs_last_score_kernel_ms.argtypes = [vp, C.POINTER(C.c_float)]
+    L.gs_complete_fit.argtypes = [vp, vp, i32, i32, C.POINTER(vp)]
+    L.gs_complete_transform.argtypes = [vp, vp, vp, i32, vp]
+    L.gs_model_info.argtypes = [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]
+    L.gs_model_step.argtypes = [vp, i32, C.POINTER(i32), vp, C.POINTER(C.c_double)]
+    L.gs_model_destroy.argtypes = [vp]
+    L.gs_model_destroy.restype = None
+    _lib = L
+    return L
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data_as(C.c_void_p)
+    if hasattr(a, "data_ptr"):  # torch tensor (host pinned or device)
+        return C.c_void_p(a.data_ptr())
+    return C.c_void_p(int(a))
+
+
+class Scheduler:
+    """One context on one CUDA device: tables in HBM + the batched scoring entry points."""
+
+    def __init__(self, device: int = 0):
+        self._L = load_library()
+        h = C.c_void_p()
+        rc = self._L.gs_create(int(device), C.byref(h))
+        if rc != GS_OK:
+            raise GsError(rc, f"gs_create(device={device}) failed — no usable CUDA device? (no CPU fallback)")
+        self._h = h
+        self.device = int(device)
+        self.n_nodes = 0
+        self.n_res = 0
+
+    # -- plumbing ---------------------------------------------------------------------
+    def _check(self, rc: int):
+        if rc != GS_OK:
+            raise GsError(rc, self._L.gs_last_error(self._h).decode())
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.gs_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- uploads ----------------------------------------------------------------------
+    def upload_cluster(self, cl: Cluster, node_base: int = 0):
+        keep = [np.ascontiguousarray(cl.node_model, dtype=np.uint8), np.ascontiguousarray(cl.node_ngpu, dtype=np.uint8),
+                np.ascontiguousarray(cl.gpu_off, dtype=np.uint32), np.ascontiguousarray(cl.res_app, dtype=np.uint32),
+                np.ascontiguousarray(cl.res_slo, dtype=np.float32)]
+        s = _GsCluster(int(keep[0].shape[0]), int(cl.max_gpus), *[_ptr(a) for a in keep], int(cl.redis_reachable))
+        self._check(self._L.gs_upload_cluster(self._h, C.byref(s), int(node_base)))
+        self.n_nodes = int(keep[0].shape[0])
+        self.n_res = int(keep[3].shape[0])
+
+    def upload_predictions(self, pr: Predictions):
+        conf = np.ascontiguousarray(pr.conf, dtype=np.float32)
+        interf = np.ascontiguousarray(pr.interf, dtype=np.float32)
+        col_of = np.ascontiguousarray(pr.col_of, dtype=np.int32)
+        s = _GsPredictions(int(conf.shape[0]), int(conf.shape[1]) if conf.ndim == 2 else 0, _ptr(conf), _ptr(interf),
+                           _ptr(col_of))
+        self._check(self._L.gs_upload_predictions(self._h, C.byref(s)))
+
+    # -- scoring, host buffers --------------------------------------------------------
+    def score_batch(self, pods: Pods, normalize: bool = True, direct: bool = False, out=None, want_matrices=True):
+        """Score + (optionally) NormalizeScore for every (pod,node): returns (score, sel, best)."""
+        app = np.ascontiguousarray(pods.app, dtype=np.uint32)
+        slo = np.ascontiguousarray(pods.slo, dtype=np.float32)
+        self_slot = None if pods.self_slot is None else np.ascontiguousarray(pods.self_slot, dtype=np.int32)
+        P, N = int(app.shape[0]), self.n_nodes
+        if out is not None:
+            score, sel, best = out
+        elif want_matrices:
+            score = np.empty((P, N), dtype=np.uint8)
+            sel = np.empty((P, N), dtype=np.uint8)
+            best = np.empty(P, dtype=np.int32)
+        else:
+            score = sel = None
+            best = np.empty(P, dtype=np.int32)
+        flags = (SCORE_NORMALIZE if normalize else 0) | (SCORE_DIRECT if direct else 0)
+        self._check(self._L.gs_score_batch(self._h, _ptr(app), _ptr(slo), _ptr(self_slot), P, flags, _ptr(score),
+                                           _ptr(sel), _ptr(best)))
+        return score, sel, best
+
+    # -- scoring, device pointers (torch tensors or raw addresses) ----------------------
+    def score_raw_dev(self, d_app, d_slo, n_pods, d_score, d_sel, d_hi_arg, d_neg_lo, d_self=None, direct=False,
+                      stream=None):
+        self._check(self._L.gs_score_raw_dev(self._h, _ptr(d_app), _ptr(d_slo), _ptr(d_self), int(n_pods),
+                                             SCORE_DIRECT if direct else 0, _ptr(d_score), _ptr(d_sel),
+                                             _ptr(d_hi_arg), _ptr(d_neg_lo), _ptr(stream)))
+
+    def normalize_dev(self, n_pods, d_score, d_hi_arg, d_neg_lo, d_best=None, stream=None):
+        self._check(self._L.gs_normalize_dev(self._h, int(n_pods), _ptr(d_score), _ptr(d_hi_arg), _ptr(d_neg_lo),
+                                             _ptr(d_best), _ptr(stream)))
+
+    def set_profiling(self, enabled: bool):
+        self._check(self._L.gs_set_profiling(self._h, int(bool(enabled))))
+
+    def last_score_kernel_ms(self) -> float:
+        ms = C.c_float(0)
+        self._check(self._L.gs_last_score_kernel_ms(self._h, C.byref(ms)))
+        return float(ms.value)
+
+    # -- the other entry points -------------------------------------------------------
+    def normalize_scores(self, scores) -> np.ndarray:
+        a = np.ascontiguousarray(scores, dtype=np.int64).copy()
+        self._check(self._L.gs_normalize_scores(self._h, _ptr(a), int(a.shape[0])))
+        return a
+
+    def select_mig(self, pods: Pods) -> np.ndarray:
+        app = np.ascontiguousarray(pods.app, dtype=np.uint32)
+        slo = np.ascontiguousarray(pods.slo, dtype=np.float32)
+        out = np.empty(app.shape[0], dtype=np.uint8)
+        self._check(self._L.gs_select_mig(self._h, _ptr(app), _ptr(slo), int(app.shape[0]), _ptr(out)))
+        return out
+
+
+MIG_CONFIGS = ["all-4g.24gb", "all-2g.12gb", "all-1g.6gb"]  # gpu_plugins.go:52

@@ -1,0 +1,413 @@
+// context.cu — the C ABI of include/gpusched.h: context, table uploads, scoring entry
+// points.  Host logic only; kernels live in score_kernels.cu.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+
+#include "../../include/gpusched.h"
+#include "context.h"
+
+namespace gs {
+
+int Ctx::fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  err = buf;
+  return code;
+}
+
+int Ctx::cuda_fail(cudaError_t e, const char* what) {
+  return fail(GS_ERR_CUDA, "%s: %s (%s)", what, cudaGetErrorName(e), cudaGetErrorString(e));
+}
+
+// grow-only device buffer
+int Ctx::reserve(DevBuf& b, size_t bytes, const char* what) {
+  if (bytes <= b.cap) return GS_OK;
+  if (b.p) cudaFree(b.p);
+  b.p = nullptr;
+  b.cap = 0;
+  size_t want = bytes + bytes / 8 + 256;
+  cudaError_t e = cudaMalloc(&b.p, want);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail(GS_ERR_NOMEM, "cudaMalloc(%zu bytes) for %s: %s", want, what, cudaGetErrorString(e));
+  }
+  b.cap = want;
+  return GS_OK;
+}
+
+void Ctx::release(DevBuf& b) {
+  if (b.p) cudaFree(b.p);
+  b.p = nullptr;
+  b.cap = 0;
+}
+
+int Ctx::upload(DevBuf& b, const void* src, size_t bytes, const char* what) {
+  int rc = reserve(b, bytes ? bytes : 1, what);
+  if (rc) return rc;
+  if (bytes) {
+    cudaError_t e = cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, stream);
+    if (e != cudaSuccess) return cuda_fail(e, what);
+  }
+  return GS_OK;
+}
+
+DevTables Ctx::tables() const {
+  DevTables T;
+  T.n_nodes = n_nodes;
+  T.max_gpus = max_gpus;
+  T.n_apps = n_apps;
+  T.n_cols = n_cols;
+  T.redis_reachable = redis_reachable;
+  T.node_base = node_base;
+  T.node_model = (const uint8_t*)node_model.p;
+  T.node_ngpu = (const uint8_t*)node_ngpu.p;
+  T.gpu_off = (const uint32_t*)gpu_off.p;
+  T.res_app = (const uint32_t*)res_app.p;
+  T.res_slo = (const float*)res_slo.p;
+  T.conf = (const float*)conf.p;
+  T.interf = (const float*)interf.p;
+  T.col_of = (const int32_t*)col_of.p;
+  T.res_rec = (const float4*)res_rec.p;
+  return T;
+}
+
+// derive the per-resident records once both table sets are present
+int Ctx::ensure_prepared() {
+  if (!have_cluster || !have_preds)
+    return fail(GS_ERR_STATE, "scoring needs gs_upload_cluster and gs_upload_predictions first");
+  if (!prep_dirty) return GS_OK;
+  int rc = reserve(res_rec, sizeof(float4) * (size_t)(n_res ? n_res : 1), "res_rec");
+  if (rc) return rc;
+  DevTables T = tables();
+  cudaError_t e = launch_resident_prep(T, (float4*)res_rec.p, stream);
+  if (e != cudaSuccess) return cuda_fail(e, "resident_prep");
+  // rare (once per upload): finish here so that callers' own streams need no ordering with ours
+  e = cudaStreamSynchronize(stream);
+  if (e != cudaSuccess) return cuda_fail(e, "resident_prep sync");
+  prep_dirty = false;
+  return GS_OK;
+}
+
+int Ctx::ensure_scratch(int n_pods) {
+  uint32_t mc = max_chunks_for(n_pods, n_apps);
+  int rc;
+  if ((rc = reserve(sc_counts, sizeof(uint32_t) * (size_t)(n_apps + 2), "pod bucket counts"))) return rc;
+  if ((rc = reserve(sc_cursor, sizeof(uint32_t) * (size_t)(n_apps + 2), "pod bucket cursors"))) return rc;
+  if ((rc = reserve(sc_nchunks, 256, "chunk counter"))) return rc;
+  if ((rc = reserve(sc_chunks, sizeof(ChunkDesc) * (size_t)mc, "chunk descriptors"))) return rc;
+  if ((rc = reserve(sc_sorted, sizeof(PodRec) * (size_t)(n_pods ? n_pods : 1), "sorted pods"))) return rc;
+  return GS_OK;
+}
+
+}  // namespace gs
+
+using gs::Ctx;
+
+#define GS_LOCK(ctx) std::lock_guard<std::mutex> _lk((ctx)->mu)
+#define GS_CUDA(ctx, call)                                       \
+  do {                                                           \
+    cudaError_t _e = (call);                                     \
+    if (_e != cudaSuccess) return (ctx)->cuda_fail(_e, #call);   \
+  } while (0)
+
+struct gs_ctx : public gs::Ctx {};
+
+extern "C" {
+
+const char* gs_version(void) { return "gpusched 0.1 sm_100a " __DATE__; }
+
+int gs_create(int device, gs_ctx** out) {
+  if (!out) return GS_ERR_INVALID;
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    cudaGetLastError();
+    return GS_ERR_CUDA;  // no CPU fallback by design
+  }
+  if (device < 0 || device >= count) return GS_ERR_INVALID;
+  gs_ctx* c = new (std::nothrow) gs_ctx();
+  if (!c) return GS_ERR_NOMEM;
+  c->device = device;
+  if (cudaSetDevice(device) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    cudaGetLastError();
+    delete c;
+    return GS_ERR_CUDA;
+  }
+  *out = c;
+  return GS_OK;
+}
+
+void gs_destroy(gs_ctx* c) {
+  if (!c) return;
+  {
+    GS_LOCK(c);
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    gs::DevBuf* bufs[] = {&c->node_model, &c->node_ngpu, &c->gpu_off,   &c->res_app,   &c->res_slo, &c->conf,
+                          &c->interf,     &c->col_of,    &c->res_rec,   &c->sc_counts, &c->sc_cursor,
+                          &c->sc_nchunks, &c->sc_chunks, &c->sc_sorted, &c->b_pod_app, &c->b_pod_slo,
+                          &c->b_pod_self, &c->b_score,   &c->b_sel,     &c->b_extrema, &c->b_best,  &c->b_misc};
+    for (gs::DevBuf* b : bufs) c->release(*b);
+    if (c->ev_begin) cudaEventDestroy(c->ev_begin);
+    if (c->ev_end) cudaEventDestroy(c->ev_end);
+    cudaStreamDestroy(c->stream);
+  }
+  delete c;
+}
+
+const char* gs_last_error(const gs_ctx* c) { return c ? c->err.c_str() : "null context"; }
+
+int gs_upload_cluster(gs_ctx* c, const gs_cluster* cl, int32_t node_base) {
+  if (!c) return GS_ERR_INVALID;
+  GS_LOCK(c);
+  if (!cl) return c->fail(GS_ERR_INVALID, "gs_upload_cluster: null cluster");
+  if (cl->n_nodes < 0 || cl->max_gpus < 1 || cl->max_gpus > GS_MAX_GPUS_PER_NODE)
+    return c->fail(GS_ERR_INVALID, "gs_upload_cluster: n_nodes=%d max_gpus=%d out of range (max_gpus 1..%d)",
+                   cl->n_nodes, cl->max_gpus, GS_MAX_GPUS_PER_NODE);
+  const size_t N = (size_t)cl->n_nodes, slots = N * (size_t)cl->max_gpus;
+  if (N && (!cl->node_model || !cl->node_ngpu)) return c->fail(GS_ERR_INVALID, "gs_upload_cluster: null node table");
+  if (!cl->gpu_off) return c->fail(GS_ERR_INVALID, "gs_upload_cluster: null gpu_off");
+  if (cl->gpu_off[0] != 0) return c->fail(GS_ERR_INVALID, "gs_upload_cluster: gpu_off[0] must be 0");
+  for (size_t s = 0; s < slots; ++s)
+    if (cl->gpu_off[s + 1] < cl->gpu_off[s])
+      return c->fail(GS_ERR_INVALID, "gs_upload_cluster: gpu_off decreases at slot %zu", s);
+  for (size_t n = 0; n < N; ++n) {
+    if (cl->node_model[n] > GS_MODEL_V100)
+      return c->fail(GS_ERR_INVALID, "gs_upload_cluster: node %zu has model %d", n, (int)cl->node_model[n]);
+    if (cl->node_ngpu[n] > cl->max_gpus)
+      return c->fail(GS_ERR_INVALID, "gs_upload_cluster: node %zu lists %d GPUs > max_gpus %d", n,
+                     (int)cl->node_ngpu[n], cl->max_gpus);
+    for (int g = cl->node_ngpu[n]; g < cl->max_gpus; ++g)
+      if (cl->gpu_off[n * cl->max_gpus + g + 1] != cl->gpu_off[n * cl->max_gpus + g])
+        return c->fail(GS_ERR_INVALID, "gs_upload_cluster: node %zu slot %d beyond node_ngpu holds residents", n, g);
+  }
+  const size_t R = cl->gpu_off[slots];
+  if (R && (!cl->res_app || !cl->res_slo)) return c->fail(GS_ERR_INVALID, "gs_upload_cluster: null resident table");
+  GS_CUDA(c, cudaSetDevice(c->device));
+  int rc;
+  if ((rc = c->upload(c->node_model, cl->node_model, N, "node_model"))) return rc;
+  if ((rc = c->upload(c->node_ngpu, cl->node_ngpu, N, "node_ngpu"))) return rc;
+  if ((rc = c->upload(c->gpu_off, cl->gpu_off, sizeof(uint32_t) * (slots + 1), "gpu_off"))) return rc;
+  if ((rc = c->upload(c->res_app, cl->res_app, sizeof(uint32_t) * R, "res_app"))) return rc;
+  if ((rc = c->upload(c->res_slo, cl->res_slo, sizeof(float) * R, "res_slo"))) return rc;
+  GS_CUDA(c, cudaStreamSynchronize(c->stream));  // caller may free its buffers on return
+  c->n_nodes = cl->n_nodes;
+  c->max_gpus = cl->max_gpus;
+  c->n_res = (int64_t)R;
+  c->redis_reachable = cl->redis_reachable ? 1 : 0;
+  c->node_base = node_base;
+  c->have_cluster = true;
+  c->prep_dirty = true;
+  return GS_OK;
+}
+
+int gs_upload_predictions(gs_ctx* c, const gs_predictions* pr) {
+  if (!c) return GS_ERR_INVALID;
+  GS_LOCK(c);
+  if (!pr || pr->n_apps < 0 || pr->n_cols < 0 || !pr->col_of || (pr->n_apps && pr->n_cols && !pr->conf) ||
+      (pr->n_apps && !pr->interf))
+    return c->fail(GS_ERR_INVALID, "gs_upload_predictions: null table or negative size");
+  for (int i = 0; i < 2 * (GS_MAX_GPUS_PER_NODE + 1); ++i)
+    if (pr->col_of[i] >= pr->n_cols || pr->col_of[i] < -1)
+      return c->fail(GS_ERR_INVALID, "gs_upload_predictions: col_of[%d]=%d outside [-1,%d)", i, pr->col_of[i],
+                     pr->n_cols);
+  GS_CUDA(c, cudaSetDevice(c->device));
+  const size_t A = (size_t)pr->n_apps, K = (size_t)pr->n_cols;
+  int rc;
+  if ((rc = c->upload(c->conf, pr->conf, sizeof(float) * A * K, "conf"))) return rc;
+  if ((rc = c->upload(c->interf, pr->interf, sizeof(float) * 2 * A * A, "interf"))) return rc;
+  if ((rc = c->upload(c->col_of, pr->col_of, sizeof(int32_t) * 2 * (GS_MAX_GPUS_PER_NODE + 1), "col_of"))) return rc;
+  GS_CUDA(c, cudaStreamSynchronize(c->stream));
+  c->n_apps = pr->n_apps;
+  c->n_cols = pr->n_cols;
+  c->have_preds = true;
+  c->prep_dirty = true;
+  return GS_OK;
+}
+
+// shared by the host- and device-pointer entry points; ctx->mu held
+static int score_raw_locked(gs_ctx* c, const uint32_t* d_app, const float* d_slo, const int32_t* d_self, int32_t P,
+                            uint32_t flags, uint8_t* d_score, uint8_t* d_sel, uint64_t* d_hi, uint64_t* d_neg,
+                            cudaStream_t s) {
+  int rc = c->ensure_prepared();
+  if (rc) return rc;
+  GS_CUDA(c, cudaMemsetAsync(d_hi, 0, sizeof(uint64_t) * (size_t)P, s));
+  GS_CUDA(c, cudaMemsetAsync(d_neg, 0, sizeof(uint64_t) * (size_t)P, s));
+  gs::DevTables T = c->tables();
+  const bool fast = !(flags & GS_SCORE_DIRECT) && d_self == nullptr && c->max_gpus <= gs::kFastMaxGpus;
+  cudaError_t e;
+  if (fast && (rc = c->ensure_scratch(P))) return rc;
+  if (c->profiling) {
+    if (!c->ev_begin) {
+      GS_CUDA(c, cudaEventCreate(&c->ev_begin));
+      GS_CUDA(c, cudaEventCreate(&c->ev_end));
+    }
+    c->ev_valid = false;
+  }
+  if (fast) {
+    gs::PodScratch sc;
+    sc.counts = (uint32_t*)c->sc_counts.p;
+    sc.cursor = (uint32_t*)c->sc_cursor.p;
+    sc.n_chunks = (uint32_t*)c->sc_nchunks.p;
+    sc.chunks = (gs::ChunkDesc*)c->sc_chunks.p;
+    sc.sorted = (gs::PodRec*)c->sc_sorted.p;
+    sc.max_chunks = gs::max_chunks_for(P, c->n_apps);
+    e = gs::launch_score_fast(T, d_app, d_slo, P, sc, d_score, d_sel, (unsigned long long*)d_hi,
+                              (unsigned long long*)d_neg, s, c->profiling ? c->ev_begin : nullptr);
+  } else {
+    if (c->profiling) GS_CUDA(c, cudaEventRecord(c->ev_begin, s));
+    e = gs::launch_score_direct(T, d_app, d_slo, d_self, P, d_score, d_sel, (unsigned long long*)d_hi,
+                                (unsigned long long*)d_neg, s);
+  }
+  if (e != cudaSuccess) return c->cuda_fail(e, fast ? "score_fast" : "score_direct");
+  if (c->profiling) {
+    GS_CUDA(c, cudaEventRecord(c->ev_end, s));
+    c->ev_valid = true;
+  }
+  return GS_OK;
+}
+
+int gs_score_raw_dev(gs_ctx* c, const uint32_t* d_pod_app, const float* d_pod_slo, const int32_t* d_pod_self,
+                     int32_t n_pods, uint32_t flags, uint8_t* d_score, uint8_t* d_sel, uint64_t* d_hi_arg,
+                     uint64_t* d_neg_lo, void* stream) {
+  if (!c) return GS_ERR_INVALID;
+  GS_LOCK(c);
+  if (n_pods < 0 || (n_pods && (!d_pod_app || !d_pod_slo || !d_score || !d_sel || !d_hi_arg || !d_neg_lo)))
+    return c->fail(GS_ERR_INVALID, "gs_score_raw_dev: null pointer or negative n_pods");
+  GS_CUDA(c, cudaSetDevice(c->device));
+  if (n_pods == 0) return GS_OK;
+  return score_raw_locked(c, d_pod_app, d_pod_slo, d_pod_self, n_pods, flags, d_score, d_sel, d_hi_arg, d_neg_lo,
+                          stream ? (cudaStream_t)stream : c->stream);
+}
+
+int gs_normalize_dev(gs_ctx* c, int32_t n_pods, uint8_t* d_score, const uint64_t* d_hi_arg, const uint64_t* d_neg_lo,
+                     int32_t* d_best, void* stream) {
+  if (!c) return GS_ERR_INVALID;
+  GS_LOCK(c);
+  if (n_pods < 0 || (n_pods && (!d_score || !d_hi_arg || !d_neg_lo)))
+    return c->fail(GS_ERR_INVALID, "gs_normalize_dev: null pointer or negative n_pods");
+  if (!c->have_cluster) return c->fail(GS_ERR_STATE, "gs_normalize_dev before gs_upload_cluster");
+  GS_CUDA(c, cudaSetDevice(c->device));
+  cudaError_t e = gs::launch_normalize(n_pods, c->n_nodes, 1, d_score, (const unsigned long long*)d_hi_arg,
+                                       (const unsigned long long*)d_neg_lo, d_best,
+                                       stream ? (cudaStream_t)stream : c->stream);
+  if (e != cudaSuccess) return c->cuda_fail(e, "normalize");
+  return GS_OK;
+}
+
+int gs_score_batch(gs_ctx* c, const uint32_t* pod_app, const float* pod_slo, const int32_t* pod_self, int32_t P,
+                   uint32_t flags, uint8_t* out_score, uint8_t* out_sel, int32_t* out_best) {
+  if (!c) return GS_ERR_INVALID;
+  GS_LOCK(c);
+  if (P < 0 || (P && (!pod_app || !pod_slo))) return c->fail(GS_ERR_INVALID, "gs_score_batch: null pod table");
+  if (!c->have_cluster || !c->have_preds)
+    return c->fail(GS_ERR_STATE, "scoring needs gs_upload_cluster and gs_upload_predictions first");
+  if (P == 0) return GS_OK;
+  GS_CUDA(c, cudaSetDevice(c->device));
+  const size_t N = (size_t)c->n_nodes, PN = (size_t)P * N;
+  // a self table that excludes nobody is the common case: treat as absent
+  if (pod_self) {
+    bool any = false;
+    for (int32_t p = 0; p < P && !any; ++p) any = pod_self[p] >= 0;
+    if (!any) pod_self = nullptr;
+  }
+  if (pod_self)
+    for (int32_t p = 0; p < P; ++p)
+      if (pod_self[p] >= c->n_res) return c->fail(GS_ERR_INVALID, "gs_score_batch: pod_self[%d] beyond residents", p);
+  int rc;
+  cudaStream_t s = c->stream;
+  if ((rc = c->upload(c->b_pod_app, pod_app, sizeof(uint32_t) * (size_t)P, "pod_app"))) return rc;
+  if ((rc = c->upload(c->b_pod_slo, pod_slo, sizeof(float) * (size_t)P, "pod_slo"))) return rc;
+  if (pod_self && (rc = c->upload(c->b_pod_self, pod_self, sizeof(int32_t) * (size_t)P, "pod_self"))) return rc;
+  if ((rc = c->reserve(c->b_score, PN ? PN : 1, "scores"))) return rc;
+  if ((rc = c->reserve(c->b_sel, PN ? PN : 1, "selections"))) return rc;
+  if ((rc = c->reserve(c->b_extrema, sizeof(uint64_t) * 2 * (size_t)P, "extrema"))) return rc;
+  if ((rc = c->reserve(c->b_best, sizeof(int32_t) * (size_t)P, "best"))) return rc;
+  uint64_t* d_hi = (uint64_t*)c->b_extrema.p;
+  uint64_t* d_neg = d_hi + P;
+  rc = score_raw_locked(c, (const uint32_t*)c->b_pod_app.p, (const float*)c->b_pod_slo.p,
+                        pod_self ? (const int32_t*)c->b_pod_self.p : nullptr, P, flags, (uint8_t*)c->b_score.p,
+                        (uint8_t*)c->b_sel.p, d_hi, d_neg, s);
+  if (rc) return rc;
+  if (N) {
+    cudaError_t e = gs::launch_normalize(P, c->n_nodes, (flags & GS_SCORE_NORMALIZE) ? 1 : 0, (uint8_t*)c->b_score.p,
+                                         (const unsigned long long*)d_hi, (const unsigned long long*)d_neg,
+                                         (int32_t*)c->b_best.p, s);
+    if (e != cudaSuccess) return c->cuda_fail(e, "normalize");
+  }
+  if (out_score && PN) GS_CUDA(c, cudaMemcpyAsync(out_score, c->b_score.p, PN, cudaMemcpyDeviceToHost, s));
+  if (out_sel && PN) GS_CUDA(c, cudaMemcpyAsync(out_sel, c->b_sel.p, PN, cudaMemcpyDeviceToHost, s));
+  if (out_best) {
+    if (N)
+      GS_CUDA(c, cudaMemcpyAsync(out_best, c->b_best.p, sizeof(int32_t) * (size_t)P, cudaMemcpyDeviceToHost, s));
+    else
+      for (int32_t p = 0; p < P; ++p) out_best[p] = -1;
+  }
+  GS_CUDA(c, cudaStreamSynchronize(s));
+  return GS_OK;
+}
+
+int gs_normalize_scores(gs_ctx* c, int64_t* scores, int32_t n) {
+  if (!c) return GS_ERR_INVALID;
+  GS_LOCK(c);
+  if (n < 0 || (n && !scores)) return c->fail(GS_ERR_INVALID, "gs_normalize_scores: null list");
+  if (n == 0) return GS_OK;
+  GS_CUDA(c, cudaSetDevice(c->device));
+  int rc;
+  if ((rc = c->upload(c->b_misc, scores, sizeof(int64_t) * (size_t)n, "score list"))) return rc;
+  cudaError_t e = gs::launch_normalize_i64((long long*)c->b_misc.p, n, c->stream);
+  if (e != cudaSuccess) return c->cuda_fail(e, "normalize_i64");
+  GS_CUDA(c, cudaMemcpyAsync(scores, c->b_misc.p, sizeof(int64_t) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+  GS_CUDA(c, cudaStreamSynchronize(c->stream));
+  return GS_OK;
+}
+
+int gs_set_profiling(gs_ctx* c, int enabled) {
+  if (!c) return GS_ERR_INVALID;
+  GS_LOCK(c);
+  c->profiling = enabled != 0;
+  c->ev_valid = false;
+  return GS_OK;
+}
+
+int gs_last_score_kernel_ms(gs_ctx* c, float* out_ms) {
+  if (!c) return GS_ERR_INVALID;
+  GS_LOCK(c);
+  if (!out_ms) return c->fail(GS_ERR_INVALID, "gs_last_score_kernel_ms: null output");
+  if (!c->profiling || !c->ev_valid) return c->fail(GS_ERR_STATE, "no profiled scoring call to report");
+  GS_CUDA(c, cudaSetDevice(c->device));
+  GS_CUDA(c, cudaEventSynchronize(c->ev_end));
+  GS_CUDA(c, cudaEventElapsedTime(out_ms, c->ev_begin, c->ev_end));
+  return GS_OK;
+}
+
+int gs_select_mig(gs_ctx* c, const uint32_t* pod_app, const float* pod_slo, int32_t P, uint8_t* out) {
+  if (!c) return GS_ERR_INVALID;
+  GS_LOCK(c);
+  if (P < 0 || (P && (!pod_app || !pod_slo || !out))) return c->fail(GS_ERR_INVALID, "gs_select_mig: null pointer");
+  if (!c->have_preds) return c->fail(GS_ERR_STATE, "gs_select_mig before gs_upload_predictions");
+  if (P == 0) return GS_OK;
+  GS_CUDA(c, cudaSetDevice(c->device));
+  int rc;
+  if ((rc = c->upload(c->b_pod_app, pod_app, sizeof(uint32_t) * (size_t)P, "pod_app"))) return rc;
+  if ((rc = c->upload(c->b_pod_slo, pod_slo, sizeof(float) * (size_t)P, "pod_slo"))) return rc;
+  if ((rc = c->reserve(c->b_misc, (size_t)P, "mig choice"))) return rc;
+  gs::DevTables T = c->tables();
+  cudaError_t e = gs::launch_select_mig(T, (const uint32_t*)c->b_pod_app.p, (const float*)c->b_pod_slo.p, P,
+                                        (uint8_t*)c->b_misc.p, c->stream);
+  if (e != cudaSuccess) return c->cuda_fail(e, "select_mig");
+  GS_CUDA(c, cudaMemcpyAsync(out, c->b_misc.p, (size_t)P, cudaMemcpyDeviceToHost, c->stream));
+  GS_CUDA(c, cudaStreamSynchronize(c->stream));
+  return GS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,56 @@
+// context.h — the per-device context behind gs_ctx.
+#pragma once
+#include <cstdint>
+#include <mutex>
+#include <string>
+
+#include "tables.h"
+
+namespace gs {
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+};
+
+struct Ctx {
+  std::mutex mu;
+  std::string err;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+
+  // cluster snapshot
+  bool have_cluster = false;
+  int n_nodes = 0, max_gpus = 1, redis_reachable = 1, node_base = 0;
+  int64_t n_res = 0;
+  DevBuf node_model, node_ngpu, gpu_off, res_app, res_slo;
+  // prediction tables
+  bool have_preds = false;
+  int n_apps = 0, n_cols = 0;
+  DevBuf conf, interf, col_of;
+  // derived
+  bool prep_dirty = true;
+  DevBuf res_rec;
+  // scratch of the restructured scoring path
+  DevBuf sc_counts, sc_cursor, sc_nchunks, sc_chunks, sc_sorted;
+  // staging for the host-pointer entry points
+  DevBuf b_pod_app, b_pod_slo, b_pod_self, b_score, b_sel, b_extrema, b_best, b_misc;
+
+  // instrumentation
+  bool profiling = false;
+  bool ev_valid = false;
+  cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+
+  int fail(int code, const char* fmt, ...) __attribute__((format(printf, 3, 4)));
+  int cuda_fail(cudaError_t e, const char* what);
+  int reserve(DevBuf& b, size_t bytes, const char* what);
+  void release(DevBuf& b);
+  int upload(DevBuf& b, const void* src, size_t bytes, const char* what);
+  DevTables tables() const;
+  int ensure_prepared();
+  int ensure_scratch(int n_pods);
+};
+
+cudaError_t launch_normalize_i64(long long* scores, int n, cudaStream_t s);
+
+}  // namespace gs

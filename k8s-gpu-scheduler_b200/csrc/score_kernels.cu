@@ -1,0 +1,609 @@
+// score_kernels.cu — sm_100a kernels for Score -> Logic -> NormalizeScore.
+//
+// Reference: pkg/plugins/gpu_plugin/gpu_plugins.go:455-777 (Logic), :816-841
+// (NormalizeScore), :366-399 (MIG choice in reconfigure).
+//
+// Two scoring kernels produce identical bytes:
+//   score_direct_kernel  one thread per (pod,node), walks the GPU and resident lists
+//                        exactly like Logic() does; handles every case (self-exclusion,
+//                        up to 31 GPUs per node).
+//   score_fast_kernel    the restructured path.  A resident's term depends on the pod
+//                        being scheduled only through that pod's APP (its interference
+//                        column, :607-612), so pods are bucketed by app; one thread owns a
+//                        (node, app) pair, builds the node's per-GPU running sums
+//                        (negative_sum, positive_sum, counts, candidate interference)
+//                        ONCE in registers, then streams the bucket's pods through them.
+//                        Per pod and GPU only the candidate's own term and the weighted
+//                        combine remain.
+#include "score_math.cuh"
+#include "tables.h"
+#include "context.h"
+
+namespace gs {
+
+// ------------------------------------------------------------------ helpers ----------
+
+// Fold one pod's per-lane (score, node) into per-pod extrema.  key orders by score, then
+// by lowest thread id; 0 = lane holds no node.
+__device__ __forceinline__ uint32_t lane_key(int score, int tid_in_tile) {
+  return (((uint32_t)score << 7) | (uint32_t)(kTile - 1 - tid_in_tile)) + 1u;
+}
+
+__device__ __forceinline__ void publish_extrema(uint32_t key, uint32_t negmax, uint32_t tile_node0, int node_base,
+                                                uint32_t pod, unsigned long long* hi_arg,
+                                                unsigned long long* neg_lo) {
+  uint32_t k = key - 1u;
+  uint32_t score = k >> 7;
+  uint32_t node = tile_node0 + (uint32_t)(kTile - 1) - (k & 127u) + (uint32_t)node_base;
+  unsigned long long packed = ((unsigned long long)score << 32) | (unsigned long long)(0xFFFFFFFFu - node);
+  atomicMax(&hi_arg[pod], packed);
+  atomicMax(&neg_lo[pod], (unsigned long long)negmax);
+}
+
+// ------------------------------------------------------------------ resident prep ----
+
+// Per resident r of GPU slot s: the part of its term that does not depend on the pod
+// being scheduled.  gpu_plugins.go:572 (SLO==0 skip), :583-587 (conf column), :595-606
+// (co-resident interference, float32, in resident order).
+__global__ void resident_prep_kernel(DevTables T, float4* __restrict__ res_rec) {
+  int slot = blockIdx.x * blockDim.x + threadIdx.x;
+  if (slot >= T.n_nodes * T.max_gpus) return;
+  int node = slot / T.max_gpus;
+  int model = T.node_model[node];
+  int k = T.node_ngpu[node];
+  uint32_t lo = T.gpu_off[slot], hi = T.gpu_off[slot + 1];
+  int col = (model != kModelNone && k <= kMaxGpusPerNode) ? T.col_of[(model - 1) * (kMaxGpusPerNode + 1) + k] : -1;
+  size_t A = (size_t)T.n_apps;
+  for (uint32_t r = lo; r < hi; ++r) {
+    uint32_t app = T.res_app[r];
+    float slo = T.res_slo[r];
+    bool valid = model != kModelNone && slo != 0.0f && app < (uint32_t)T.n_apps && col >= 0;
+    float4 rec = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (valid) {
+      const float* row = T.interf + (size_t)(model - 1) * A * A + (size_t)app * A;
+      float S = 0.f;
+      for (uint32_t c = lo; c < hi; ++c) {
+        if (c == r) continue;
+        uint32_t ac = T.res_app[c];
+        if (ac < (uint32_t)T.n_apps) S = __fadd_rn(S, row[ac]);
+      }
+      rec = make_float4(slo, __fdiv_rn(1.0f, slo), T.conf[(size_t)app * T.n_cols + col], S);
+    }
+    res_rec[r] = rec;
+  }
+}
+
+cudaError_t launch_resident_prep(const DevTables& T, float4* res_rec, cudaStream_t s) {
+  int slots = T.n_nodes * T.max_gpus;
+  if (slots == 0) return cudaSuccess;
+  resident_prep_kernel<<<(slots + 127) / 128, 128, 0, s>>>(T, res_rec);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ direct kernel ----
+
+__device__ __forceinline__ bool conf_lookup(const DevTables& T, uint32_t app, int model, int k, float* out) {
+  if (app >= (uint32_t)T.n_apps || k < 0 || k > kMaxGpusPerNode) return false;
+  int col = T.col_of[(model - 1) * (kMaxGpusPerNode + 1) + k];
+  if (col < 0) return false;
+  *out = T.conf[(size_t)app * T.n_cols + col];
+  return true;
+}
+
+// V100 candidate prediction: smallest of 1P/2P/4P above the SLO, gpu_plugins.go:639-651
+__device__ __forceinline__ float conf_v100_for(const DevTables& T, uint32_t app, float slo, bool* f6) {
+  float c = -1.0f;
+  bool any = false;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    float tmp;
+    bool ok = conf_lookup(T, app, kModelV100, 1 << i, &tmp);
+    any |= ok;
+    if (ok && tmp > slo && (c == -1.0f || tmp < c)) c = tmp;
+  }
+  *f6 = any;
+  return c;
+}
+
+// Logic() for one (pod,node); grid = (pods, node tiles).
+__global__ void __launch_bounds__(kTile) score_direct_kernel(DevTables T, const uint32_t* __restrict__ pod_app,
+                                                            const float* __restrict__ pod_slo,
+                                                            const int32_t* __restrict__ pod_self,
+                                                            uint8_t* __restrict__ out_score,
+                                                            uint8_t* __restrict__ out_sel,
+                                                            unsigned long long* hi_arg,
+                                                            unsigned long long* neg_lo) {
+  __shared__ uint32_t s_key[kTile / 32], s_neg[kTile / 32];
+  const uint32_t p = blockIdx.x;
+  const int node = blockIdx.y * kTile + threadIdx.x;
+  const bool in_range = node < T.n_nodes;
+  const uint32_t app = pod_app[p];
+  const float cur_slo = pod_slo[p];
+  const int32_t self = pod_self ? pod_self[p] : -1;
+  const size_t A = (size_t)T.n_apps;
+
+  int score = 0;
+  unsigned sel = kSelNone, flags = 0;
+  if (in_range && T.redis_reachable) {
+    const int model = T.node_model[node];
+    const int k = T.node_ngpu[node];
+    if (model != kModelNone && k > 0) flags |= kFlagEligible;
+    if (model != kModelNone) {
+      const float inv_cur = __fdiv_rn(1.0f, cur_slo);
+      const float* itab = T.interf + (size_t)(model - 1) * A * A;
+      for (int g = 0; g < k; ++g) {
+        GpuAcc acc = {0.0, 0.0, 0, 0};
+        const uint32_t lo = T.gpu_off[(size_t)node * T.max_gpus + g];
+        const uint32_t hi = T.gpu_off[(size_t)node * T.max_gpus + g + 1];
+        for (uint32_t r = lo; r < hi; ++r) {
+          float slo = T.res_slo[r];
+          if (slo == 0.0f) continue;
+          uint32_t ar = T.res_app[r];
+          float conf;
+          if (!conf_lookup(T, ar, model, k, &conf)) continue;
+          float interf = 0.f;
+          for (uint32_t c = lo; c < hi; ++c) {
+            if (c == r || (self >= 0 && c == (uint32_t)self)) continue;
+            uint32_t ac = T.res_app[c];
+            if (ac < (uint32_t)T.n_apps) interf = __fadd_rn(interf, itab[(size_t)ar * A + ac]);
+          }
+          if (app < (uint32_t)T.n_apps) interf = __fadd_rn(interf, itab[(size_t)ar * A + app]);
+          add_term(acc, slo, __fdiv_rn(1.0f, slo), conf, interf);
+        }
+        float conf = -1.0f;
+        if (model == kModelA30) {
+          float v;
+          bool ok = conf_lookup(T, app, model, k, &v);
+          conf = ok ? v : 0.0f;
+          if (ok) flags |= kFlagF6;
+        } else {
+          bool f6;
+          conf = conf_v100_for(T, app, cur_slo, &f6);
+          if (f6) flags |= kFlagF6;
+        }
+        if (conf != -1.0f) {
+          flags |= kFlagF7;
+          float interf = 0.f;
+          if (app < (uint32_t)T.n_apps) {
+            for (uint32_t c = lo; c < hi; ++c) {
+              if (self >= 0 && c == (uint32_t)self) continue;
+              uint32_t ac = T.res_app[c];
+              if (ac < (uint32_t)T.n_apps) interf = __fadd_rn(interf, itab[(size_t)app * A + ac]);
+            }
+          }
+          add_term(acc, cur_slo, inv_cur, conf, interf);
+        }
+        int si = score_int(combine(acc.neg_sum, acc.pos_sum, acc.cnt_neg, acc.cnt_pos));
+        if (si > score) {
+          score = si;
+          sel = (unsigned)g;
+        }
+      }
+    }
+  }
+  if (in_range) {
+    size_t o = (size_t)p * T.n_nodes + node;
+    out_score[o] = (uint8_t)score;
+    out_sel[o] = (uint8_t)(sel | flags);
+  }
+  // per-pod extrema over this tile
+  uint32_t key = in_range ? lane_key(score, threadIdx.x) : 0u;
+  uint32_t neg = in_range ? (uint32_t)(100 - score) : 0u;
+  key = __reduce_max_sync(0xFFFFFFFFu, key);
+  neg = __reduce_max_sync(0xFFFFFFFFu, neg);
+  if ((threadIdx.x & 31) == 0) {
+    s_key[threadIdx.x >> 5] = key;
+    s_neg[threadIdx.x >> 5] = neg;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int w = 1; w < kTile / 32; ++w) {
+      key = max(key, s_key[w]);
+      neg = max(neg, s_neg[w]);
+    }
+    publish_extrema(key, neg, blockIdx.y * kTile, T.node_base, p, hi_arg, neg_lo);
+  }
+}
+
+cudaError_t launch_score_direct(const DevTables& T, const uint32_t* pod_app, const float* pod_slo,
+                                const int32_t* pod_self, int n_pods, uint8_t* score, uint8_t* sel,
+                                unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s) {
+  if (n_pods == 0 || T.n_nodes == 0) return cudaSuccess;
+  dim3 grid((unsigned)n_pods, (unsigned)((T.n_nodes + kTile - 1) / kTile));
+  score_direct_kernel<<<grid, kTile, 0, s>>>(T, pod_app, pod_slo, pod_self, score, sel, hi_arg, neg_lo);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ pod bucketing ----
+
+__global__ void pod_hist_kernel(const uint32_t* __restrict__ pod_app, int n_pods, int n_apps, uint32_t* counts) {
+  int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_pods) return;
+  uint32_t a = pod_app[p];
+  atomicAdd(&counts[a < (uint32_t)n_apps ? a : (uint32_t)n_apps], 1u);
+}
+
+// Single CTA: exclusive scan of the bucket sizes -> scatter cursors and chunk descriptors.
+__global__ void __launch_bounds__(1024) pod_scan_kernel(int n_apps, const uint32_t* __restrict__ counts,
+                                                        uint32_t* __restrict__ cursor,
+                                                        ChunkDesc* __restrict__ chunks, uint32_t* n_chunks,
+                                                        uint32_t max_chunks) {
+  __shared__ uint32_t s_warp_c[32], s_warp_n[32];
+  __shared__ uint32_t s_carry_c, s_carry_n;
+  if (threadIdx.x == 0) {
+    s_carry_c = 0;
+    s_carry_n = 0;
+  }
+  __syncthreads();
+  const int n_buckets = n_apps + 1;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int base = 0; base < n_buckets; base += 1024) {
+    int b = base + threadIdx.x;
+    uint32_t c = b < n_buckets ? counts[b] : 0u;
+    uint32_t n = (c + kChunk - 1) / kChunk;
+    uint32_t ic = c, in = n;  // inclusive warp scans
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      uint32_t tc = __shfl_up_sync(0xFFFFFFFFu, ic, d);
+      uint32_t tn = __shfl_up_sync(0xFFFFFFFFu, in, d);
+      if (lane >= d) {
+        ic += tc;
+        in += tn;
+      }
+    }
+    if (lane == 31) {
+      s_warp_c[warp] = ic;
+      s_warp_n[warp] = in;
+    }
+    __syncthreads();
+    if (warp == 0) {
+      uint32_t wc = s_warp_c[lane], wn = s_warp_n[lane];
+      uint32_t xc = wc, xn = wn;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        uint32_t tc = __shfl_up_sync(0xFFFFFFFFu, xc, d);
+        uint32_t tn = __shfl_up_sync(0xFFFFFFFFu, xn, d);
+        if (lane >= d) {
+          xc += tc;
+          xn += tn;
+        }
+      }
+      s_warp_c[lane] = xc - wc;  // exclusive warp offsets
+      s_warp_n[lane] = xn - wn;
+    }
+    __syncthreads();
+    uint32_t off_c = s_carry_c + s_warp_c[warp] + ic - c;
+    uint32_t off_n = s_carry_n + s_warp_n[warp] + in - n;
+    if (b < n_buckets) {
+      cursor[b] = off_c;
+      uint32_t app = b < n_apps ? (uint32_t)b : kAppUnknown;
+      for (uint32_t j = 0; j < n; ++j) {
+        if (off_n + j < max_chunks) {
+          uint32_t len = c - j * kChunk;
+          chunks[off_n + j] = ChunkDesc{app, off_c + j * kChunk, len < (uint32_t)kChunk ? len : (uint32_t)kChunk, 0u};
+        }
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 1023) {
+      s_carry_c = off_c + c;
+      s_carry_n = off_n + n;
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *n_chunks = s_carry_n < max_chunks ? s_carry_n : max_chunks;
+}
+
+__global__ void pod_scatter_kernel(DevTables T, const uint32_t* __restrict__ pod_app,
+                                   const float* __restrict__ pod_slo, int n_pods, uint32_t* cursor,
+                                   PodRec* __restrict__ sorted) {
+  int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_pods) return;
+  uint32_t a = pod_app[p];
+  float slo = pod_slo[p];
+  uint32_t pos = atomicAdd(&cursor[a < (uint32_t)T.n_apps ? a : (uint32_t)T.n_apps], 1u);
+  bool f6;
+  float c = conf_v100_for(T, a, slo, &f6);
+  PodRec rec;
+  rec.slo = slo;
+  rec.inv_slo = __fdiv_rn(1.0f, slo);
+  rec.conf_v100 = c;
+  rec.orig = (uint32_t)p | (f6 ? 0x80000000u : 0u);
+  sorted[pos] = rec;
+}
+
+// ------------------------------------------------------------------ fast kernel ------
+
+// grid = (chunk slots, node tiles); CTA = kTile threads = kTile consecutive nodes, all
+// working on the same app bucket chunk, so the pod loop is warp-uniform.
+__global__ void __launch_bounds__(kTile) score_fast_kernel(DevTables T, const PodRec* __restrict__ pods,
+                                                          const ChunkDesc* __restrict__ chunks,
+                                                          const uint32_t* __restrict__ n_chunks,
+                                                          uint8_t* __restrict__ out_score,
+                                                          uint8_t* __restrict__ out_sel,
+                                                          unsigned long long* hi_arg,
+                                                          unsigned long long* neg_lo) {
+  __shared__ PodRec s_pods[kChunk];
+  __shared__ uint32_t s_key[kTile / 32][kChunk];
+  __shared__ uint32_t s_neg[kTile / 32][kChunk];
+  if (blockIdx.x >= *n_chunks) return;
+  const ChunkDesc cd = chunks[blockIdx.x];
+  const int len = (int)cd.len;
+  if (threadIdx.x < len) s_pods[threadIdx.x] = pods[cd.start + threadIdx.x];
+
+  const uint32_t tile_node0 = blockIdx.y * kTile;
+  const int node = (int)tile_node0 + threadIdx.x;
+  const bool in_range = node < T.n_nodes;
+  const uint32_t app = cd.app;
+  const bool app_known = app < (uint32_t)T.n_apps;
+  const size_t A = (size_t)T.n_apps;
+
+  int model = kModelNone, k = 0;
+  if (in_range && T.redis_reachable) {
+    model = T.node_model[node];
+    k = T.node_ngpu[node];
+  }
+  const bool scored = model != kModelNone && k > 0;  // the GPU loop runs at least once
+  unsigned node_flags = scored ? kFlagEligible : 0u;
+
+  // per-GPU state, register resident
+  double neg_sum[kFastMaxGpus], pos_sum[kFastMaxGpus];
+  float cand_interf[kFastMaxGpus];
+  int cnt[kFastMaxGpus];  // cnt_neg | cnt_pos << 16
+  float conf_a30 = 0.0f;
+  int nocand = (int)kSelNone;  // score << 8 | sel for pods without a candidate term
+
+  if (scored) {
+    const float* itab = T.interf + (size_t)(model - 1) * A * A;
+    if (model == kModelA30) {
+      float v;
+      bool ok = conf_lookup(T, app, model, k, &v);
+      conf_a30 = ok ? v : 0.0f;  // missing key -> Go zero value, gpu_plugins.go:637
+      if (ok) node_flags |= kFlagF6;
+    }
+    int nc_score = 0;
+    unsigned nc_sel = kSelNone;
+#pragma unroll
+    for (int g = 0; g < kFastMaxGpus; ++g) {
+      GpuAcc acc = {0.0, 0.0, 0, 0};
+      float ci = 0.f;
+      if (g < k) {
+        const uint32_t lo = T.gpu_off[(size_t)node * T.max_gpus + g];
+        const uint32_t hi = T.gpu_off[(size_t)node * T.max_gpus + g + 1];
+        for (uint32_t r = lo; r < hi; ++r) {
+          const uint32_t ar = T.res_app[r];
+          const float4 rec = T.res_rec[r];
+          if (app_known && ar < (uint32_t)T.n_apps) ci = __fadd_rn(ci, itab[(size_t)app * A + ar]);
+          if (rec.x != 0.0f) {
+            float interf = rec.w;
+            if (app_known) interf = __fadd_rn(interf, itab[(size_t)ar * A + app]);
+            add_term(acc, rec.x, rec.y, rec.z, interf);
+          }
+        }
+        int si = score_int(combine(acc.neg_sum, acc.pos_sum, acc.cnt_neg, acc.cnt_pos));
+        if (si > nc_score) {
+          nc_score = si;
+          nc_sel = (unsigned)g;
+        }
+      }
+      neg_sum[g] = acc.neg_sum;
+      pos_sum[g] = acc.pos_sum;
+      cnt[g] = acc.cnt_neg | (acc.cnt_pos << 16);
+      cand_interf[g] = ci;
+    }
+    nocand = (nc_score << 8) | (int)nc_sel;
+  }
+  __syncthreads();
+
+  const int warp = threadIdx.x >> 5;
+  for (int i = 0; i < len; ++i) {
+    const PodRec pr = s_pods[i];
+    const uint32_t orig = pr.orig & 0x7FFFFFFFu;
+    int score = 0;
+    unsigned sel = kSelNone, flags = node_flags;
+    if (scored) {
+      float conf = conf_a30;
+      if (model == kModelV100) {
+        conf = pr.conf_v100;
+        if (pr.orig & 0x80000000u) flags |= kFlagF6;
+      }
+      if (conf == -1.0f) {  // gpu_plugins.go:667-696: residents only
+        score = nocand >> 8;
+        sel = (unsigned)(nocand & 0xFF);
+      } else {
+        flags |= kFlagF7;
+#pragma unroll
+        for (int g = 0; g < kFastMaxGpus; ++g) {
+          if (g < k) {
+            bool neg;
+            float t = term_t(pr.slo, pr.inv_slo, conf, cand_interf[g], &neg);
+            double v = term_value(t, neg);
+            double ns = neg ? __dadd_rn(neg_sum[g], v) : neg_sum[g];
+            double ps = neg ? pos_sum[g] : __dadd_rn(pos_sum[g], v);
+            int cn = (cnt[g] & 0xFFFF) + (neg ? 1 : 0);
+            int cp = (cnt[g] >> 16) + (neg ? 0 : 1);
+            int si = score_int(combine(ns, ps, cn, cp));
+            if (si > score) {
+              score = si;
+              sel = (unsigned)g;
+            }
+          }
+        }
+      }
+    }
+    if (in_range) {
+      size_t o = (size_t)orig * T.n_nodes + node;
+      out_score[o] = (uint8_t)score;
+      out_sel[o] = (uint8_t)(sel | flags);
+    }
+    uint32_t key = in_range ? lane_key(score, threadIdx.x) : 0u;
+    uint32_t neg = in_range ? (uint32_t)(100 - score) : 0u;
+    key = __reduce_max_sync(0xFFFFFFFFu, key);
+    neg = __reduce_max_sync(0xFFFFFFFFu, neg);
+    if ((threadIdx.x & 31) == 0) {
+      s_key[warp][i] = key;
+      s_neg[warp][i] = neg;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < len) {
+    uint32_t key = s_key[0][threadIdx.x], neg = s_neg[0][threadIdx.x];
+#pragma unroll
+    for (int w = 1; w < kTile / 32; ++w) {
+      key = max(key, s_key[w][threadIdx.x]);
+      neg = max(neg, s_neg[w][threadIdx.x]);
+    }
+    publish_extrema(key, neg, tile_node0, T.node_base, s_pods[threadIdx.x].orig & 0x7FFFFFFFu, hi_arg, neg_lo);
+  }
+}
+
+cudaError_t launch_score_fast(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
+                              const PodScratch& sc, uint8_t* score, uint8_t* sel, unsigned long long* hi_arg,
+                              unsigned long long* neg_lo, cudaStream_t s, cudaEvent_t before_main) {
+  if (n_pods == 0 || T.n_nodes == 0) return cudaSuccess;
+  cudaError_t e = cudaMemsetAsync(sc.counts, 0, sizeof(uint32_t) * (size_t)(T.n_apps + 2), s);
+  if (e != cudaSuccess) return e;
+  int pb = (n_pods + 255) / 256;
+  pod_hist_kernel<<<pb, 256, 0, s>>>(pod_app, n_pods, T.n_apps, sc.counts);
+  pod_scan_kernel<<<1, 1024, 0, s>>>(T.n_apps, sc.counts, sc.cursor, sc.chunks, sc.n_chunks, sc.max_chunks);
+  pod_scatter_kernel<<<pb, 256, 0, s>>>(T, pod_app, pod_slo, n_pods, sc.cursor, sc.sorted);
+  if (before_main && (e = cudaEventRecord(before_main, s)) != cudaSuccess) return e;
+  dim3 grid(sc.max_chunks, (unsigned)((T.n_nodes + kTile - 1) / kTile));
+  score_fast_kernel<<<grid, kTile, 0, s>>>(T, sc.sorted, sc.chunks, sc.n_chunks, score, sel, hi_arg, neg_lo);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ normalise --------
+
+// NormalizeScore (gpu_plugins.go:816-841) over raw scores in place: one warp per pod.
+// Raw scores lie in [0,100], so the integer rescale (s-lo)*100/(hi-lo) is a 101-entry
+// table per pod, built with the same truncating integer division.
+__global__ void __launch_bounds__(128) normalize_kernel(int n_pods, int n_nodes, int rescale,
+                                                       uint8_t* __restrict__ score,
+                                                       const unsigned long long* __restrict__ hi_arg,
+                                                       const unsigned long long* __restrict__ neg_lo,
+                                                       int32_t* __restrict__ best) {
+  __shared__ uint8_t s_lut[4][128];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int p = blockIdx.x * 4 + warp;
+  if (p >= n_pods) return;
+  const unsigned long long ha = hi_arg[p];
+  const int hi = (int)(ha >> 32);
+  const int lo = 100 - (int)neg_lo[p];
+  if (lane == 0 && best) best[p] = (int32_t)(0xFFFFFFFFu - (uint32_t)(ha & 0xFFFFFFFFull));
+  if (!rescale) return;
+  const int range = hi - lo;
+  uint8_t* lut = s_lut[warp];
+  for (int s = lane; s < 128; s += 32) {
+    int v = 0;
+    if (range != 0 && s >= lo && s <= hi) v = ((s - lo) * 100) / range;
+    lut[s] = (uint8_t)v;
+  }
+  __syncwarp();
+  uint8_t* row = score + (size_t)p * n_nodes;
+  // scalar head up to 16-byte alignment, vector body, scalar tail
+  uintptr_t addr = (uintptr_t)row;
+  int head = (int)((16 - (addr & 15)) & 15);
+  if (head > n_nodes) head = n_nodes;
+  for (int i = lane; i < head; i += 32) row[i] = lut[row[i] & 127];
+  int nvec = (n_nodes - head) / 16;
+  uint4* v4 = (uint4*)(row + head);
+  for (int i = lane; i < nvec; i += 32) {
+    uint4 v = v4[i];
+    uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      uint32_t x = w[j];
+      w[j] = (uint32_t)lut[x & 127] | ((uint32_t)lut[(x >> 8) & 127] << 8) | ((uint32_t)lut[(x >> 16) & 127] << 16) |
+             ((uint32_t)lut[(x >> 24) & 127] << 24);
+    }
+    v4[i] = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+  for (int i = head + nvec * 16 + lane; i < n_nodes; i += 32) row[i] = lut[row[i] & 127];
+}
+
+cudaError_t launch_normalize(int n_pods, int n_nodes, int rescale, uint8_t* score,
+                             const unsigned long long* hi_arg, const unsigned long long* neg_lo, int32_t* best,
+                             cudaStream_t s) {
+  if (n_pods == 0) return cudaSuccess;
+  normalize_kernel<<<(n_pods + 3) / 4, 128, 0, s>>>(n_pods, n_nodes, rescale, score, hi_arg, neg_lo, best);
+  return cudaGetLastError();
+}
+
+// NormalizeScore on one NodeScoreList of int64 scores, literally gpu_plugins.go:816-841.
+__global__ void __launch_bounds__(1024) normalize_i64_kernel(long long* __restrict__ scores, int n) {
+  __shared__ long long s_hi[32], s_lo[32];
+  long long hi = -0x7FFFFFFFFFFFFFFFLL, lo = 0x7FFFFFFFFFFFFFFFLL;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    long long v = scores[i];
+    hi = v > hi ? v : hi;
+    lo = v < lo ? v : lo;
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    long long oh = __shfl_xor_sync(0xFFFFFFFFu, hi, d), ol = __shfl_xor_sync(0xFFFFFFFFu, lo, d);
+    hi = oh > hi ? oh : hi;
+    lo = ol < lo ? ol : lo;
+  }
+  if ((threadIdx.x & 31) == 0) {
+    s_hi[threadIdx.x >> 5] = hi;
+    s_lo[threadIdx.x >> 5] = lo;
+  }
+  __syncthreads();
+  hi = s_hi[0];
+  lo = s_lo[0];
+  for (int w = 1; w < (int)(blockDim.x >> 5); ++w) {
+    hi = s_hi[w] > hi ? s_hi[w] : hi;
+    lo = s_lo[w] < lo ? s_lo[w] : lo;
+  }
+  const long long old_range = hi - lo, new_range = 100;
+  for (int i = threadIdx.x; i < n; i += blockDim.x)
+    scores[i] = old_range == 0 ? 0 : ((scores[i] - lo) * new_range / old_range);
+}
+
+cudaError_t launch_normalize_i64(long long* scores, int n, cudaStream_t s) {
+  if (n == 0) return cudaSuccess;
+  normalize_i64_kernel<<<1, 1024, 0, s>>>(scores, n);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ MIG choice -------
+
+// reconfigure()'s arithmetic, gpu_plugins.go:366-399; one thread per pod.
+__global__ void select_mig_kernel(DevTables T, const uint32_t* __restrict__ pod_app,
+                                  const float* __restrict__ pod_slo, int n_pods, uint8_t* __restrict__ out) {
+  int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_pods) return;
+  uint32_t app = pod_app[p];
+  float slo = pod_slo[p];
+  int opt = 0;
+  double max_score = 0.0;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    float conf;
+    if (!conf_lookup(T, app, kModelA30, 1 << i, &conf)) continue;
+    double sc;
+    if (slo > conf) {
+      double td = (double)__fadd_rn(__fsub_rn(slo, conf), 1.0f);
+      sc = __ddiv_rn(100.0, __dadd_rn(1.0, __dmul_rn(td, td)));
+    } else {
+      sc = __ddiv_rn(100.0, __dadd_rn(1.0, (double)__fsub_rn(slo, conf)));
+    }
+    if (sc >= max_score) {
+      max_score = sc;
+      opt = (1 << i) - 1;
+    }
+  }
+  if (opt == 3) opt = 2;
+  out[p] = (uint8_t)opt;
+}
+
+cudaError_t launch_select_mig(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
+                              uint8_t* out, cudaStream_t s) {
+  if (n_pods == 0) return cudaSuccess;
+  select_mig_kernel<<<(n_pods + 255) / 256, 256, 0, s>>>(T, pod_app, pod_slo, n_pods, out);
+  return cudaGetLastError();
+}
+
+}  // namespace gs

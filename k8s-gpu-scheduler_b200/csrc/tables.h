@@ -1,0 +1,77 @@
+// tables.h — device-side views of the structure-of-arrays tables and launcher prototypes.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace gs {
+
+// Device pointers to everything the scoring kernels read.  Passed by value.
+struct DevTables {
+  int n_nodes;
+  int max_gpus;
+  int n_apps;
+  int n_cols;
+  int redis_reachable;
+  int node_base;
+  const uint8_t* node_model;  // [N]
+  const uint8_t* node_ngpu;   // [N]
+  const uint32_t* gpu_off;    // [N*G+1]
+  const uint32_t* res_app;    // [R]
+  const float* res_slo;       // [R]
+  const float* conf;          // [A*K]
+  const float* interf;        // [2*A*A]
+  const int32_t* col_of;      // [2*32]
+  // derived per resident by resident_prep: {slo (0 = never contributes), 1/slo, conf, S}
+  // S = float32 sum, in resident order, of interf[row(r)][app(c)] over co-residents c != r
+  const float4* res_rec;      // [R]
+};
+
+// One pending pod in app-sorted order.
+struct PodRec {
+  float slo;
+  float inv_slo;    // float32 1/slo
+  float conf_v100;  // the V100 candidate prediction of gpu_plugins.go:639-651, -1 if none
+  uint32_t orig;    // bits 0..30 original pod index, bit 31 = F6 on V100 nodes
+};
+
+// A work item of the restructured kernel: up to kChunk pods of one app.
+struct ChunkDesc {
+  uint32_t app;
+  uint32_t start;
+  uint32_t len;
+  uint32_t pad;
+};
+
+constexpr int kChunk = 64;       // pods per work item
+constexpr int kFastMaxGpus = 8;  // GPUs per node the register-resident kernel covers
+constexpr int kTile = 128;       // nodes per CTA
+
+// Scratch of the restructured path (owned by the context, or the static no-alloc arena).
+struct PodScratch {
+  uint32_t* counts;   // [A+2] pods per app bucket (bucket A = unknown app)
+  uint32_t* cursor;   // [A+2] scatter cursors
+  uint32_t* n_chunks; // [1]
+  ChunkDesc* chunks;  // [max_chunks]
+  PodRec* sorted;     // [P]
+  uint32_t max_chunks;
+};
+
+inline uint32_t max_chunks_for(int n_pods, int n_apps) {
+  return (uint32_t)(n_pods / kChunk + n_apps + 2);
+}
+
+cudaError_t launch_resident_prep(const DevTables& T, float4* res_rec, cudaStream_t s);
+cudaError_t launch_score_direct(const DevTables& T, const uint32_t* pod_app, const float* pod_slo,
+                                const int32_t* pod_self, int n_pods, uint8_t* score, uint8_t* sel,
+                                unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s);
+cudaError_t launch_score_fast(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
+                              const PodScratch& scratch, uint8_t* score, uint8_t* sel,
+                              unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s,
+                              cudaEvent_t before_main = nullptr);
+cudaError_t launch_normalize(int n_pods, int n_nodes, int rescale, uint8_t* score,
+                             const unsigned long long* hi_arg, const unsigned long long* neg_lo,
+                             int32_t* best, cudaStream_t s);
+cudaError_t launch_select_mig(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
+                              uint8_t* out, cudaStream_t s);
+
+}  // namespace gs

@@ -1,0 +1,171 @@
+"""GPU parity: the CUDA scoring path, through the C ABI, against the CPU oracle.
+
+Bit-exact on raw scores, normalised scores, packed selection bytes (selected GPU + F-bits)
+and best node.  Both kernels (restructured and direct) are held to the same bar.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _check(sched, oracle_mod, preds, cluster, pods, node_base=0):
+    sched.upload_predictions(preds)
+    sched.upload_cluster(cluster, node_base=node_base)
+    ora = oracle_mod.Oracle(preds, cluster)
+    for normalize in (False, True):
+        want = ora.score_batch(pods, normalize=normalize, node_base=node_base)
+        for direct in (False, True):
+            got = sched.score_batch(pods, normalize=normalize, direct=direct)
+            for w, g, name in zip(want, got, ("score", "sel", "best")):
+                bad = np.argwhere(w != g)
+                assert bad.size == 0, (f"{name} differs at {bad[:5].tolist()} (normalize={normalize}, direct={direct}): "
+                                       f"want {w[tuple(bad[0])]}, got {g[tuple(bad[0])]}")
+
+
+def test_config1_1k_pods_100_nodes_8_gpus(sched, oracle_mod, synth):
+    """BASELINE.json configs[0]: the reference's own CPU-runnable case."""
+    preds, cluster, pods = synth.make_workload(1000, 100, gpus_per_node=8)
+    _check(sched, oracle_mod, preds, cluster, pods)
+
+
+def test_no_8p_column_variant(sched, oracle_mod, synth):
+    """The reference tables stop at 4P: every resident is skipped (:585-587), A30 candidates get conf 0 (:637)."""
+    preds, cluster, pods = synth.make_workload(400, 150, gpus_per_node=8, with_8p=False)
+    _check(sched, oracle_mod, preds, cluster, pods)
+
+
+def test_ragged_gpus_and_unknown_apps(sched, oracle_mod, synth):
+    preds, cluster, pods = synth.make_workload(700, 333, gpus_per_node=8, n_apps=97, ragged_gpus=True,
+                                               p_unknown_app=0.07)
+    _check(sched, oracle_mod, preds, cluster, pods)
+
+
+@pytest.mark.parametrize("n_pods,n_nodes,gpn", [(1, 1, 1), (3, 17, 2), (65, 129, 4), (257, 5, 8), (130, 1000, 8)])
+def test_odd_shapes(sched, oracle_mod, synth, n_pods, n_nodes, gpn):
+    preds, cluster, pods = synth.make_workload(n_pods, n_nodes, gpus_per_node=gpn, n_apps=33, seed=1234 + n_pods)
+    _check(sched, oracle_mod, preds, cluster, pods, node_base=1000)
+
+
+def test_more_than_8_gpus_per_node_uses_direct_kernel(sched, oracle_mod, synth):
+    preds, cluster, pods = synth.make_workload(200, 60, gpus_per_node=16, n_apps=50, with_8p=False, ragged_gpus=True)
+    # give the table columns that exist for some of the ragged GPU counts
+    _check(sched, oracle_mod, preds, cluster, pods)
+
+
+def test_single_app_many_pods_and_all_unique_apps(sched, oracle_mod, synth):
+    preds, cluster, pods = synth.make_workload(900, 140, gpus_per_node=8, n_apps=300)
+    one = synth.Pods(app=np.full(900, 5, dtype=np.uint32), slo=pods.slo)
+    _check(sched, oracle_mod, preds, cluster, one)
+    uniq = synth.Pods(app=(np.arange(900) % 300).astype(np.uint32), slo=pods.slo)
+    _check(sched, oracle_mod, preds, cluster, uniq)
+
+
+def test_special_slo_values(sched, oracle_mod, synth):
+    """SLO 0 (+Inf reciprocal), NaN, Inf, negative and denormal SLOs take the same IEEE path as Go."""
+    preds, cluster, pods = synth.make_workload(64, 120, gpus_per_node=8, n_apps=40)
+    slo = pods.slo.copy()
+    slo[:10] = [0.0, -0.0, np.nan, np.inf, -np.inf, -50.0, 1e-40, 3.4e38, 1e-30, 599.99]
+    _check(sched, oracle_mod, preds, cluster, synth.Pods(app=pods.app, slo=slo))
+    res = cluster.res_slo.copy()
+    res[::7] = np.nan
+    res[1::11] = -25.0
+    res[2::13] = np.inf
+    cluster.res_slo = res
+    _check(sched, oracle_mod, preds, cluster, pods)
+
+
+def test_redis_unreachable_scores_zero(sched, oracle_mod, synth):
+    preds, cluster, pods = synth.make_workload(50, 40, gpus_per_node=8, n_apps=20)
+    cluster.redis_reachable = 0
+    _check(sched, oracle_mod, preds, cluster, pods)
+    score, sel, best = sched.score_batch(pods, normalize=True)
+    assert not score.any() and (sel == 31).all() and (best == 0).all()
+
+
+def test_self_exclusion(sched, oracle_mod, synth):
+    """Pods that are themselves residents (gpu_plugins.go:596,:704)."""
+    preds, cluster, pods = synth.make_workload(300, 90, gpus_per_node=8, n_apps=30)
+    rng = np.random.default_rng(5)
+    R = cluster.res_app.size
+    self_slot = np.where(rng.random(300) < 0.5, rng.integers(0, R, size=300), -1).astype(np.int32)
+    app = pods.app.copy()
+    slo = pods.slo.copy()
+    m = self_slot >= 0
+    app[m] = cluster.res_app[self_slot[m]]
+    slo[m] = cluster.res_slo[self_slot[m]]
+    _check(sched, oracle_mod, preds, cluster, synth.Pods(app=app, slo=slo, self_slot=self_slot))
+    # an all -1 table is the same as none
+    _check(sched, oracle_mod, preds, cluster, synth.Pods(app=pods.app, slo=pods.slo, self_slot=np.full(300, -1, np.int32)))
+
+
+def test_empty_inputs(sched, synth):
+    preds, cluster, pods = synth.make_workload(10, 20, gpus_per_node=8, n_apps=8)
+    sched.upload_predictions(preds)
+    sched.upload_cluster(cluster)
+    score, sel, best = sched.score_batch(synth.Pods(app=np.zeros(0, np.uint32), slo=np.zeros(0, np.float32)))
+    assert score.shape == (0, 20) and best.shape == (0,)
+    empty = synth.make_cluster(0, 8, 8)
+    sched.upload_cluster(empty)
+    score, sel, best = sched.score_batch(pods)
+    assert score.shape == (10, 0) and (best == -1).all()
+
+
+def test_errors(pkg, synth):
+    s = pkg.Scheduler(0)
+    preds, cluster, pods = synth.make_workload(10, 20, gpus_per_node=8, n_apps=8)
+    with pytest.raises(pkg.GsError) as e:
+        s.score_batch(pods)
+    assert e.value.code == -3  # GS_ERR_STATE: nothing uploaded
+    bad = synth.make_cluster(5, 8, 8)
+    bad.node_model = bad.node_model.copy()
+    bad.node_model[0] = 9
+    with pytest.raises(pkg.GsError) as e:
+        s.upload_cluster(bad)
+    assert e.value.code == -1
+    s.close()
+
+
+def test_normalize_scores_list(sched, oracle_mod):
+    rng = np.random.default_rng(0)
+    for lst in ([10, 20, 30], [7, 7, 7], [0, 1, 3], [5], [], rng.integers(-1000, 1000, size=5000).tolist(),
+                [-(2 ** 40), 2 ** 40, 17]):
+        assert sched.normalize_scores(lst).tolist() == oracle_mod.normalize(lst).tolist()
+
+
+def test_select_mig(sched, oracle_mod, synth):
+    preds, cluster, pods = synth.make_workload(5000, 10, n_apps=200, p_unknown_app=0.05)
+    sched.upload_predictions(preds)
+    got = sched.select_mig(pods)
+    want = oracle_mod.Oracle(preds, cluster).select_mig(pods)
+    assert np.array_equal(got, want)
+    assert set(np.unique(got)) <= {0, 1, 2}
+    # tables without any A30 column: always configuration 0
+    preds2 = synth.make_predictions(200)
+    preds2.col_of[0, :] = -1
+    sched.upload_predictions(preds2)
+    assert not sched.select_mig(pods).any()
+
+
+def test_full_size_properties_fast_vs_direct(sched, oracle_mod, synth):
+    """At a size the oracle cannot finish quickly: the two independent CUDA kernels agree byte for
+    byte, NormalizeScore's invariants hold, and a sampled set of rows matches the oracle."""
+    preds, cluster, pods = synth.make_workload(6000, 2500, gpus_per_node=8)
+    sched.upload_predictions(preds)
+    sched.upload_cluster(cluster)
+    raw_f = sched.score_batch(pods, normalize=False)
+    raw_d = sched.score_batch(pods, normalize=False, direct=True)
+    for a, b in zip(raw_f, raw_d):
+        assert np.array_equal(a, b)
+    nrm, sel, best = sched.score_batch(pods, normalize=True)
+    raw = raw_f[0].astype(np.int64)
+    lo, hi = raw.min(axis=1, keepdims=True), raw.max(axis=1, keepdims=True)
+    rng_ = hi - lo
+    want = np.where(rng_ == 0, 0, (raw - lo) * 100 // np.where(rng_ == 0, 1, rng_))
+    assert np.array_equal(nrm, want.astype(np.uint8))
+    assert np.array_equal(best, raw.argmax(axis=1).astype(np.int32))          # lowest index among maxima
+    assert np.array_equal((sel & 31) == 31, raw_f[0] == 0)                     # a GPU is selected iff score >= 1
+    rows = np.random.default_rng(1).choice(6000, size=40, replace=False)
+    sub = synth.Pods(app=pods.app[rows], slo=pods.slo[rows])
+    w = oracle_mod.Oracle(preds, cluster).score_batch(sub, normalize=True)
+    assert np.array_equal(w[0], nrm[rows]) and np.array_equal(w[1], sel[rows]) and np.array_equal(w[2], best[rows])
