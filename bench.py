@@ -188,8 +188,13 @@ def main():
     d_best = torch.empty(P, dtype=torch.int32, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
+    # a non-default stream: a NULL stream argument would mean "the context's own stream"
+    work_stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(work_stream)
+
     def step():
         st = torch.cuda.current_stream().cuda_stream
+        assert st != 0
         sch.score_raw_dev(d_app, d_slo, P, d_score, d_sel, d_ext[0], d_ext[1], stream=st)
         if world > 1:
             dist.all_reduce(d_ext, op=dist.ReduceOp.MAX)

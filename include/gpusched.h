@@ -207,6 +207,11 @@ GS_API int gs_select_mig(gs_ctx* ctx, const uint32_t* pod_app, const float* pod_
  * events on the launching stream; gs_last_score_kernel_ms waits for the last bracket and
  * returns its duration.  Used by bench.py for the roofline figure. */
 GS_API int gs_set_profiling(gs_ctx* ctx, int enabled);
+/* Arithmetic self-test (no counterpart in the reference): runs the streamlined reciprocal,
+ * small-integer division and floor used by the restructured scoring kernel against CUDA's
+ * IEEE intrinsics on `n_million` x 10^6 pseudo-random operands and returns the number of
+ * results that differ in any bit (must be 0). */
+GS_API int gs_selftest(gs_ctx* ctx, uint64_t seed, int32_t n_million, uint64_t* out_mismatches);
 GS_API int gs_last_score_kernel_ms(gs_ctx* ctx, float* out_ms);
 
 /* ---------------------------------------------------------------- completion ------- */

@@ -30,7 +30,7 @@ ERR_NAMES = {-1: "GS_ERR_INVALID", -2: "GS_ERR_CUDA", -3: "GS_ERR_STATE", -4: "G
 EXPORTS = [
     "gs_create", "gs_destroy", "gs_last_error", "gs_version", "gs_upload_cluster", "gs_upload_predictions",
     "gs_score_batch", "gs_score_raw_dev", "gs_normalize_dev", "gs_normalize_scores", "gs_select_mig",
-    "gs_set_profiling", "gs_last_score_kernel_ms", "gs_complete_fit", "gs_complete_transform", "gs_model_info", "gs_model_step", "gs_model_destroy",
+    "gs_set_profiling", "gs_last_score_kernel_ms", "gs_selftest", "gs_complete_fit", "gs_complete_transform", "gs_model_info", "gs_model_step", "gs_model_destroy",
 ]
 
 
@@ -79,6 +79,7 @@ def load_library():
     L.gs_select_mig.argtypes = [vp, vp, vp, i32, vp]
     L.gs_set_profiling.argtypes = [vp, C.c_int]
     L.gs_last_score_kernel_ms.argtypes = [vp, C.POINTER(C.c_float)]
+    L.gs_selftest.argtypes = [vp, C.c_uint64, i32, C.POINTER(C.c_uint64)]
     L.gs_complete_fit.argtypes = [vp, vp, i32, i32, C.POINTER(vp)]
     L.gs_complete_transform.argtypes = [vp, vp, vp, i32, vp]
     L.gs_model_info.argtypes = [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]
@@ -186,6 +187,11 @@ class Scheduler:
         ms = C.c_float(0)
         self._check(self._L.gs_last_score_kernel_ms(self._h, C.byref(ms)))
         return float(ms.value)
+
+    def selftest(self, seed: int = 1, n_million: int = 100) -> int:
+        bad = C.c_uint64(0)
+        self._check(self._L.gs_selftest(self._h, int(seed), int(n_million), C.byref(bad)))
+        return int(bad.value)
 
     # -- the other entry points -------------------------------------------------------
     def normalize_scores(self, scores) -> np.ndarray:

@@ -281,8 +281,9 @@ int gs_score_raw_dev(gs_ctx* c, const uint32_t* d_pod_app, const float* d_pod_sl
                      uint64_t* d_neg_lo, void* stream) {
   if (!c) return GS_ERR_INVALID;
   GS_LOCK(c);
-  if (n_pods < 0 || (n_pods && (!d_pod_app || !d_pod_slo || !d_score || !d_sel || !d_hi_arg || !d_neg_lo)))
-    return c->fail(GS_ERR_INVALID, "gs_score_raw_dev: null pointer or negative n_pods");
+  if (n_pods < 0 || n_pods > gs::kMaxPods ||
+      (n_pods && (!d_pod_app || !d_pod_slo || !d_score || !d_sel || !d_hi_arg || !d_neg_lo)))
+    return c->fail(GS_ERR_INVALID, "gs_score_raw_dev: null pointer or n_pods outside [0, 2^30]");
   GS_CUDA(c, cudaSetDevice(c->device));
   if (n_pods == 0) return GS_OK;
   return score_raw_locked(c, d_pod_app, d_pod_slo, d_pod_self, n_pods, flags, d_score, d_sel, d_hi_arg, d_neg_lo,
@@ -308,7 +309,8 @@ int gs_score_batch(gs_ctx* c, const uint32_t* pod_app, const float* pod_slo, con
                    uint32_t flags, uint8_t* out_score, uint8_t* out_sel, int32_t* out_best) {
   if (!c) return GS_ERR_INVALID;
   GS_LOCK(c);
-  if (P < 0 || (P && (!pod_app || !pod_slo))) return c->fail(GS_ERR_INVALID, "gs_score_batch: null pod table");
+  if (P < 0 || P > gs::kMaxPods || (P && (!pod_app || !pod_slo)))
+    return c->fail(GS_ERR_INVALID, "gs_score_batch: null pod table or n_pods outside [0, 2^30]");
   if (!c->have_cluster || !c->have_preds)
     return c->fail(GS_ERR_STATE, "scoring needs gs_upload_cluster and gs_upload_predictions first");
   if (P == 0) return GS_OK;
@@ -387,6 +389,22 @@ int gs_last_score_kernel_ms(gs_ctx* c, float* out_ms) {
   GS_CUDA(c, cudaSetDevice(c->device));
   GS_CUDA(c, cudaEventSynchronize(c->ev_end));
   GS_CUDA(c, cudaEventElapsedTime(out_ms, c->ev_begin, c->ev_end));
+  return GS_OK;
+}
+
+int gs_selftest(gs_ctx* c, uint64_t seed, int32_t n_million, uint64_t* out_mismatches) {
+  if (!c) return GS_ERR_INVALID;
+  GS_LOCK(c);
+  if (!out_mismatches || n_million < 1) return c->fail(GS_ERR_INVALID, "gs_selftest: bad argument");
+  GS_CUDA(c, cudaSetDevice(c->device));
+  int rc;
+  if ((rc = c->reserve(c->b_misc, 256, "selftest counter"))) return rc;
+  GS_CUDA(c, cudaMemsetAsync(c->b_misc.p, 0, sizeof(unsigned long long), c->stream));
+  // 3907 blocks x 256 threads = 1 000 192 threads; iters operands each
+  cudaError_t e = gs::launch_selftest(seed, 3907, n_million, (unsigned long long*)c->b_misc.p, c->stream);
+  if (e != cudaSuccess) return c->cuda_fail(e, "selftest");
+  GS_CUDA(c, cudaMemcpyAsync(out_mismatches, c->b_misc.p, sizeof(uint64_t), cudaMemcpyDeviceToHost, c->stream));
+  GS_CUDA(c, cudaStreamSynchronize(c->stream));
   return GS_OK;
 }
 

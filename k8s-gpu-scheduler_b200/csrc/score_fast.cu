@@ -1,0 +1,278 @@
+// score_fast.cu — the restructured Score kernel (sm_100a).
+//
+// Reference: pkg/plugins/gpu_plugin/gpu_plugins.go:562-757 (the per-GPU loop of Logic).
+//
+// A resident's term depends on the pod being scheduled only through that pod's APP (the
+// interference column added last, :607-612), and so does the candidate's interference sum
+// (:703-714).  Pods are therefore bucketed by app; a CTA takes one work item = up to
+// kChunk pods of one app x kTile consecutive nodes, one thread per node.  Each thread
+//   1. builds, once, the running sums of each of its node's GPUs (negative_sum,
+//      positive_sum, counts) and the candidate interference, exactly as Logic does;
+//   2. folds everything of the weighted combine (:731-743) that does not depend on the
+//      candidate's own term into per-(GPU, branch) constants:
+//        branch "neg" (candidate's SLO > conf - interf):  tmp = cst + 100*((kk*(N0+v))/c)
+//        branch "pos":                                     tmp = cst + 100*((kk*(P0+v))/c)
+//      with kk = k or 1-k (1 if the other side is empty), c = the branch's count, cst =
+//      the other side's finished product (0 if empty).  These are the SAME IEEE
+//      operations in the SAME order as the reference performs — x*1.0 and 0.0+x are exact
+//      — so the result is bit-identical;
+//   3. streams the bucket's pods through them: per pod and GPU one reciprocal, one
+//      division by a small integer and eight other float64 operations remain.
+// kk/cst live in shared memory (one conflict-free 16-byte slot per thread, GPU and branch),
+// the sums in registers, {1/c, c} in a small shared table.
+//
+// Pods whose SLO is 0/NaN/Inf, lanes whose float32 term could overflow, and nodes whose
+// sums are not finite take the general path (score_math.cuh's op-for-op forms) — chosen
+// per warp, so the streamlined loop is divergence-free.
+#include "score_common.cuh"
+
+namespace gs {
+
+constexpr int kLutSize = 64;  // counts the {1/c, c} table covers
+
+struct FastSmem {
+  double2 kkcst[kFastMaxGpus][2][kTile];  // [g][0 = neg, 1 = pos][thread] = {kk, cst}
+  double2 lut[kLutSize];                  // {RN(1/c), (double)c}
+  PodRec pods[kChunk];
+  uint32_t key[kTile / 32][kChunk];
+  uint32_t neg[kTile / 32][kChunk];
+};
+static_assert(sizeof(FastSmem) <= 48 * 1024, "static shared memory");
+
+__global__ void __launch_bounds__(kTile, 4) score_fast_kernel(DevTables T, const PodRec* __restrict__ pods,
+                                                             const ChunkDesc* __restrict__ chunks,
+                                                             const uint32_t* __restrict__ n_chunks,
+                                                             uint8_t* __restrict__ out_score,
+                                                             uint8_t* __restrict__ out_sel,
+                                                             unsigned long long* hi_arg,
+                                                             unsigned long long* neg_lo) {
+  __shared__ FastSmem sm_storage;
+  FastSmem* sm = &sm_storage;
+  if (blockIdx.x >= *n_chunks) return;
+  const int tid = threadIdx.x;
+  const ChunkDesc cd = chunks[blockIdx.x];
+  const int len = (int)cd.len;
+  if (tid < len) sm->pods[tid] = pods[cd.start + tid];
+  if (tid < kLutSize) sm->lut[tid] = make_double2(tid ? __ddiv_rn(1.0, (double)tid) : 0.0, (double)tid);
+
+  const uint32_t tile_node0 = blockIdx.y * kTile;
+  const int node = (int)tile_node0 + tid;
+  const bool in_range = node < T.n_nodes;
+  const uint32_t app = cd.app;
+  const bool app_known = app < (uint32_t)T.n_apps;
+  const size_t A = (size_t)T.n_apps;
+
+  int model = kModelNone, k = 0;
+  if (in_range && T.redis_reachable) {
+    model = T.node_model[node];
+    k = T.node_ngpu[node];
+  }
+  const bool scored = model != kModelNone && k > 0;  // the GPU loop of Logic runs at least once
+  unsigned node_flags = scored ? kFlagEligible : 0u;
+
+  // register-resident per-GPU state of the streamlined loop
+  double base_n[kFastMaxGpus], base_p[kFastMaxGpus];
+  float cand_interf[kFastMaxGpus];
+  uint32_t lut_off[kFastMaxGpus];  // byte offsets of the neg (low half) / pos (high half) count in lut
+  float conf_a30 = 0.0f, ci_max = 0.0f;
+  int nocand = (int)kSelNone;  // score << 8 | sel for pods without a candidate term (:667-696)
+  bool thr_general = false;    // this node's sums/counts fall outside the streamlined domain
+
+  // GPUs a node does not have (and lanes without a node) get constants that evaluate to
+  // tmp = 0 + 100*((0*(0+v))/1) = 0: they can never win (a GPU needs int64(tmp) >= 1), so
+  // the streamlined loop runs all kFastMaxGpus slots without a guard.
+#pragma unroll
+  for (int g = 0; g < kFastMaxGpus; ++g) {
+    base_n[g] = 0.0;
+    base_p[g] = 0.0;
+    cand_interf[g] = 0.f;
+    lut_off[g] = 16u | (16u << 16);
+    sm->kkcst[g][0][tid] = make_double2(0.0, 0.0);
+    sm->kkcst[g][1][tid] = make_double2(0.0, 0.0);
+  }
+  if (scored) {
+    const float* itab = T.interf + (size_t)(model - 1) * A * A;
+    if (model == kModelA30) {
+      float v;
+      bool ok = conf_lookup(T, app, model, k, &v);
+      conf_a30 = ok ? v : 0.0f;  // missing key -> Go zero value, gpu_plugins.go:637
+      if (ok) node_flags |= kFlagF6;
+    }
+    int nc_score = 0;
+    unsigned nc_sel = kSelNone;
+#pragma unroll
+    for (int g = 0; g < kFastMaxGpus; ++g) {
+      if (g < k) {
+        GpuAcc acc = {0.0, 0.0, 0, 0};
+        float ci = 0.f;
+        const uint32_t lo = T.gpu_off[(size_t)node * T.max_gpus + g];
+        const uint32_t hi = T.gpu_off[(size_t)node * T.max_gpus + g + 1];
+        for (uint32_t r = lo; r < hi; ++r) {
+          const uint32_t ar = T.res_app[r];
+          const float4 rec = T.res_rec[r];
+          if (app_known && ar < (uint32_t)T.n_apps) ci = __fadd_rn(ci, itab[(size_t)app * A + ar]);
+          if (rec.x != 0.0f) {
+            float interf = rec.w;
+            if (app_known) interf = __fadd_rn(interf, itab[(size_t)ar * A + app]);
+            add_term(acc, rec.x, rec.y, rec.z, interf);
+          }
+        }
+        const int cn0 = acc.cnt_neg, cp0 = acc.cnt_pos;
+        int si = score_int(combine(acc.neg_sum, acc.pos_sum, cn0, cp0));
+        if (si > nc_score) {
+          nc_score = si;
+          nc_sel = (unsigned)g;
+        }
+        // constants of the two branches (same operations, same order as combine())
+        double kk_n = 1.0, cst_n = 0.0, kk_p = 1.0, cst_p = 0.0;
+        if (cp0 > 0) {  // candidate lands on the negative side, positives exist
+          double kq = __ddiv_rn((double)(cn0 + 1), (double)(cn0 + 1 + cp0));
+          kk_n = kq;
+          cst_n = __dmul_rn(100.0, __ddiv_rn(__dmul_rn(__dsub_rn(1.0, kq), acc.pos_sum), (double)cp0));
+        }
+        if (cn0 > 0) {  // candidate lands on the positive side, negatives exist
+          double kq = __ddiv_rn((double)cn0, (double)(cn0 + cp0 + 1));
+          kk_p = __dsub_rn(1.0, kq);
+          cst_p = __dmul_rn(100.0, __ddiv_rn(__dmul_rn(kq, acc.neg_sum), (double)cn0));
+        }
+        sm->kkcst[g][0][tid] = make_double2(kk_n, cst_n);
+        sm->kkcst[g][1][tid] = make_double2(kk_p, cst_p);
+        base_n[g] = acc.neg_sum;
+        base_p[g] = acc.pos_sum;
+        cand_interf[g] = ci;
+        lut_off[g] = (uint32_t)((cn0 + 1) * 16) | ((uint32_t)((cp0 + 1) * 16) << 16);
+        ci_max = fmaxf(ci_max, fabsf(ci));
+        // streamlined domain: finite sums and candidate interference, counts inside the table
+        const bool fin = fabs(acc.neg_sum) <= 1e300 && fabs(acc.pos_sum) <= 1e300 && fabs(cst_n) <= 1e300 &&
+                         fabs(cst_p) <= 1e300 && fabsf(ci) <= 3.0e38f;
+        if (!fin || cn0 + 1 >= kLutSize || cp0 + 1 >= kLutSize) thr_general = true;
+      }
+    }
+    nocand = (nc_score << 8) | (int)nc_sel;
+  }
+  __syncthreads();
+
+  const int warp = tid >> 5;
+  const unsigned char* lut_bytes = reinterpret_cast<const unsigned char*>(sm->lut);
+  for (int i = 0; i < len; ++i) {
+    const PodRec pr = sm->pods[i];
+    const uint32_t orig = pr.orig & kPodIndexMask;
+    float conf = conf_a30;
+    unsigned flags = node_flags;
+    if (model == kModelV100) {
+      conf = pr.conf_v100;
+      if (pr.orig & kPodF6) flags |= kFlagF6;
+    }
+    const bool has_cand = scored && conf != -1.0f;
+    int packed = nocand;  // also right for !scored lanes: score 0, nothing selected
+    // May any lane's float32 term leave the finite range?  |t| <= |1/slo|*(|slo|+|conf|+max|ci|).
+    const float t_bound = fabsf(pr.inv_slo) * (fabsf(pr.slo) + fabsf(conf) + ci_max);
+    const bool lane_general = has_cand && (thr_general || !(t_bound < 1.0e38f));
+    const bool warp_general = (pr.orig & kPodSpecial) || __any_sync(0xFFFFFFFFu, lane_general);
+    if (!warp_general) {
+      int score = 0;
+      unsigned sel = kSelNone;
+#pragma unroll
+      for (int g = 0; g < kFastMaxGpus; ++g) {
+        bool neg;
+        const float t = term_t(pr.slo, pr.inv_slo, conf, cand_interf[g], &neg);
+        double w = fabs((double)t);
+        if (neg) w = __dadd_rn(w, 1.0);
+        if (neg) w = __dmul_rn(w, w);
+        const double v = rcp_ge1(__dadd_rn(1.0, w));
+        const double2 kc = sm->kkcst[g][neg ? 0 : 1][tid];
+        const uint32_t off = neg ? (lut_off[g] & 0xFFFFu) : (lut_off[g] >> 16);
+        const double2 rc = *reinterpret_cast<const double2*>(lut_bytes + off);
+        const double S = __dadd_rn(neg ? base_n[g] : base_p[g], v);
+        const double q = div_small_int(__dmul_rn(kc.x, S), rc.x, rc.y);
+        const int si = floor_nonneg(__dadd_rn(kc.y, __dmul_rn(100.0, q)));
+        if (si > score) {
+          score = si;
+          sel = (unsigned)g;
+        }
+      }
+      if (has_cand) packed = (score << 8) | (int)sel;
+    } else if (has_cand) {
+      unsigned selbyte;
+      const int sc = logic_eval(T, app, pr.slo, -1, node, &selbyte);
+      packed = (sc << 8) | (int)(selbyte & 31u);
+    }
+    if (has_cand) flags |= kFlagF7;
+    const int score = packed >> 8;
+    if (in_range) {
+      const size_t o = (size_t)orig * T.n_nodes + node;
+      out_score[o] = (uint8_t)score;
+      out_sel[o] = (uint8_t)((unsigned)(packed & 0xFF) | flags);
+    }
+    uint32_t key = in_range ? lane_key(score, tid) : 0u;
+    uint32_t ngm = in_range ? (uint32_t)(100 - score) : 0u;
+    key = __reduce_max_sync(0xFFFFFFFFu, key);
+    ngm = __reduce_max_sync(0xFFFFFFFFu, ngm);
+    if ((tid & 31) == 0) {
+      sm->key[warp][i] = key;
+      sm->neg[warp][i] = ngm;
+    }
+  }
+  __syncthreads();
+  if (tid < len) {
+    uint32_t key = sm->key[0][tid], ngm = sm->neg[0][tid];
+#pragma unroll
+    for (int w = 1; w < kTile / 32; ++w) {
+      key = max(key, sm->key[w][tid]);
+      ngm = max(ngm, sm->neg[w][tid]);
+    }
+    publish_extrema(key, ngm, tile_node0, T.node_base, sm->pods[tid].orig & kPodIndexMask, hi_arg, neg_lo);
+  }
+}
+
+cudaError_t launch_score_fast(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
+                              const PodScratch& sc, uint8_t* score, uint8_t* sel, unsigned long long* hi_arg,
+                              unsigned long long* neg_lo, cudaStream_t s, cudaEvent_t before_main) {
+  if (n_pods == 0 || T.n_nodes == 0) return cudaSuccess;
+  static_assert(kChunk <= kTile, "a CTA loads its pods with one thread each");
+  cudaError_t e = launch_pod_bucketing(T, pod_app, pod_slo, n_pods, sc, s);
+  if (e != cudaSuccess) return e;
+  if (before_main && (e = cudaEventRecord(before_main, s)) != cudaSuccess) return e;
+  dim3 grid(sc.max_chunks, (unsigned)((T.n_nodes + kTile - 1) / kTile));
+  score_fast_kernel<<<grid, kTile, 0, s>>>(T, sc.sorted, sc.chunks, sc.n_chunks, score, sel, hi_arg,
+                                                          neg_lo);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ self test --------
+
+// Compares the streamlined arithmetic with CUDA's IEEE intrinsics on pseudo-random
+// operands from the domains the kernel uses them on; counts mismatches.
+__global__ void selftest_kernel(unsigned long long seed, int iters, unsigned long long* mismatches) {
+  unsigned long long x = seed + 0x9E3779B97F4A7C15ull * (blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x + 1);
+  unsigned long long bad = 0;
+  for (int it = 0; it < iters; ++it) {
+    x ^= x << 13;
+    x ^= x >> 7;
+    x ^= x << 17;
+    // z >= 1: random mantissa, exponent 0..258 (the kernel's z is below 2^257)
+    unsigned long long mant = x & 0x000FFFFFFFFFFFFFull;
+    unsigned long long ez = 1023ull + ((x >> 52) % 259ull);
+    double z = __longlong_as_double((long long)((ez << 52) | mant));
+    if (__double_as_longlong(rcp_ge1(z)) != __double_as_longlong(__drcp_rn(z))) ++bad;
+    // m in (2^-300, 2^10), c in 1..63
+    unsigned long long y = x * 0xD1342543DE82EF95ull + 1ull;
+    unsigned long long em = 723ull + ((y >> 52) % 310ull);
+    double m = __longlong_as_double((long long)((em << 52) | (y & 0x000FFFFFFFFFFFFFull)));
+    int c = 1 + (int)((y >> 40) % 63ull);
+    double cd = (double)c;
+    if (__double_as_longlong(div_small_int(m, __ddiv_rn(1.0, cd), cd)) != __double_as_longlong(__ddiv_rn(m, cd))) ++bad;
+    // floor of v in [0, 128)
+    double v = (double)(y >> 11) * (1.0 / 70368744177664.0);  // 2^53 / 2^46 = 128
+    if (floor_nonneg(v) != __double2int_rz(v)) ++bad;
+  }
+  if (bad) atomicAdd(mismatches, bad);
+}
+
+cudaError_t launch_selftest(unsigned long long seed, int blocks, int iters, unsigned long long* d_mismatches,
+                            cudaStream_t s) {
+  selftest_kernel<<<blocks, 256, 0, s>>>(seed, iters, d_mismatches);
+  return cudaGetLastError();
+}
+
+}  // namespace gs

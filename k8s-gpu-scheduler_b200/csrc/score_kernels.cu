@@ -15,30 +15,10 @@
 //                        ONCE in registers, then streams the bucket's pods through them.
 //                        Per pod and GPU only the candidate's own term and the weighted
 //                        combine remain.
-#include "score_math.cuh"
-#include "tables.h"
+#include "score_common.cuh"
 #include "context.h"
 
 namespace gs {
-
-// ------------------------------------------------------------------ helpers ----------
-
-// Fold one pod's per-lane (score, node) into per-pod extrema.  key orders by score, then
-// by lowest thread id; 0 = lane holds no node.
-__device__ __forceinline__ uint32_t lane_key(int score, int tid_in_tile) {
-  return (((uint32_t)score << 7) | (uint32_t)(kTile - 1 - tid_in_tile)) + 1u;
-}
-
-__device__ __forceinline__ void publish_extrema(uint32_t key, uint32_t negmax, uint32_t tile_node0, int node_base,
-                                                uint32_t pod, unsigned long long* hi_arg,
-                                                unsigned long long* neg_lo) {
-  uint32_t k = key - 1u;
-  uint32_t score = k >> 7;
-  uint32_t node = tile_node0 + (uint32_t)(kTile - 1) - (k & 127u) + (uint32_t)node_base;
-  unsigned long long packed = ((unsigned long long)score << 32) | (unsigned long long)(0xFFFFFFFFu - node);
-  atomicMax(&hi_arg[pod], packed);
-  atomicMax(&neg_lo[pod], (unsigned long long)negmax);
-}
 
 // ------------------------------------------------------------------ resident prep ----
 
@@ -82,29 +62,6 @@ cudaError_t launch_resident_prep(const DevTables& T, float4* res_rec, cudaStream
 
 // ------------------------------------------------------------------ direct kernel ----
 
-__device__ __forceinline__ bool conf_lookup(const DevTables& T, uint32_t app, int model, int k, float* out) {
-  if (app >= (uint32_t)T.n_apps || k < 0 || k > kMaxGpusPerNode) return false;
-  int col = T.col_of[(model - 1) * (kMaxGpusPerNode + 1) + k];
-  if (col < 0) return false;
-  *out = T.conf[(size_t)app * T.n_cols + col];
-  return true;
-}
-
-// V100 candidate prediction: smallest of 1P/2P/4P above the SLO, gpu_plugins.go:639-651
-__device__ __forceinline__ float conf_v100_for(const DevTables& T, uint32_t app, float slo, bool* f6) {
-  float c = -1.0f;
-  bool any = false;
-#pragma unroll
-  for (int i = 0; i < 3; ++i) {
-    float tmp;
-    bool ok = conf_lookup(T, app, kModelV100, 1 << i, &tmp);
-    any |= ok;
-    if (ok && tmp > slo && (c == -1.0f || tmp < c)) c = tmp;
-  }
-  *f6 = any;
-  return c;
-}
-
 // Logic() for one (pod,node); grid = (pods, node tiles).
 __global__ void __launch_bounds__(kTile) score_direct_kernel(DevTables T, const uint32_t* __restrict__ pod_app,
                                                             const float* __restrict__ pod_slo,
@@ -117,74 +74,13 @@ __global__ void __launch_bounds__(kTile) score_direct_kernel(DevTables T, const 
   const uint32_t p = blockIdx.x;
   const int node = blockIdx.y * kTile + threadIdx.x;
   const bool in_range = node < T.n_nodes;
-  const uint32_t app = pod_app[p];
-  const float cur_slo = pod_slo[p];
-  const int32_t self = pod_self ? pod_self[p] : -1;
-  const size_t A = (size_t)T.n_apps;
-
   int score = 0;
-  unsigned sel = kSelNone, flags = 0;
-  if (in_range && T.redis_reachable) {
-    const int model = T.node_model[node];
-    const int k = T.node_ngpu[node];
-    if (model != kModelNone && k > 0) flags |= kFlagEligible;
-    if (model != kModelNone) {
-      const float inv_cur = __fdiv_rn(1.0f, cur_slo);
-      const float* itab = T.interf + (size_t)(model - 1) * A * A;
-      for (int g = 0; g < k; ++g) {
-        GpuAcc acc = {0.0, 0.0, 0, 0};
-        const uint32_t lo = T.gpu_off[(size_t)node * T.max_gpus + g];
-        const uint32_t hi = T.gpu_off[(size_t)node * T.max_gpus + g + 1];
-        for (uint32_t r = lo; r < hi; ++r) {
-          float slo = T.res_slo[r];
-          if (slo == 0.0f) continue;
-          uint32_t ar = T.res_app[r];
-          float conf;
-          if (!conf_lookup(T, ar, model, k, &conf)) continue;
-          float interf = 0.f;
-          for (uint32_t c = lo; c < hi; ++c) {
-            if (c == r || (self >= 0 && c == (uint32_t)self)) continue;
-            uint32_t ac = T.res_app[c];
-            if (ac < (uint32_t)T.n_apps) interf = __fadd_rn(interf, itab[(size_t)ar * A + ac]);
-          }
-          if (app < (uint32_t)T.n_apps) interf = __fadd_rn(interf, itab[(size_t)ar * A + app]);
-          add_term(acc, slo, __fdiv_rn(1.0f, slo), conf, interf);
-        }
-        float conf = -1.0f;
-        if (model == kModelA30) {
-          float v;
-          bool ok = conf_lookup(T, app, model, k, &v);
-          conf = ok ? v : 0.0f;
-          if (ok) flags |= kFlagF6;
-        } else {
-          bool f6;
-          conf = conf_v100_for(T, app, cur_slo, &f6);
-          if (f6) flags |= kFlagF6;
-        }
-        if (conf != -1.0f) {
-          flags |= kFlagF7;
-          float interf = 0.f;
-          if (app < (uint32_t)T.n_apps) {
-            for (uint32_t c = lo; c < hi; ++c) {
-              if (self >= 0 && c == (uint32_t)self) continue;
-              uint32_t ac = T.res_app[c];
-              if (ac < (uint32_t)T.n_apps) interf = __fadd_rn(interf, itab[(size_t)app * A + ac]);
-            }
-          }
-          add_term(acc, cur_slo, inv_cur, conf, interf);
-        }
-        int si = score_int(combine(acc.neg_sum, acc.pos_sum, acc.cnt_neg, acc.cnt_pos));
-        if (si > score) {
-          score = si;
-          sel = (unsigned)g;
-        }
-      }
-    }
-  }
   if (in_range) {
+    unsigned selbyte;
+    score = logic_eval(T, pod_app[p], pod_slo[p], pod_self ? pod_self[p] : -1, node, &selbyte);
     size_t o = (size_t)p * T.n_nodes + node;
     out_score[o] = (uint8_t)score;
-    out_sel[o] = (uint8_t)(sel | flags);
+    out_sel[o] = (uint8_t)selbyte;
   }
   // per-pod extrema over this tile
   uint32_t key = in_range ? lane_key(score, threadIdx.x) : 0u;
@@ -309,168 +205,22 @@ __global__ void pod_scatter_kernel(DevTables T, const uint32_t* __restrict__ pod
   rec.slo = slo;
   rec.inv_slo = __fdiv_rn(1.0f, slo);
   rec.conf_v100 = c;
-  rec.orig = (uint32_t)p | (f6 ? 0x80000000u : 0u);
+  // "plain" pods have a finite non-zero SLO with a finite reciprocal: the streamlined
+  // arithmetic of score_fast_kernel applies; anything else takes its general path
+  const bool plain = slo != 0.0f && fabsf(slo) <= 3.0e38f && fabsf(rec.inv_slo) <= 3.0e38f;
+  rec.orig = (uint32_t)p | (f6 ? kPodF6 : 0u) | (plain ? 0u : kPodSpecial);
   sorted[pos] = rec;
 }
 
-// ------------------------------------------------------------------ fast kernel ------
-
-// grid = (chunk slots, node tiles); CTA = kTile threads = kTile consecutive nodes, all
-// working on the same app bucket chunk, so the pod loop is warp-uniform.
-__global__ void __launch_bounds__(kTile) score_fast_kernel(DevTables T, const PodRec* __restrict__ pods,
-                                                          const ChunkDesc* __restrict__ chunks,
-                                                          const uint32_t* __restrict__ n_chunks,
-                                                          uint8_t* __restrict__ out_score,
-                                                          uint8_t* __restrict__ out_sel,
-                                                          unsigned long long* hi_arg,
-                                                          unsigned long long* neg_lo) {
-  __shared__ PodRec s_pods[kChunk];
-  __shared__ uint32_t s_key[kTile / 32][kChunk];
-  __shared__ uint32_t s_neg[kTile / 32][kChunk];
-  if (blockIdx.x >= *n_chunks) return;
-  const ChunkDesc cd = chunks[blockIdx.x];
-  const int len = (int)cd.len;
-  if (threadIdx.x < len) s_pods[threadIdx.x] = pods[cd.start + threadIdx.x];
-
-  const uint32_t tile_node0 = blockIdx.y * kTile;
-  const int node = (int)tile_node0 + threadIdx.x;
-  const bool in_range = node < T.n_nodes;
-  const uint32_t app = cd.app;
-  const bool app_known = app < (uint32_t)T.n_apps;
-  const size_t A = (size_t)T.n_apps;
-
-  int model = kModelNone, k = 0;
-  if (in_range && T.redis_reachable) {
-    model = T.node_model[node];
-    k = T.node_ngpu[node];
-  }
-  const bool scored = model != kModelNone && k > 0;  // the GPU loop runs at least once
-  unsigned node_flags = scored ? kFlagEligible : 0u;
-
-  // per-GPU state, register resident
-  double neg_sum[kFastMaxGpus], pos_sum[kFastMaxGpus];
-  float cand_interf[kFastMaxGpus];
-  int cnt[kFastMaxGpus];  // cnt_neg | cnt_pos << 16
-  float conf_a30 = 0.0f;
-  int nocand = (int)kSelNone;  // score << 8 | sel for pods without a candidate term
-
-  if (scored) {
-    const float* itab = T.interf + (size_t)(model - 1) * A * A;
-    if (model == kModelA30) {
-      float v;
-      bool ok = conf_lookup(T, app, model, k, &v);
-      conf_a30 = ok ? v : 0.0f;  // missing key -> Go zero value, gpu_plugins.go:637
-      if (ok) node_flags |= kFlagF6;
-    }
-    int nc_score = 0;
-    unsigned nc_sel = kSelNone;
-#pragma unroll
-    for (int g = 0; g < kFastMaxGpus; ++g) {
-      GpuAcc acc = {0.0, 0.0, 0, 0};
-      float ci = 0.f;
-      if (g < k) {
-        const uint32_t lo = T.gpu_off[(size_t)node * T.max_gpus + g];
-        const uint32_t hi = T.gpu_off[(size_t)node * T.max_gpus + g + 1];
-        for (uint32_t r = lo; r < hi; ++r) {
-          const uint32_t ar = T.res_app[r];
-          const float4 rec = T.res_rec[r];
-          if (app_known && ar < (uint32_t)T.n_apps) ci = __fadd_rn(ci, itab[(size_t)app * A + ar]);
-          if (rec.x != 0.0f) {
-            float interf = rec.w;
-            if (app_known) interf = __fadd_rn(interf, itab[(size_t)ar * A + app]);
-            add_term(acc, rec.x, rec.y, rec.z, interf);
-          }
-        }
-        int si = score_int(combine(acc.neg_sum, acc.pos_sum, acc.cnt_neg, acc.cnt_pos));
-        if (si > nc_score) {
-          nc_score = si;
-          nc_sel = (unsigned)g;
-        }
-      }
-      neg_sum[g] = acc.neg_sum;
-      pos_sum[g] = acc.pos_sum;
-      cnt[g] = acc.cnt_neg | (acc.cnt_pos << 16);
-      cand_interf[g] = ci;
-    }
-    nocand = (nc_score << 8) | (int)nc_sel;
-  }
-  __syncthreads();
-
-  const int warp = threadIdx.x >> 5;
-  for (int i = 0; i < len; ++i) {
-    const PodRec pr = s_pods[i];
-    const uint32_t orig = pr.orig & 0x7FFFFFFFu;
-    int score = 0;
-    unsigned sel = kSelNone, flags = node_flags;
-    if (scored) {
-      float conf = conf_a30;
-      if (model == kModelV100) {
-        conf = pr.conf_v100;
-        if (pr.orig & 0x80000000u) flags |= kFlagF6;
-      }
-      if (conf == -1.0f) {  // gpu_plugins.go:667-696: residents only
-        score = nocand >> 8;
-        sel = (unsigned)(nocand & 0xFF);
-      } else {
-        flags |= kFlagF7;
-#pragma unroll
-        for (int g = 0; g < kFastMaxGpus; ++g) {
-          if (g < k) {
-            bool neg;
-            float t = term_t(pr.slo, pr.inv_slo, conf, cand_interf[g], &neg);
-            double v = term_value(t, neg);
-            double ns = neg ? __dadd_rn(neg_sum[g], v) : neg_sum[g];
-            double ps = neg ? pos_sum[g] : __dadd_rn(pos_sum[g], v);
-            int cn = (cnt[g] & 0xFFFF) + (neg ? 1 : 0);
-            int cp = (cnt[g] >> 16) + (neg ? 0 : 1);
-            int si = score_int(combine(ns, ps, cn, cp));
-            if (si > score) {
-              score = si;
-              sel = (unsigned)g;
-            }
-          }
-        }
-      }
-    }
-    if (in_range) {
-      size_t o = (size_t)orig * T.n_nodes + node;
-      out_score[o] = (uint8_t)score;
-      out_sel[o] = (uint8_t)(sel | flags);
-    }
-    uint32_t key = in_range ? lane_key(score, threadIdx.x) : 0u;
-    uint32_t neg = in_range ? (uint32_t)(100 - score) : 0u;
-    key = __reduce_max_sync(0xFFFFFFFFu, key);
-    neg = __reduce_max_sync(0xFFFFFFFFu, neg);
-    if ((threadIdx.x & 31) == 0) {
-      s_key[warp][i] = key;
-      s_neg[warp][i] = neg;
-    }
-  }
-  __syncthreads();
-  if (threadIdx.x < len) {
-    uint32_t key = s_key[0][threadIdx.x], neg = s_neg[0][threadIdx.x];
-#pragma unroll
-    for (int w = 1; w < kTile / 32; ++w) {
-      key = max(key, s_key[w][threadIdx.x]);
-      neg = max(neg, s_neg[w][threadIdx.x]);
-    }
-    publish_extrema(key, neg, tile_node0, T.node_base, s_pods[threadIdx.x].orig & 0x7FFFFFFFu, hi_arg, neg_lo);
-  }
-}
-
-cudaError_t launch_score_fast(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
-                              const PodScratch& sc, uint8_t* score, uint8_t* sel, unsigned long long* hi_arg,
-                              unsigned long long* neg_lo, cudaStream_t s, cudaEvent_t before_main) {
-  if (n_pods == 0 || T.n_nodes == 0) return cudaSuccess;
+// Bucket the pods by app: histogram -> scan (cursors + work items) -> scatter.
+cudaError_t launch_pod_bucketing(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
+                                 const PodScratch& sc, cudaStream_t s) {
   cudaError_t e = cudaMemsetAsync(sc.counts, 0, sizeof(uint32_t) * (size_t)(T.n_apps + 2), s);
   if (e != cudaSuccess) return e;
   int pb = (n_pods + 255) / 256;
   pod_hist_kernel<<<pb, 256, 0, s>>>(pod_app, n_pods, T.n_apps, sc.counts);
   pod_scan_kernel<<<1, 1024, 0, s>>>(T.n_apps, sc.counts, sc.cursor, sc.chunks, sc.n_chunks, sc.max_chunks);
   pod_scatter_kernel<<<pb, 256, 0, s>>>(T, pod_app, pod_slo, n_pods, sc.cursor, sc.sorted);
-  if (before_main && (e = cudaEventRecord(before_main, s)) != cudaSuccess) return e;
-  dim3 grid(sc.max_chunks, (unsigned)((T.n_nodes + kTile - 1) / kTile));
-  score_fast_kernel<<<grid, kTile, 0, s>>>(T, sc.sorted, sc.chunks, sc.n_chunks, score, sel, hi_arg, neg_lo);
   return cudaGetLastError();
 }
 

@@ -31,8 +31,12 @@ struct PodRec {
   float slo;
   float inv_slo;    // float32 1/slo
   float conf_v100;  // the V100 candidate prediction of gpu_plugins.go:639-651, -1 if none
-  uint32_t orig;    // bits 0..30 original pod index, bit 31 = F6 on V100 nodes
+  uint32_t orig;    // bits 0..29 original pod index, kPodF6, kPodSpecial
 };
+constexpr uint32_t kPodF6 = 0x80000000u;       // F6 holds on V100 nodes (some 1P/2P/4P column exists)
+constexpr uint32_t kPodSpecial = 0x40000000u;  // SLO is 0, NaN or infinite (or its reciprocal is)
+constexpr uint32_t kPodIndexMask = 0x3FFFFFFFu;
+constexpr int kMaxPods = 1 << 30;
 
 // A work item of the restructured kernel: up to kChunk pods of one app.
 struct ChunkDesc {
@@ -42,7 +46,7 @@ struct ChunkDesc {
   uint32_t pad;
 };
 
-constexpr int kChunk = 64;       // pods per work item
+constexpr int kChunk = 128;      // pods per work item
 constexpr int kFastMaxGpus = 8;  // GPUs per node the register-resident kernel covers
 constexpr int kTile = 128;       // nodes per CTA
 
@@ -64,10 +68,14 @@ cudaError_t launch_resident_prep(const DevTables& T, float4* res_rec, cudaStream
 cudaError_t launch_score_direct(const DevTables& T, const uint32_t* pod_app, const float* pod_slo,
                                 const int32_t* pod_self, int n_pods, uint8_t* score, uint8_t* sel,
                                 unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s);
+cudaError_t launch_pod_bucketing(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
+                                 const PodScratch& scratch, cudaStream_t s);
 cudaError_t launch_score_fast(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
                               const PodScratch& scratch, uint8_t* score, uint8_t* sel,
                               unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s,
                               cudaEvent_t before_main = nullptr);
+cudaError_t launch_selftest(unsigned long long seed, int blocks, int iters, unsigned long long* d_mismatches,
+                            cudaStream_t s);
 cudaError_t launch_normalize(int n_pods, int n_nodes, int rescale, uint8_t* score,
                              const unsigned long long* hi_arg, const unsigned long long* neg_lo,
                              int32_t* best, cudaStream_t s);

@@ -169,3 +169,46 @@ def test_full_size_properties_fast_vs_direct(sched, oracle_mod, synth):
     sub = synth.Pods(app=pods.app[rows], slo=pods.slo[rows])
     w = oracle_mod.Oracle(preds, cluster).score_batch(sub, normalize=True)
     assert np.array_equal(w[0], nrm[rows]) and np.array_equal(w[1], sel[rows]) and np.array_equal(w[2], best[rows])
+
+
+def test_streamlined_arithmetic_matches_ieee_intrinsics(sched):
+    """rcp_ge1 / div_small_int / floor_nonneg (score_math.cuh) against __drcp_rn / __ddiv_rn /
+    __double2int_rz on 3 x 2*10^8 pseudo-random operands: not one differing bit."""
+    assert sched.selftest(seed=0xB2005EED, n_million=200) == 0
+    assert sched.selftest(seed=12345, n_million=50) == 0
+
+
+def test_overflowing_terms_take_the_general_path(sched, oracle_mod, synth):
+    """Tiny SLOs make the float32 term overflow to Inf inside otherwise ordinary pods/residents."""
+    preds, cluster, pods = synth.make_workload(200, 150, gpus_per_node=8, n_apps=20)
+    slo = pods.slo.copy()
+    slo[::3] = 1e-37
+    slo[1::5] = 3e-39   # denormal
+    slo[2::7] = -1e-36
+    res = cluster.res_slo.copy()
+    res[::5] = 1e-37
+    cluster.res_slo = res
+    preds.conf[3, :] = np.inf
+    preds.conf[4, :] = np.nan
+    preds.interf[0, 5, :] = 3e38
+    preds.interf[1, :, 6] = -3e38
+    _check(sched, oracle_mod, preds, cluster, synth.Pods(app=pods.app, slo=slo))
+
+
+def test_many_residents_per_gpu(sched, oracle_mod, synth):
+    """Counts beyond the small-integer table (>= 63 residents on a GPU) and mid-size counts."""
+    preds, cluster, pods = synth.make_workload(150, 40, gpus_per_node=2, n_apps=25)
+    rng = np.random.default_rng(3)
+    counts = rng.integers(0, 12, size=40 * 2)
+    counts[5] = 70
+    counts[17] = 64
+    counts[18] = 62
+    off = np.zeros(81, dtype=np.uint32)
+    off[1:] = np.cumsum(counts)
+    R = int(off[-1])
+    cluster.gpu_off = off
+    cluster.node_ngpu = np.full(40, 2, dtype=np.uint8)
+    cluster.res_app = rng.integers(0, 25, size=R).astype(np.uint32)
+    cluster.res_slo = np.round(rng.uniform(10, 600, size=R), 2).astype(np.float32)
+    preds.col_of[:, 2] = preds.col_of[:, 8]  # give the tables a 2P column
+    _check(sched, oracle_mod, preds, cluster, pods)
