@@ -283,7 +283,7 @@ int gs_score_raw_dev(gs_ctx* c, const uint32_t* d_pod_app, const float* d_pod_sl
   GS_LOCK(c);
   if (n_pods < 0 || n_pods > gs::kMaxPods ||
       (n_pods && (!d_pod_app || !d_pod_slo || !d_score || !d_sel || !d_hi_arg || !d_neg_lo)))
-    return c->fail(GS_ERR_INVALID, "gs_score_raw_dev: null pointer or n_pods outside [0, 2^30]");
+    return c->fail(GS_ERR_INVALID, "gs_score_raw_dev: null pointer or n_pods outside [0, 2^29]");
   GS_CUDA(c, cudaSetDevice(c->device));
   if (n_pods == 0) return GS_OK;
   return score_raw_locked(c, d_pod_app, d_pod_slo, d_pod_self, n_pods, flags, d_score, d_sel, d_hi_arg, d_neg_lo,
@@ -310,7 +310,7 @@ int gs_score_batch(gs_ctx* c, const uint32_t* pod_app, const float* pod_slo, con
   if (!c) return GS_ERR_INVALID;
   GS_LOCK(c);
   if (P < 0 || P > gs::kMaxPods || (P && (!pod_app || !pod_slo)))
-    return c->fail(GS_ERR_INVALID, "gs_score_batch: null pod table or n_pods outside [0, 2^30]");
+    return c->fail(GS_ERR_INVALID, "gs_score_batch: null pod table or n_pods outside [0, 2^29]");
   if (!c->have_cluster || !c->have_preds)
     return c->fail(GS_ERR_STATE, "scoring needs gs_upload_cluster and gs_upload_predictions first");
   if (P == 0) return GS_OK;

@@ -21,9 +21,14 @@
 // kk/cst live in shared memory (one conflict-free 16-byte slot per thread, GPU and branch),
 // the sums in registers, {1/c, c} in a small shared table.
 //
-// Pods whose SLO is 0/NaN/Inf, lanes whose float32 term could overflow, and nodes whose
-// sums are not finite take the general path (score_math.cuh's op-for-op forms) — chosen
-// per warp, so the streamlined loop is divergence-free.
+// Pods without an SLO (SLO 0, 10 % of the synthetic batch; also denormal SLOs) have an
+// infinite 1/SLO: the candidate's term is exactly 0 (or NaN when SLO == conf - interf), so
+// int64(tmp) per (GPU, branch) is a per-thread constant, precomputed in step 2, and the pod
+// costs a handful of float32 compares per GPU.
+//
+// Pods whose SLO is NaN/Inf, lanes whose float32 term could overflow, and nodes whose
+// sums are not finite take the general path (score_common.cuh's op-for-op logic_eval) —
+// chosen per warp, so the streamlined loop is divergence-free.
 #include "score_common.cuh"
 
 namespace gs {
@@ -32,6 +37,7 @@ constexpr int kLutSize = 64;  // counts the {1/c, c} table covers
 
 struct FastSmem {
   double2 kkcst[kFastMaxGpus][2][kTile];  // [g][0 = neg, 1 = pos][thread] = {kk, cst}
+  uint16_t zinf[kFastMaxGpus][kTile];     // int64(tmp) when the candidate's term is 0: neg | pos << 8
   double2 lut[kLutSize];                  // {RN(1/c), (double)c}
   PodRec pods[kChunk];
   uint32_t key[kTile / 32][kChunk];
@@ -89,6 +95,7 @@ __global__ void __launch_bounds__(kTile, 4) score_fast_kernel(DevTables T, const
     lut_off[g] = 16u | (16u << 16);
     sm->kkcst[g][0][tid] = make_double2(0.0, 0.0);
     sm->kkcst[g][1][tid] = make_double2(0.0, 0.0);
+    sm->zinf[g][tid] = 0;
   }
   if (scored) {
     const float* itab = T.interf + (size_t)(model - 1) * A * A;
@@ -137,6 +144,13 @@ __global__ void __launch_bounds__(kTile, 4) score_fast_kernel(DevTables T, const
         }
         sm->kkcst[g][0][tid] = make_double2(kk_n, cst_n);
         sm->kkcst[g][1][tid] = make_double2(kk_p, cst_p);
+        {  // a candidate term of exactly 0 on either side (general ops: any sums, any counts)
+          const double tn = __dadd_rn(cst_n, __dmul_rn(100.0, __ddiv_rn(__dmul_rn(kk_n, __dadd_rn(acc.neg_sum, 0.0)),
+                                                                    (double)(cn0 + 1))));
+          const double tp = __dadd_rn(cst_p, __dmul_rn(100.0, __ddiv_rn(__dmul_rn(kk_p, __dadd_rn(acc.pos_sum, 0.0)),
+                                                                    (double)(cp0 + 1))));
+          sm->zinf[g][tid] = (uint16_t)((unsigned)score_int(tn) | ((unsigned)score_int(tp) << 8));
+        }
         base_n[g] = acc.neg_sum;
         base_p[g] = acc.pos_sum;
         cand_interf[g] = ci;
@@ -159,7 +173,7 @@ __global__ void __launch_bounds__(kTile, 4) score_fast_kernel(DevTables T, const
     const uint32_t orig = pr.orig & kPodIndexMask;
     float conf = conf_a30;
     unsigned flags = node_flags;
-    if (model == kModelV100) {
+    if (scored && model == kModelV100) {
       conf = pr.conf_v100;
       if (pr.orig & kPodF6) flags |= kFlagF6;
     }
@@ -168,8 +182,24 @@ __global__ void __launch_bounds__(kTile, 4) score_fast_kernel(DevTables T, const
     // May any lane's float32 term leave the finite range?  |t| <= |1/slo|*(|slo|+|conf|+max|ci|).
     const float t_bound = fabsf(pr.inv_slo) * (fabsf(pr.slo) + fabsf(conf) + ci_max);
     const bool lane_general = has_cand && (thr_general || !(t_bound < 1.0e38f));
-    const bool warp_general = (pr.orig & kPodSpecial) || __any_sync(0xFFFFFFFFu, lane_general);
-    if (!warp_general) {
+    if (pr.orig & kPodInfInv) {
+      // t = +-Inf * (slo - d): 1/(1+Inf) = 0 on either side, NaN when slo - d is 0 or NaN
+      int score = 0;
+      unsigned sel = kSelNone;
+#pragma unroll
+      for (int g = 0; g < kFastMaxGpus; ++g) {
+        const float d = __fsub_rn(conf, cand_interf[g]);
+        const float e = __fsub_rn(pr.slo, d);
+        const unsigned z = sm->zinf[g][tid];
+        int si = pr.slo > d ? (int)(z & 0xFFu) : (int)(z >> 8);
+        if (!(e < 0.0f || e > 0.0f)) si = 0;  // NaN term: int64(NaN) never wins
+        if (si > score) {
+          score = si;
+          sel = (unsigned)g;
+        }
+      }
+      if (has_cand) packed = (score << 8) | (int)sel;
+    } else if (!((pr.orig & kPodGeneral) || __any_sync(0xFFFFFFFFu, lane_general))) {
       int score = 0;
       unsigned sel = kSelNone;
 #pragma unroll

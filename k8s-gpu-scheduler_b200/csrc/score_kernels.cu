@@ -205,10 +205,11 @@ __global__ void pod_scatter_kernel(DevTables T, const uint32_t* __restrict__ pod
   rec.slo = slo;
   rec.inv_slo = __fdiv_rn(1.0f, slo);
   rec.conf_v100 = c;
-  // "plain" pods have a finite non-zero SLO with a finite reciprocal: the streamlined
-  // arithmetic of score_fast_kernel applies; anything else takes its general path
-  const bool plain = slo != 0.0f && fabsf(slo) <= 3.0e38f && fabsf(rec.inv_slo) <= 3.0e38f;
-  rec.orig = (uint32_t)p | (f6 ? kPodF6 : 0u) | (plain ? 0u : kPodSpecial);
+  // class of the pod for score_fast_kernel: plain (finite SLO with a finite non-zero
+  // reciprocal), infinite reciprocal (SLO missing = 0, or denormal), or general
+  const bool inf_inv = fabsf(rec.inv_slo) > 3.4e38f;                       // +-Inf; false for NaN
+  const bool plain = fabsf(slo) <= 3.4e38f && rec.inv_slo != 0.0f && !inf_inv;  // false for NaN, +-Inf
+  rec.orig = (uint32_t)p | (f6 ? kPodF6 : 0u) | (inf_inv ? kPodInfInv : (plain ? 0u : kPodGeneral));
   sorted[pos] = rec;
 }
 

@@ -31,12 +31,13 @@ struct PodRec {
   float slo;
   float inv_slo;    // float32 1/slo
   float conf_v100;  // the V100 candidate prediction of gpu_plugins.go:639-651, -1 if none
-  uint32_t orig;    // bits 0..29 original pod index, kPodF6, kPodSpecial
+  uint32_t orig;    // bits 0..28 original pod index, kPodF6, kPodGeneral, kPodInfInv
 };
 constexpr uint32_t kPodF6 = 0x80000000u;       // F6 holds on V100 nodes (some 1P/2P/4P column exists)
-constexpr uint32_t kPodSpecial = 0x40000000u;  // SLO is 0, NaN or infinite (or its reciprocal is)
-constexpr uint32_t kPodIndexMask = 0x3FFFFFFFu;
-constexpr int kMaxPods = 1 << 30;
+constexpr uint32_t kPodGeneral = 0x40000000u;  // SLO is NaN or infinite: general path
+constexpr uint32_t kPodInfInv = 0x20000000u;   // 1/SLO is infinite (SLO is 0 or denormal): every term is 0 or NaN
+constexpr uint32_t kPodIndexMask = 0x1FFFFFFFu;
+constexpr int kMaxPods = 1 << 29;
 
 // A work item of the restructured kernel: up to kChunk pods of one app.
 struct ChunkDesc {
