@@ -39,11 +39,39 @@ struct FastSmem {
   double2 kkcst[kFastMaxGpus][2][kTile];  // [g][0 = neg, 1 = pos][thread] = {kk, cst}
   uint16_t zinf[kFastMaxGpus][kTile];     // int64(tmp) when the candidate's term is 0: neg | pos << 8
   double2 lut[kLutSize];                  // {RN(1/c), (double)c}
-  PodRec pods[kChunk];
-  uint32_t key[kTile / 32][kChunk];
-  uint32_t neg[kTile / 32][kChunk];
+  PodRec pods[kStage];
+  uint32_t key[kTile / 32][kStage];
+  uint32_t neg[kTile / 32][kStage];
 };
 static_assert(sizeof(FastSmem) <= 48 * 1024, "static shared memory");
+static_assert(kStage == kTile, "a CTA stages its pods with one thread each");
+
+// m / c for a count c: the table form where its preconditions hold, IEEE division otherwise
+// (both correctly rounded, hence identical).
+__device__ __forceinline__ double div_count(double m, int c, const double2* lut) {
+  const double am = fabs(m);
+  if (c < kLutSize && (am == 0.0 || (am > 1e-250 && am < 1e300))) {
+    const double2 e = lut[c];
+    return div_small_int(m, e.x, e.y);
+  }
+  return __ddiv_rn(m, (double)c);
+}
+
+// combine() of score_math.cuh with the divisions by counts done through the table
+__device__ __forceinline__ double combine_lut(double neg_sum, double pos_sum, int cn, int cp, const double2* lut) {
+  double tmp = 0.0;
+  if (cn > 0 && cp > 0) {
+    const double k = div_count((double)cn, cn + cp, lut);
+    const double a = __dmul_rn(100.0, div_count(__dmul_rn(__dsub_rn(1.0, k), pos_sum), cp, lut));
+    const double b = __dmul_rn(100.0, div_count(__dmul_rn(k, neg_sum), cn, lut));
+    tmp = __dadd_rn(a, b);
+  } else if (cn > 0) {
+    tmp = __dmul_rn(100.0, div_count(neg_sum, cn, lut));
+  } else if (cp > 0) {
+    tmp = __dmul_rn(100.0, div_count(pos_sum, cp, lut));
+  }
+  return tmp;
+}
 
 __global__ void __launch_bounds__(kTile, 4) score_fast_kernel(DevTables T, const PodRec* __restrict__ pods,
                                                              const ChunkDesc* __restrict__ chunks,
@@ -57,8 +85,6 @@ __global__ void __launch_bounds__(kTile, 4) score_fast_kernel(DevTables T, const
   if (blockIdx.x >= *n_chunks) return;
   const int tid = threadIdx.x;
   const ChunkDesc cd = chunks[blockIdx.x];
-  const int len = (int)cd.len;
-  if (tid < len) sm->pods[tid] = pods[cd.start + tid];
   if (tid < kLutSize) sm->lut[tid] = make_double2(tid ? __ddiv_rn(1.0, (double)tid) : 0.0, (double)tid);
 
   const uint32_t tile_node0 = blockIdx.y * kTile;
@@ -76,29 +102,31 @@ __global__ void __launch_bounds__(kTile, 4) score_fast_kernel(DevTables T, const
   const bool scored = model != kModelNone && k > 0;  // the GPU loop of Logic runs at least once
   unsigned node_flags = scored ? kFlagEligible : 0u;
 
-  // register-resident per-GPU state of the streamlined loop
-  double base_n[kFastMaxGpus], base_p[kFastMaxGpus];
-  float cand_interf[kFastMaxGpus];
-  uint32_t lut_off[kFastMaxGpus];  // byte offsets of the neg (low half) / pos (high half) count in lut
   float conf_a30 = 0.0f, ci_max = 0.0f;
   int nocand = (int)kSelNone;  // score << 8 | sel for pods without a candidate term (:667-696)
   bool thr_general = false;    // this node's sums/counts fall outside the streamlined domain
 
-  // GPUs a node does not have (and lanes without a node) get constants that evaluate to
-  // tmp = 0 + 100*((0*(0+v))/1) = 0: they can never win (a GPU needs int64(tmp) >= 1), so
-  // the streamlined loop runs all kFastMaxGpus slots without a guard.
+  // Step 1+2, one GPU at a time (a rolled loop: its results go through thread-local arrays
+  // and are picked up into registers below).  GPUs a node does not have (and lanes without a
+  // node) keep constants that evaluate to tmp = 0 + 100*((0*(0+v))/1) = 0: they can never
+  // win (a GPU needs int64(tmp) >= 1), so the streamlined loop needs no guard.
+  double l_bn[kFastMaxGpus], l_bp[kFastMaxGpus];
+  float l_ci[kFastMaxGpus];
+  uint32_t l_off[kFastMaxGpus];
 #pragma unroll
   for (int g = 0; g < kFastMaxGpus; ++g) {
-    base_n[g] = 0.0;
-    base_p[g] = 0.0;
-    cand_interf[g] = 0.f;
-    lut_off[g] = 16u | (16u << 16);
+    l_bn[g] = 0.0;
+    l_bp[g] = 0.0;
+    l_ci[g] = 0.f;
+    l_off[g] = 16u | (16u << 16);
     sm->kkcst[g][0][tid] = make_double2(0.0, 0.0);
     sm->kkcst[g][1][tid] = make_double2(0.0, 0.0);
     sm->zinf[g][tid] = 0;
   }
+  __syncthreads();  // lut
   if (scored) {
     const float* itab = T.interf + (size_t)(model - 1) * A * A;
+    const double2* lut = sm->lut;
     if (model == kModelA30) {
       float v;
       bool ok = conf_lookup(T, app, model, k, &v);
@@ -107,151 +135,172 @@ __global__ void __launch_bounds__(kTile, 4) score_fast_kernel(DevTables T, const
     }
     int nc_score = 0;
     unsigned nc_sel = kSelNone;
-#pragma unroll
-    for (int g = 0; g < kFastMaxGpus; ++g) {
-      if (g < k) {
-        GpuAcc acc = {0.0, 0.0, 0, 0};
-        float ci = 0.f;
-        const uint32_t lo = T.gpu_off[(size_t)node * T.max_gpus + g];
-        const uint32_t hi = T.gpu_off[(size_t)node * T.max_gpus + g + 1];
-        for (uint32_t r = lo; r < hi; ++r) {
-          const uint32_t ar = T.res_app[r];
-          const float4 rec = T.res_rec[r];
-          if (app_known && ar < (uint32_t)T.n_apps) ci = __fadd_rn(ci, itab[(size_t)app * A + ar]);
-          if (rec.x != 0.0f) {
-            float interf = rec.w;
-            if (app_known) interf = __fadd_rn(interf, itab[(size_t)ar * A + app]);
-            add_term(acc, rec.x, rec.y, rec.z, interf);
-          }
+    const uint32_t* offp = T.gpu_off + (size_t)node * T.max_gpus;
+    uint32_t lo = offp[0];
+#pragma unroll 1
+    for (int g = 0; g < k; ++g) {
+      const uint32_t hi = offp[g + 1];
+      GpuAcc acc = {0.0, 0.0, 0, 0};
+      float ci = 0.f;
+      for (uint32_t r = lo; r < hi; ++r) {
+        const uint32_t ar = T.res_app[r];
+        const float4 rec = T.res_rec[r];
+        if (app_known && ar < (uint32_t)T.n_apps) ci = __fadd_rn(ci, itab[(size_t)app * A + ar]);
+        if (rec.x != 0.0f) {
+          float interf = rec.w;
+          if (app_known) interf = __fadd_rn(interf, itab[(size_t)ar * A + app]);
+          add_term(acc, rec.x, rec.y, rec.z, interf);
         }
-        const int cn0 = acc.cnt_neg, cp0 = acc.cnt_pos;
-        int si = score_int(combine(acc.neg_sum, acc.pos_sum, cn0, cp0));
-        if (si > nc_score) {
-          nc_score = si;
-          nc_sel = (unsigned)g;
-        }
-        // constants of the two branches (same operations, same order as combine())
-        double kk_n = 1.0, cst_n = 0.0, kk_p = 1.0, cst_p = 0.0;
-        if (cp0 > 0) {  // candidate lands on the negative side, positives exist
-          double kq = __ddiv_rn((double)(cn0 + 1), (double)(cn0 + 1 + cp0));
-          kk_n = kq;
-          cst_n = __dmul_rn(100.0, __ddiv_rn(__dmul_rn(__dsub_rn(1.0, kq), acc.pos_sum), (double)cp0));
-        }
-        if (cn0 > 0) {  // candidate lands on the positive side, negatives exist
-          double kq = __ddiv_rn((double)cn0, (double)(cn0 + cp0 + 1));
-          kk_p = __dsub_rn(1.0, kq);
-          cst_p = __dmul_rn(100.0, __ddiv_rn(__dmul_rn(kq, acc.neg_sum), (double)cn0));
-        }
-        sm->kkcst[g][0][tid] = make_double2(kk_n, cst_n);
-        sm->kkcst[g][1][tid] = make_double2(kk_p, cst_p);
-        {  // a candidate term of exactly 0 on either side (general ops: any sums, any counts)
-          const double tn = __dadd_rn(cst_n, __dmul_rn(100.0, __ddiv_rn(__dmul_rn(kk_n, __dadd_rn(acc.neg_sum, 0.0)),
-                                                                    (double)(cn0 + 1))));
-          const double tp = __dadd_rn(cst_p, __dmul_rn(100.0, __ddiv_rn(__dmul_rn(kk_p, __dadd_rn(acc.pos_sum, 0.0)),
-                                                                    (double)(cp0 + 1))));
-          sm->zinf[g][tid] = (uint16_t)((unsigned)score_int(tn) | ((unsigned)score_int(tp) << 8));
-        }
-        base_n[g] = acc.neg_sum;
-        base_p[g] = acc.pos_sum;
-        cand_interf[g] = ci;
-        lut_off[g] = (uint32_t)((cn0 + 1) * 16) | ((uint32_t)((cp0 + 1) * 16) << 16);
-        ci_max = fmaxf(ci_max, fabsf(ci));
-        // streamlined domain: finite sums and candidate interference, counts inside the table
-        const bool fin = fabs(acc.neg_sum) <= 1e300 && fabs(acc.pos_sum) <= 1e300 && fabs(cst_n) <= 1e300 &&
-                         fabs(cst_p) <= 1e300 && fabsf(ci) <= 3.0e38f;
-        if (!fin || cn0 + 1 >= kLutSize || cp0 + 1 >= kLutSize) thr_general = true;
+      }
+      lo = hi;
+      const int cn0 = acc.cnt_neg, cp0 = acc.cnt_pos;
+      const int si = score_int(combine_lut(acc.neg_sum, acc.pos_sum, cn0, cp0, lut));
+      if (si > nc_score) {
+        nc_score = si;
+        nc_sel = (unsigned)g;
+      }
+      // constants of the two branches (same operations, same order as combine())
+      double kk_n = 1.0, cst_n = 0.0, kk_p = 1.0, cst_p = 0.0;
+      if (cp0 > 0) {  // candidate lands on the negative side, positives exist
+        const double kq = div_count((double)(cn0 + 1), cn0 + 1 + cp0, lut);
+        kk_n = kq;
+        cst_n = __dmul_rn(100.0, div_count(__dmul_rn(__dsub_rn(1.0, kq), acc.pos_sum), cp0, lut));
+      }
+      if (cn0 > 0) {  // candidate lands on the positive side, negatives exist
+        const double kq = div_count((double)cn0, cn0 + cp0 + 1, lut);
+        kk_p = __dsub_rn(1.0, kq);
+        cst_p = __dmul_rn(100.0, div_count(__dmul_rn(kq, acc.neg_sum), cn0, lut));
+      }
+      sm->kkcst[g][0][tid] = make_double2(kk_n, cst_n);
+      sm->kkcst[g][1][tid] = make_double2(kk_p, cst_p);
+      {  // a candidate term of exactly 0 on either side
+        const double tn = __dadd_rn(cst_n, __dmul_rn(100.0, div_count(__dmul_rn(kk_n, __dadd_rn(acc.neg_sum, 0.0)),
+                                                                     cn0 + 1, lut)));
+        const double tp = __dadd_rn(cst_p, __dmul_rn(100.0, div_count(__dmul_rn(kk_p, __dadd_rn(acc.pos_sum, 0.0)),
+                                                                     cp0 + 1, lut)));
+        sm->zinf[g][tid] = (uint16_t)((unsigned)score_int(tn) | ((unsigned)score_int(tp) << 8));
+      }
+      l_bn[g] = acc.neg_sum;
+      l_bp[g] = acc.pos_sum;
+      l_ci[g] = ci;
+      l_off[g] = (uint32_t)((cn0 + 1) * 16) | ((uint32_t)((cp0 + 1) * 16) << 16);
+      ci_max = fmaxf(ci_max, fabsf(ci));
+      // streamlined domain: finite sums and candidate interference, counts inside the table
+      const bool fin = fabs(acc.neg_sum) <= 1e300 && fabs(acc.pos_sum) <= 1e300 && fabs(cst_n) <= 1e300 &&
+                       fabs(cst_p) <= 1e300 && fabsf(ci) <= 3.0e38f;
+      if (!fin || cn0 + 1 >= kLutSize || cp0 + 1 >= kLutSize) {
+        thr_general = true;
+        l_off[g] = 16u | (16u << 16);  // keep the table reads in range; the result is discarded
       }
     }
     nocand = (nc_score << 8) | (int)nc_sel;
   }
-  __syncthreads();
+  // register-resident per-GPU state of the streamlined loop
+  double base_n[kFastMaxGpus], base_p[kFastMaxGpus];
+  float cand_interf[kFastMaxGpus];
+  uint32_t lut_off[kFastMaxGpus];  // byte offsets of the neg (low half) / pos (high half) count in lut
+#pragma unroll
+  for (int g = 0; g < kFastMaxGpus; ++g) {
+    base_n[g] = l_bn[g];
+    base_p[g] = l_bp[g];
+    cand_interf[g] = l_ci[g];
+    lut_off[g] = l_off[g];
+  }
 
   const int warp = tid >> 5;
   const unsigned char* lut_bytes = reinterpret_cast<const unsigned char*>(sm->lut);
-  for (int i = 0; i < len; ++i) {
-    const PodRec pr = sm->pods[i];
-    const uint32_t orig = pr.orig & kPodIndexMask;
-    float conf = conf_a30;
-    unsigned flags = node_flags;
-    if (scored && model == kModelV100) {
-      conf = pr.conf_v100;
-      if (pr.orig & kPodF6) flags |= kFlagF6;
-    }
-    const bool has_cand = scored && conf != -1.0f;
-    int packed = nocand;  // also right for !scored lanes: score 0, nothing selected
-    // May any lane's float32 term leave the finite range?  |t| <= |1/slo|*(|slo|+|conf|+max|ci|).
-    const float t_bound = fabsf(pr.inv_slo) * (fabsf(pr.slo) + fabsf(conf) + ci_max);
-    const bool lane_general = has_cand && (thr_general || !(t_bound < 1.0e38f));
-    if (pr.orig & kPodInfInv) {
-      // t = +-Inf * (slo - d): 1/(1+Inf) = 0 on either side, NaN when slo - d is 0 or NaN
-      int score = 0;
-      unsigned sel = kSelNone;
+  for (uint32_t stage0 = 0; stage0 < cd.len; stage0 += kStage) {
+    const int len = (int)min((uint32_t)kStage, cd.len - stage0);
+    __syncthreads();  // previous stage fully consumed (and, first time, step 2's shared writes)
+    if (tid < len) sm->pods[tid] = pods[cd.start + stage0 + tid];
+    __syncthreads();
+    for (int i = 0; i < len; ++i) {
+      const PodRec pr = sm->pods[i];
+      const uint32_t orig = pr.orig & kPodIndexMask;
+      float conf = conf_a30;
+      unsigned flags = node_flags;
+      if (scored && model == kModelV100) {
+        conf = pr.conf_v100;
+        if (pr.orig & kPodF6) flags |= kFlagF6;
+      }
+      const bool has_cand = scored && conf != -1.0f;
+      int packed = nocand;  // also right for !scored lanes: score 0, nothing selected
+      if (pr.orig & kPodInfInv) {
+        // t = +-Inf * (slo - d): 1/(1+Inf) = 0 on either side, NaN when slo - d is 0 or NaN
+        int score = 0;
+        unsigned sel = kSelNone;
 #pragma unroll
-      for (int g = 0; g < kFastMaxGpus; ++g) {
-        const float d = __fsub_rn(conf, cand_interf[g]);
-        const float e = __fsub_rn(pr.slo, d);
-        const unsigned z = sm->zinf[g][tid];
-        int si = pr.slo > d ? (int)(z & 0xFFu) : (int)(z >> 8);
-        if (!(e < 0.0f || e > 0.0f)) si = 0;  // NaN term: int64(NaN) never wins
-        if (si > score) {
-          score = si;
-          sel = (unsigned)g;
+        for (int g = 0; g < kFastMaxGpus; ++g) {
+          const float d = __fsub_rn(conf, cand_interf[g]);
+          const float e = __fsub_rn(pr.slo, d);
+          const unsigned z = sm->zinf[g][tid];
+          int si = pr.slo > d ? (int)(z & 0xFFu) : (int)(z >> 8);
+          if (!(e < 0.0f || e > 0.0f)) si = 0;  // NaN term: int64(NaN) never wins
+          if (si > score) {
+            score = si;
+            sel = (unsigned)g;
+          }
+        }
+        if (has_cand) packed = (score << 8) | (int)sel;
+      } else {
+        // May any lane's float32 term leave the finite range?  |t| <= |1/slo|*(|slo|+|conf|+max|ci|).
+        const float t_bound = fabsf(pr.inv_slo) * (fabsf(pr.slo) + fabsf(conf) + ci_max);
+        const bool lane_general = has_cand && (thr_general || !(t_bound < 1.0e38f));
+        if (!((pr.orig & kPodGeneral) || __any_sync(0xFFFFFFFFu, lane_general))) {
+          int score = 0;
+          unsigned sel = kSelNone;
+#pragma unroll
+          for (int g = 0; g < kFastMaxGpus; ++g) {
+            bool neg;
+            const float t = term_t(pr.slo, pr.inv_slo, conf, cand_interf[g], &neg);
+            double w = fabs((double)t);
+            if (neg) w = __dadd_rn(w, 1.0);
+            if (neg) w = __dmul_rn(w, w);
+            const double v = rcp_ge1(__dadd_rn(1.0, w));
+            const double2 kc = sm->kkcst[g][neg ? 0 : 1][tid];
+            const uint32_t off = neg ? (lut_off[g] & 0xFFFFu) : (lut_off[g] >> 16);
+            const double2 rc = *reinterpret_cast<const double2*>(lut_bytes + off);
+            const double S = __dadd_rn(neg ? base_n[g] : base_p[g], v);
+            const double q = div_small_int(__dmul_rn(kc.x, S), rc.x, rc.y);
+            const int si = floor_nonneg(__dadd_rn(kc.y, __dmul_rn(100.0, q)));
+            if (si > score) {
+              score = si;
+              sel = (unsigned)g;
+            }
+          }
+          if (has_cand) packed = (score << 8) | (int)sel;
+        } else if (has_cand) {
+          unsigned selbyte;
+          const int sc = logic_eval(T, app, pr.slo, -1, node, &selbyte);
+          packed = (sc << 8) | (int)(selbyte & 31u);
         }
       }
-      if (has_cand) packed = (score << 8) | (int)sel;
-    } else if (!((pr.orig & kPodGeneral) || __any_sync(0xFFFFFFFFu, lane_general))) {
-      int score = 0;
-      unsigned sel = kSelNone;
-#pragma unroll
-      for (int g = 0; g < kFastMaxGpus; ++g) {
-        bool neg;
-        const float t = term_t(pr.slo, pr.inv_slo, conf, cand_interf[g], &neg);
-        double w = fabs((double)t);
-        if (neg) w = __dadd_rn(w, 1.0);
-        if (neg) w = __dmul_rn(w, w);
-        const double v = rcp_ge1(__dadd_rn(1.0, w));
-        const double2 kc = sm->kkcst[g][neg ? 0 : 1][tid];
-        const uint32_t off = neg ? (lut_off[g] & 0xFFFFu) : (lut_off[g] >> 16);
-        const double2 rc = *reinterpret_cast<const double2*>(lut_bytes + off);
-        const double S = __dadd_rn(neg ? base_n[g] : base_p[g], v);
-        const double q = div_small_int(__dmul_rn(kc.x, S), rc.x, rc.y);
-        const int si = floor_nonneg(__dadd_rn(kc.y, __dmul_rn(100.0, q)));
-        if (si > score) {
-          score = si;
-          sel = (unsigned)g;
-        }
+      if (has_cand) flags |= kFlagF7;
+      const int score = packed >> 8;
+      if (in_range) {
+        const size_t o = (size_t)orig * T.n_nodes + node;
+        out_score[o] = (uint8_t)score;
+        out_sel[o] = (uint8_t)((unsigned)(packed & 0xFF) | flags);
       }
-      if (has_cand) packed = (score << 8) | (int)sel;
-    } else if (has_cand) {
-      unsigned selbyte;
-      const int sc = logic_eval(T, app, pr.slo, -1, node, &selbyte);
-      packed = (sc << 8) | (int)(selbyte & 31u);
+      uint32_t key = in_range ? lane_key(score, tid) : 0u;
+      uint32_t ngm = in_range ? (uint32_t)(100 - score) : 0u;
+      key = __reduce_max_sync(0xFFFFFFFFu, key);
+      ngm = __reduce_max_sync(0xFFFFFFFFu, ngm);
+      if ((tid & 31) == 0) {
+        sm->key[warp][i] = key;
+        sm->neg[warp][i] = ngm;
+      }
     }
-    if (has_cand) flags |= kFlagF7;
-    const int score = packed >> 8;
-    if (in_range) {
-      const size_t o = (size_t)orig * T.n_nodes + node;
-      out_score[o] = (uint8_t)score;
-      out_sel[o] = (uint8_t)((unsigned)(packed & 0xFF) | flags);
-    }
-    uint32_t key = in_range ? lane_key(score, tid) : 0u;
-    uint32_t ngm = in_range ? (uint32_t)(100 - score) : 0u;
-    key = __reduce_max_sync(0xFFFFFFFFu, key);
-    ngm = __reduce_max_sync(0xFFFFFFFFu, ngm);
-    if ((tid & 31) == 0) {
-      sm->key[warp][i] = key;
-      sm->neg[warp][i] = ngm;
-    }
-  }
-  __syncthreads();
-  if (tid < len) {
-    uint32_t key = sm->key[0][tid], ngm = sm->neg[0][tid];
+    __syncthreads();
+    if (tid < len) {
+      uint32_t key = sm->key[0][tid], ngm = sm->neg[0][tid];
 #pragma unroll
-    for (int w = 1; w < kTile / 32; ++w) {
-      key = max(key, sm->key[w][tid]);
-      ngm = max(ngm, sm->neg[w][tid]);
+      for (int w = 1; w < kTile / 32; ++w) {
+        key = max(key, sm->key[w][tid]);
+        ngm = max(ngm, sm->neg[w][tid]);
+      }
+      publish_extrema(key, ngm, tile_node0, T.node_base, sm->pods[tid].orig & kPodIndexMask, hi_arg, neg_lo);
     }
-    publish_extrema(key, ngm, tile_node0, T.node_base, sm->pods[tid].orig & kPodIndexMask, hi_arg, neg_lo);
   }
 }
 
@@ -259,7 +308,6 @@ cudaError_t launch_score_fast(const DevTables& T, const uint32_t* pod_app, const
                               const PodScratch& sc, uint8_t* score, uint8_t* sel, unsigned long long* hi_arg,
                               unsigned long long* neg_lo, cudaStream_t s, cudaEvent_t before_main) {
   if (n_pods == 0 || T.n_nodes == 0) return cudaSuccess;
-  static_assert(kChunk <= kTile, "a CTA loads its pods with one thread each");
   cudaError_t e = launch_pod_bucketing(T, pod_app, pod_slo, n_pods, sc, s);
   if (e != cudaSuccess) return e;
   if (before_main && (e = cudaEventRecord(before_main, s)) != cudaSuccess) return e;

@@ -47,7 +47,8 @@ struct ChunkDesc {
   uint32_t pad;
 };
 
-constexpr int kChunk = 128;      // pods per work item
+constexpr int kChunk = 256;      // pods per work item (one app); staged kStage at a time
+constexpr int kStage = 128;      // pods staged in shared memory at once (= kTile)
 constexpr int kFastMaxGpus = 8;  // GPUs per node the register-resident kernel covers
 constexpr int kTile = 128;       // nodes per CTA
 
