@@ -2,6 +2,7 @@
 // points.  Host logic only; kernels live in score_kernels.cu.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -73,6 +74,7 @@ DevTables Ctx::tables() const {
   T.res_slo = (const float*)res_slo.p;
   T.conf = (const float*)conf.p;
   T.interf = (const float*)interf.p;
+  T.interf_t = (const float*)interf_t.p;
   T.col_of = (const int32_t*)col_of.p;
   T.res_rec = (const float4*)res_rec.p;
   return T;
@@ -103,6 +105,11 @@ int Ctx::ensure_scratch(int n_pods) {
   if ((rc = reserve(sc_nchunks, 256, "chunk counter"))) return rc;
   if ((rc = reserve(sc_chunks, sizeof(ChunkDesc) * (size_t)mc, "chunk descriptors"))) return rc;
   if ((rc = reserve(sc_sorted, sizeof(PodRec) * (size_t)(n_pods ? n_pods : 1), "sorted pods"))) return rc;
+  // residents-sum table: 24 bytes per (app bucket, GPU slot), if it fits the budget
+  const size_t entries = (size_t)(n_apps + 1) * (size_t)n_nodes * (size_t)max_gpus;
+  if (entries * 24 <= stage_budget) {
+    if ((rc = reserve(sc_stage, entries * 24 + 1024, "residents-sum table"))) return rc;
+  }
   return GS_OK;
 }
 
@@ -136,6 +143,7 @@ int gs_create(int device, gs_ctx** out) {
   gs_ctx* c = new (std::nothrow) gs_ctx();
   if (!c) return GS_ERR_NOMEM;
   c->device = device;
+  if (const char* mb = getenv("GS_STAGE_TABLE_MB")) c->stage_budget = (size_t)strtoull(mb, nullptr, 10) << 20;
   if (cudaSetDevice(device) != cudaSuccess ||
       cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
     cudaGetLastError();
@@ -153,7 +161,7 @@ void gs_destroy(gs_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     gs::DevBuf* bufs[] = {&c->node_model, &c->node_ngpu, &c->gpu_off,   &c->res_app,   &c->res_slo, &c->conf,
-                          &c->interf,     &c->col_of,    &c->res_rec,   &c->sc_counts, &c->sc_cursor,
+                          &c->interf,     &c->interf_t,  &c->sc_stage,  &c->col_of,    &c->res_rec,   &c->sc_counts, &c->sc_cursor,
                           &c->sc_nchunks, &c->sc_chunks, &c->sc_sorted, &c->b_pod_app, &c->b_pod_slo,
                           &c->b_pod_self, &c->b_score,   &c->b_sel,     &c->b_extrema, &c->b_best,  &c->b_misc};
     for (gs::DevBuf* b : bufs) c->release(*b);
@@ -226,6 +234,11 @@ int gs_upload_predictions(gs_ctx* c, const gs_predictions* pr) {
   if ((rc = c->upload(c->conf, pr->conf, sizeof(float) * A * K, "conf"))) return rc;
   if ((rc = c->upload(c->interf, pr->interf, sizeof(float) * 2 * A * A, "interf"))) return rc;
   if ((rc = c->upload(c->col_of, pr->col_of, sizeof(int32_t) * 2 * (GS_MAX_GPUS_PER_NODE + 1), "col_of"))) return rc;
+  if ((rc = c->reserve(c->interf_t, sizeof(float) * 2 * A * A + 16, "interf_t"))) return rc;
+  if (A) {
+    cudaError_t e = gs::launch_transpose_interf((const float*)c->interf.p, (float*)c->interf_t.p, pr->n_apps, c->stream);
+    if (e != cudaSuccess) return c->cuda_fail(e, "transpose_interf");
+  }
   GS_CUDA(c, cudaStreamSynchronize(c->stream));
   c->n_apps = pr->n_apps;
   c->n_cols = pr->n_cols;
@@ -261,6 +274,21 @@ static int score_raw_locked(gs_ctx* c, const uint32_t* d_app, const float* d_slo
     sc.chunks = (gs::ChunkDesc*)c->sc_chunks.p;
     sc.sorted = (gs::PodRec*)c->sc_sorted.p;
     sc.max_chunks = gs::max_chunks_for(P, c->n_apps);
+    sc.stage = gs::StageA{nullptr, nullptr, nullptr, nullptr, 0};
+    {
+      const size_t entries = (size_t)(c->n_apps + 1) * (size_t)c->n_nodes * (size_t)c->max_gpus;
+      if (entries * 24 <= c->stage_budget && c->sc_stage.cap >= entries * 24) {
+        const size_t e8 = (entries + 31) / 32 * 32;  // keep every array 256-byte aligned
+        char* base = (char*)c->sc_stage.p;
+        if (e8 * 24 <= c->sc_stage.cap) {
+          sc.stage.n0 = (double*)base;
+          sc.stage.p0 = (double*)(base + e8 * 8);
+          sc.stage.ci = (float*)(base + e8 * 16);
+          sc.stage.cnt = (uint32_t*)(base + e8 * 20);
+          sc.stage.stride = (size_t)c->n_nodes * (size_t)c->max_gpus;
+        }
+      }
+    }
     e = gs::launch_score_fast(T, d_app, d_slo, P, sc, d_score, d_sel, (unsigned long long*)d_hi,
                               (unsigned long long*)d_neg, s, c->profiling ? c->ev_begin : nullptr);
   } else {

@@ -27,12 +27,13 @@ struct Ctx {
   // prediction tables
   bool have_preds = false;
   int n_apps = 0, n_cols = 0;
-  DevBuf conf, interf, col_of;
+  DevBuf conf, interf, interf_t, col_of;
   // derived
   bool prep_dirty = true;
   DevBuf res_rec;
   // scratch of the restructured scoring path
-  DevBuf sc_counts, sc_cursor, sc_nchunks, sc_chunks, sc_sorted;
+  DevBuf sc_counts, sc_cursor, sc_nchunks, sc_chunks, sc_sorted, sc_stage;
+  size_t stage_budget = (size_t)4 << 30;  // largest per-batch residents-sum table (GS_STAGE_TABLE_MB)
   // staging for the host-pointer entry points
   DevBuf b_pod_app, b_pod_slo, b_pod_self, b_score, b_sel, b_extrema, b_best, b_misc;
 

@@ -73,7 +73,95 @@ __device__ __forceinline__ double combine_lut(double neg_sum, double pos_sum, in
   return tmp;
 }
 
-__global__ void __launch_bounds__(kTile, 4) score_fast_kernel(DevTables T, const PodRec* __restrict__ pods,
+// ------------------------------------------------------------------ stage A ----------
+
+// The residents' sums of every (app bucket, GPU slot) that has pods in this batch.  A warp
+// takes one GPU slot with its 32 lanes on 32 consecutive apps: the slot's resident list is
+// the same for all lanes (uniform trip count, broadcast loads) and both interference reads
+// are contiguous in the app (row r of interf, row r of its transpose).  Results go through a
+// padded shared tile so that the table is written, and later read, slot-contiguous.
+constexpr int kStageTile = 32;
+
+__global__ void __launch_bounds__(256) stage_a_kernel(DevTables T, const uint32_t* __restrict__ counts, StageA out) {
+  __shared__ double s_n0[kStageTile][kStageTile + 1], s_p0[kStageTile][kStageTile + 1];
+  __shared__ float s_ci[kStageTile][kStageTile + 1];
+  __shared__ uint32_t s_cnt[kStageTile][kStageTile + 1];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int slots = T.n_nodes * T.max_gpus;
+  const int s0 = blockIdx.x * kStageTile, a0 = blockIdx.y * kStageTile;
+  const int app_idx = a0 + lane;  // bucket n_apps = pods whose app is unknown
+  const bool app_known = app_idx < T.n_apps;
+  const bool wanted = app_idx <= T.n_apps && counts[app_idx] > 0;
+  if (!__syncthreads_or(wanted)) return;  // no pod of these 32 apps in the batch
+  const size_t A = (size_t)T.n_apps;
+  for (int j = 0; j < kStageTile / 8; ++j) {
+    const int sl = warp * (kStageTile / 8) + j;
+    const int slot = s0 + sl;
+    GpuAcc acc = {0.0, 0.0, 0, 0};
+    float ci = 0.f;
+    if (slot < slots && T.redis_reachable) {
+      const int node = slot / T.max_gpus, g = slot - node * T.max_gpus;
+      const int model = T.node_model[node];
+      if (model != kModelNone && g < (int)T.node_ngpu[node]) {
+        const float* itab = T.interf + (size_t)(model - 1) * A * A;
+        const float* itab_t = T.interf_t + (size_t)(model - 1) * A * A;
+        const uint32_t lo = T.gpu_off[slot], hi = T.gpu_off[slot + 1];
+        for (uint32_t r = lo; r < hi; ++r) {
+          const uint32_t ar = T.res_app[r];
+          const float4 rec = T.res_rec[r];
+          if (app_known && ar < (uint32_t)T.n_apps) ci = __fadd_rn(ci, itab_t[(size_t)ar * A + app_idx]);
+          if (rec.x != 0.0f) {
+            float interf = rec.w;
+            if (app_known) interf = __fadd_rn(interf, itab[(size_t)ar * A + app_idx]);
+            add_term(acc, rec.x, rec.y, rec.z, interf);
+          }
+        }
+      }
+    }
+    s_n0[lane][sl] = acc.neg_sum;
+    s_p0[lane][sl] = acc.pos_sum;
+    s_ci[lane][sl] = ci;
+    s_cnt[lane][sl] = (uint32_t)acc.cnt_neg | ((uint32_t)acc.cnt_pos << 16);
+  }
+  __syncthreads();
+#pragma unroll
+  for (int pass = 0; pass < kStageTile / 8; ++pass) {
+    const int al = pass * 8 + warp;
+    if (a0 + al <= T.n_apps && s0 + lane < slots) {
+      const size_t o = (size_t)(a0 + al) * out.stride + (size_t)(s0 + lane);
+      out.n0[o] = s_n0[al][lane];
+      out.p0[o] = s_p0[al][lane];
+      out.ci[o] = s_ci[al][lane];
+      out.cnt[o] = s_cnt[al][lane];
+    }
+  }
+}
+
+// interf_t[m][b][a] = interf[m][a][b]
+__global__ void __launch_bounds__(256) transpose_interf_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                              int n) {
+  __shared__ float tile[32][33];
+  const size_t plane = (size_t)blockIdx.z * n * n;
+  int x = blockIdx.x * 32 + (threadIdx.x & 31), y0 = blockIdx.y * 32 + (threadIdx.x >> 5);
+  for (int j = 0; j < 32; j += 8)
+    if (x < n && y0 + j < n) tile[(threadIdx.x >> 5) + j][threadIdx.x & 31] = in[plane + (size_t)(y0 + j) * n + x];
+  __syncthreads();
+  x = blockIdx.y * 32 + (threadIdx.x & 31);
+  y0 = blockIdx.x * 32 + (threadIdx.x >> 5);
+  for (int j = 0; j < 32; j += 8)
+    if (x < n && y0 + j < n) out[plane + (size_t)(y0 + j) * n + x] = tile[threadIdx.x & 31][(threadIdx.x >> 5) + j];
+}
+
+cudaError_t launch_transpose_interf(const float* interf, float* interf_t, int n_apps, cudaStream_t s) {
+  dim3 grid((n_apps + 31) / 32, (n_apps + 31) / 32, 2);
+  transpose_interf_kernel<<<grid, 256, 0, s>>>(interf, interf_t, n_apps);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ main kernel ------
+
+template <bool kTable>
+__global__ void __launch_bounds__(kTile, 4) score_fast_kernel(DevTables T, StageA stage, const PodRec* __restrict__ pods,
                                                              const ChunkDesc* __restrict__ chunks,
                                                              const uint32_t* __restrict__ n_chunks,
                                                              uint8_t* __restrict__ out_score,
@@ -136,23 +224,33 @@ __global__ void __launch_bounds__(kTile, 4) score_fast_kernel(DevTables T, const
     int nc_score = 0;
     unsigned nc_sel = kSelNone;
     const uint32_t* offp = T.gpu_off + (size_t)node * T.max_gpus;
-    uint32_t lo = offp[0];
+    uint32_t lo = kTable ? 0u : offp[0];
+    const size_t st_row = (size_t)(app_known ? app : (uint32_t)T.n_apps) * stage.stride + (size_t)node * T.max_gpus;
 #pragma unroll 1
     for (int g = 0; g < k; ++g) {
-      const uint32_t hi = offp[g + 1];
       GpuAcc acc = {0.0, 0.0, 0, 0};
       float ci = 0.f;
-      for (uint32_t r = lo; r < hi; ++r) {
-        const uint32_t ar = T.res_app[r];
-        const float4 rec = T.res_rec[r];
-        if (app_known && ar < (uint32_t)T.n_apps) ci = __fadd_rn(ci, itab[(size_t)app * A + ar]);
-        if (rec.x != 0.0f) {
-          float interf = rec.w;
-          if (app_known) interf = __fadd_rn(interf, itab[(size_t)ar * A + app]);
-          add_term(acc, rec.x, rec.y, rec.z, interf);
+      if (kTable) {  // written by stage_a_kernel, slot-contiguous: coalesced across the tile
+        acc.neg_sum = stage.n0[st_row + g];
+        acc.pos_sum = stage.p0[st_row + g];
+        ci = stage.ci[st_row + g];
+        const uint32_t c = stage.cnt[st_row + g];
+        acc.cnt_neg = (int)(c & 0xFFFFu);
+        acc.cnt_pos = (int)(c >> 16);
+      } else {
+        const uint32_t hi = offp[g + 1];
+        for (uint32_t r = lo; r < hi; ++r) {
+          const uint32_t ar = T.res_app[r];
+          const float4 rec = T.res_rec[r];
+          if (app_known && ar < (uint32_t)T.n_apps) ci = __fadd_rn(ci, itab[(size_t)app * A + ar]);
+          if (rec.x != 0.0f) {
+            float interf = rec.w;
+            if (app_known) interf = __fadd_rn(interf, itab[(size_t)ar * A + app]);
+            add_term(acc, rec.x, rec.y, rec.z, interf);
+          }
         }
+        lo = hi;
       }
-      lo = hi;
       const int cn0 = acc.cnt_neg, cp0 = acc.cnt_pos;
       const int si = score_int(combine_lut(acc.neg_sum, acc.pos_sum, cn0, cp0, lut));
       if (si > nc_score) {
@@ -312,8 +410,16 @@ cudaError_t launch_score_fast(const DevTables& T, const uint32_t* pod_app, const
   if (e != cudaSuccess) return e;
   if (before_main && (e = cudaEventRecord(before_main, s)) != cudaSuccess) return e;
   dim3 grid(sc.max_chunks, (unsigned)((T.n_nodes + kTile - 1) / kTile));
-  score_fast_kernel<<<grid, kTile, 0, s>>>(T, sc.sorted, sc.chunks, sc.n_chunks, score, sel, hi_arg,
-                                                          neg_lo);
+  if (sc.stage.n0) {
+    const int slots = T.n_nodes * T.max_gpus;
+    dim3 ga((unsigned)((slots + kStageTile - 1) / kStageTile), (unsigned)((T.n_apps + 1 + kStageTile - 1) / kStageTile));
+    stage_a_kernel<<<ga, 256, 0, s>>>(T, sc.counts, sc.stage);
+    score_fast_kernel<true><<<grid, kTile, 0, s>>>(T, sc.stage, sc.sorted, sc.chunks, sc.n_chunks, score, sel, hi_arg,
+                                                   neg_lo);
+  } else {
+    score_fast_kernel<false><<<grid, kTile, 0, s>>>(T, sc.stage, sc.sorted, sc.chunks, sc.n_chunks, score, sel,
+                                                    hi_arg, neg_lo);
+  }
   return cudaGetLastError();
 }
 

@@ -20,6 +20,7 @@ struct DevTables {
   const float* res_slo;       // [R]
   const float* conf;          // [A*K]
   const float* interf;        // [2*A*A]
+  const float* interf_t;      // [2*A*A] per-model transpose: interf_t[m][b][a] = interf[m][a][b]
   const int32_t* col_of;      // [2*32]
   // derived per resident by resident_prep: {slo (0 = never contributes), 1/slo, conf, S}
   // S = float32 sum, in resident order, of interf[row(r)][app(c)] over co-residents c != r
@@ -52,7 +53,17 @@ constexpr int kStage = 128;      // pods staged in shared memory at once (= kTil
 constexpr int kFastMaxGpus = 8;  // GPUs per node the register-resident kernel covers
 constexpr int kTile = 128;       // nodes per CTA
 
-// Scratch of the restructured path (owned by the context, or the static no-alloc arena).
+// Per-batch table of the residents' sums for every (app bucket, GPU slot), written by
+// stage_a_kernel and read back coalesced by score_fast_kernel: [n_apps + 1][slots].
+struct StageA {
+  double* n0;     // negative_sum of the slot's residents given the candidate's app
+  double* p0;     // positive_sum
+  float* ci;      // the candidate's interference sum on that GPU
+  uint32_t* cnt;  // count_negative | count_positive << 16
+  size_t stride;  // slots = n_nodes * max_gpus
+};
+
+// Scratch of the restructured path (owned by the context).
 struct PodScratch {
   uint32_t* counts;   // [A+2] pods per app bucket (bucket A = unknown app)
   uint32_t* cursor;   // [A+2] scatter cursors
@@ -60,6 +71,7 @@ struct PodScratch {
   ChunkDesc* chunks;  // [max_chunks]
   PodRec* sorted;     // [P]
   uint32_t max_chunks;
+  StageA stage;       // n0 == nullptr: score_fast_kernel walks the resident lists itself
 };
 
 inline uint32_t max_chunks_for(int n_pods, int n_apps) {
@@ -76,6 +88,7 @@ cudaError_t launch_score_fast(const DevTables& T, const uint32_t* pod_app, const
                               const PodScratch& scratch, uint8_t* score, uint8_t* sel,
                               unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s,
                               cudaEvent_t before_main = nullptr);
+cudaError_t launch_transpose_interf(const float* interf, float* interf_t, int n_apps, cudaStream_t s);
 cudaError_t launch_selftest(unsigned long long seed, int blocks, int iters, unsigned long long* d_mismatches,
                             cudaStream_t s);
 cudaError_t launch_normalize(int n_pods, int n_nodes, int rescale, uint8_t* score,

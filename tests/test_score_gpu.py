@@ -212,3 +212,18 @@ def test_many_residents_per_gpu(sched, oracle_mod, synth):
     cluster.res_slo = np.round(rng.uniform(10, 600, size=R), 2).astype(np.float32)
     preds.col_of[:, 2] = preds.col_of[:, 8]  # give the tables a 2P column
     _check(sched, oracle_mod, preds, cluster, pods)
+
+
+def test_without_residents_sum_table(pkg, oracle_mod, synth, monkeypatch):
+    """GS_STAGE_TABLE_MB=0 disables the per-batch residents-sum table: the scoring kernel then walks
+    the resident lists itself.  Same bytes."""
+    monkeypatch.setenv("GS_STAGE_TABLE_MB", "0")
+    s = pkg.Scheduler(0)
+    try:
+        for kw in (dict(n_pods=1000, n_nodes=100, gpus_per_node=8),
+                   dict(n_pods=300, n_nodes=333, gpus_per_node=8, n_apps=97, ragged_gpus=True, p_unknown_app=0.07),
+                   dict(n_pods=200, n_nodes=150, gpus_per_node=4, n_apps=31, with_8p=False)):
+            preds, cluster, pods = synth.make_workload(**kw)
+            _check(s, oracle_mod, preds, cluster, pods)
+    finally:
+        s.close()
