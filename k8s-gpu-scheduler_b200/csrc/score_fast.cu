@@ -345,8 +345,11 @@ __global__ void __launch_bounds__(kTile, 4) score_fast_kernel(DevTables T, Stage
         const float t_bound = fabsf(pr.inv_slo) * (fabsf(pr.slo) + fabsf(conf) + ci_max);
         const bool lane_general = has_cand && (thr_general || !(t_bound < 1.0e38f));
         if (!((pr.orig & kPodGeneral) || __any_sync(0xFFFFFFFFu, lane_general))) {
-          int score = 0;
-          unsigned sel = kSelNone;
+          // running maximum of key = int64(tmp) * 8 + (7 - g): the highest score wins, the
+          // first GPU among equals (the reference's strict `>` in visiting order)
+          int best = 0;
+          const double2* kk_neg = &sm->kkcst[0][0][tid];
+          const double2* kk_pos = &sm->kkcst[0][1][tid];
 #pragma unroll
           for (int g = 0; g < kFastMaxGpus; ++g) {
             bool neg;
@@ -355,17 +358,16 @@ __global__ void __launch_bounds__(kTile, 4) score_fast_kernel(DevTables T, Stage
             if (neg) w = __dadd_rn(w, 1.0);
             if (neg) w = __dmul_rn(w, w);
             const double v = rcp_ge1(__dadd_rn(1.0, w));
-            const double2 kc = sm->kkcst[g][neg ? 0 : 1][tid];
+            const double2 kc = (neg ? kk_neg : kk_pos)[g * 2 * kTile];
             const uint32_t off = neg ? (lut_off[g] & 0xFFFFu) : (lut_off[g] >> 16);
             const double2 rc = *reinterpret_cast<const double2*>(lut_bytes + off);
             const double S = __dadd_rn(neg ? base_n[g] : base_p[g], v);
             const double q = div_small_int(__dmul_rn(kc.x, S), rc.x, rc.y);
             const int si = floor_nonneg(__dadd_rn(kc.y, __dmul_rn(100.0, q)));
-            if (si > score) {
-              score = si;
-              sel = (unsigned)g;
-            }
+            best = max(best, si * 8 + (kFastMaxGpus - 1 - g));
           }
+          const int score = best >> 3;
+          const unsigned sel = score > 0 ? (unsigned)(kFastMaxGpus - 1 - (best & 7)) : kSelNone;
           if (has_cand) packed = (score << 8) | (int)sel;
         } else if (has_cand) {
           unsigned selbyte;
