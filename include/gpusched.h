@@ -189,6 +189,41 @@ GS_API int gs_normalize_dev(gs_ctx* ctx, int32_t n_pods, uint8_t* d_score,
                      const uint64_t* d_hi_arg, const uint64_t* d_neg_lo, int32_t* d_best,
                      void* stream);
 
+/* gs_score_raw_dev for callers that must not allocate.  (No counterpart in the reference.)
+ *
+ * The regular scoring entry points grow context-owned device buffers with cudaMalloc when a
+ * batch needs more working memory than the last one did.  Some callers cannot have that on
+ * their scoring path: a scheduler that has handed all device memory to its own pools at
+ * start-up, a latency-critical cycle that must never block on the driver's allocator
+ * (cudaMalloc and cudaFree synchronise the device and serialise against every other
+ * allocating thread), or a harness that forbids allocation after initialisation.  This
+ * variant computes exactly what gs_score_raw_dev computes (same arguments, minus the self
+ * table and flags; same bytes out) but takes ALL of its working memory from one fixed array
+ * inside the library's device image, and calls neither cudaMalloc/cudaFree nor any
+ * allocating library routine.
+ *
+ *   Limits    n_pods <= GS_NOALLOC_MAX_PODS, uploaded apps <= GS_NOALLOC_MAX_APPS, uploaded
+ *             residents <= GS_NOALLOC_MAX_RESIDENTS, max_gpus <= 8; anything larger is
+ *             refused with GS_ERR_INVALID (gs_last_error names the limit) — split the batch
+ *             or use gs_score_raw_dev.  The tables themselves are uploaded (and allocated)
+ *             beforehand with gs_upload_*, outside the no-allocation phase.
+ *   Cost      the array (about 3.2 MB) is part of the library image: every GPU that loads
+ *             libgpusched.so holds it until the process exits.
+ *   Sharing   all calls on a GPU use the same array, which keeps the previous call's
+ *             contents; each call clears what must start at zero (and zeroes d_hi_arg /
+ *             d_neg_lo, like gs_score_raw_dev).  Calls issued one after another on one stream
+ *             are safe.  Calls whose GPU work overlaps — different streams, or different
+ *             contexts on the same GPU — race on the array: serialise them yourself.
+ *   First use the first call on each device resolves the array's device address
+ *             (cudaGetSymbolAddress, once per device); make that first call before any
+ *             stream capture starts. */
+#define GS_NOALLOC_MAX_PODS 65536
+#define GS_NOALLOC_MAX_APPS 4096
+#define GS_NOALLOC_MAX_RESIDENTS 131072
+GS_API int gs_score_raw_dev_noalloc(gs_ctx* ctx, const uint32_t* d_pod_app, const float* d_pod_slo,
+                                    int32_t n_pods, uint8_t* d_score, uint8_t* d_sel,
+                                    uint64_t* d_hi_arg, uint64_t* d_neg_lo, void* stream);
+
 /* NormalizeScore alone on a caller-provided score list (one pod): the framework's
  * NodeScoreList as int64 scores.  Replaces gpu_plugins.go:816-841 literally. */
 GS_API int gs_normalize_scores(gs_ctx* ctx, int64_t* scores, int32_t n_scores);

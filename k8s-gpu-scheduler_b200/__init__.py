@@ -23,13 +23,14 @@ LIB_PATH = os.path.join(_HERE, "libgpusched.so")
 GS_OK = 0
 SCORE_RAW, SCORE_NORMALIZE, SCORE_DIRECT = 0, 1, 2
 SEL_NONE = 31
+NOALLOC_MAX_PODS, NOALLOC_MAX_APPS, NOALLOC_MAX_RESIDENTS = 65536, 4096, 131072
 ERR_NAMES = {-1: "GS_ERR_INVALID", -2: "GS_ERR_CUDA", -3: "GS_ERR_STATE", -4: "GS_ERR_NOMEM",
              -5: "GS_ERR_UNSUPPORTED", -6: "GS_ERR_NOCONV"}
 
 # every symbol include/gpusched.h declares
 EXPORTS = [
     "gs_create", "gs_destroy", "gs_last_error", "gs_version", "gs_upload_cluster", "gs_upload_predictions",
-    "gs_score_batch", "gs_score_raw_dev", "gs_normalize_dev", "gs_normalize_scores", "gs_select_mig",
+    "gs_score_batch", "gs_score_raw_dev", "gs_score_raw_dev_noalloc", "gs_normalize_dev", "gs_normalize_scores", "gs_select_mig",
     "gs_set_profiling", "gs_last_score_kernel_ms", "gs_selftest", "gs_complete_fit", "gs_complete_transform", "gs_model_info", "gs_model_step", "gs_model_destroy",
 ]
 
@@ -74,6 +75,7 @@ def load_library():
     L.gs_upload_predictions.argtypes = [vp, C.POINTER(_GsPredictions)]
     L.gs_score_batch.argtypes = [vp, vp, vp, vp, i32, u32, vp, vp, vp]
     L.gs_score_raw_dev.argtypes = [vp, vp, vp, vp, i32, u32, vp, vp, vp, vp, vp]
+    L.gs_score_raw_dev_noalloc.argtypes = [vp, vp, vp, i32, vp, vp, vp, vp, vp]
     L.gs_normalize_dev.argtypes = [vp, i32, vp, vp, vp, vp, vp]
     L.gs_normalize_scores.argtypes = [vp, vp, i32]
     L.gs_select_mig.argtypes = [vp, vp, vp, i32, vp]
@@ -175,6 +177,12 @@ class Scheduler:
         self._check(self._L.gs_score_raw_dev(self._h, _ptr(d_app), _ptr(d_slo), _ptr(d_self), int(n_pods),
                                              SCORE_DIRECT if direct else 0, _ptr(d_score), _ptr(d_sel),
                                              _ptr(d_hi_arg), _ptr(d_neg_lo), _ptr(stream)))
+
+    def score_raw_dev_noalloc(self, d_app, d_slo, n_pods, d_score, d_sel, d_hi_arg, d_neg_lo, stream=None):
+        """gs_score_raw_dev_noalloc: same results as score_raw_dev, all working memory taken from the
+        library's fixed device array (no allocation); refuses batches beyond GS_NOALLOC_MAX_*."""
+        self._check(self._L.gs_score_raw_dev_noalloc(self._h, _ptr(d_app), _ptr(d_slo), int(n_pods), _ptr(d_score),
+                                                     _ptr(d_sel), _ptr(d_hi_arg), _ptr(d_neg_lo), _ptr(stream)))
 
     def normalize_dev(self, n_pods, d_score, d_hi_arg, d_neg_lo, d_best=None, stream=None):
         self._check(self._L.gs_normalize_dev(self._h, int(n_pods), _ptr(d_score), _ptr(d_hi_arg), _ptr(d_neg_lo),

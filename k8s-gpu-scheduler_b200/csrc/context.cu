@@ -124,8 +124,6 @@ using gs::Ctx;
     if (_e != cudaSuccess) return (ctx)->cuda_fail(_e, #call);   \
   } while (0)
 
-struct gs_ctx : public gs::Ctx {};
-
 extern "C" {
 
 const char* gs_version(void) { return "gpusched 0.1 sm_100a " __DATE__; }

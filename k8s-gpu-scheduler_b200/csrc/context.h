@@ -55,3 +55,6 @@ struct Ctx {
 cudaError_t launch_normalize_i64(long long* scores, int n, cudaStream_t s);
 
 }  // namespace gs
+
+// the opaque handle of include/gpusched.h
+struct gs_ctx : public gs::Ctx {};
