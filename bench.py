@@ -99,7 +99,12 @@ def cpu_reference_leg(preds, cluster, pods, budget_evals_per_thread=1_500_000, s
     """The CPU restatement of the reference algorithm on a bounded sample (first pods of the batch)."""
     from oracle.score_oracle import Oracle, num_threads
 
-    threads = num_threads()
+    # all host cores this process may use (torchrun exports OMP_NUM_THREADS=1; the oracle sets its
+    # own thread count explicitly)
+    try:
+        threads = len(os.sched_getaffinity(0))
+    except AttributeError:
+        threads = os.cpu_count() or num_threads()
     n_sample = max(8, min(pods.n_pods, int(budget_evals_per_thread * threads / max(1, cluster.n_nodes))))
     sub = type(pods)(app=pods.app[:n_sample], slo=pods.slo[:n_sample])
     ora = Oracle(preds, cluster)
