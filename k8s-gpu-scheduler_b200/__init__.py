@@ -215,4 +215,51 @@ class Scheduler:
         return out
 
 
+class CompletionModel:
+    """A fitted recommender completion model (gs_model): the reference's Imputer on the GPU."""
+
+    def __init__(self, sched: "Scheduler", handle):
+        self._s, self._h = sched, handle
+        d, r, n = C.c_int32(), C.c_int32(), C.c_int32()
+        sched._L.gs_model_info(handle, C.byref(d), C.byref(r), C.byref(n))
+        self.n_features, self.n_rounds, self.n_steps = d.value, r.value, n.value
+
+    def transform(self, X) -> np.ndarray:
+        X = np.ascontiguousarray(X, dtype=np.float64)
+        if X.ndim != 2 or X.shape[1] != self.n_features:
+            raise ValueError(f"expected [m, {self.n_features}]")
+        out = np.empty_like(X)
+        self._s._check(self._s._L.gs_complete_transform(self._s._h, self._h, _ptr(X), int(X.shape[0]), _ptr(out)))
+        return out
+
+    def steps(self):
+        """[(feature, coef[d-1], intercept)] in fitting order (IterativeImputer.imputation_sequence_)."""
+        out = []
+        for s in range(self.n_steps):
+            f, ic = C.c_int32(), C.c_double()
+            coef = np.empty(max(self.n_features - 1, 0), dtype=np.float64)
+            self._s._L.gs_model_step(self._h, s, C.byref(f), _ptr(coef), C.byref(ic))
+            out.append((f.value, coef, ic.value))
+        return out
+
+    def close(self):
+        if self._h:
+            self._s._L.gs_model_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def complete_fit(sched: "Scheduler", X) -> CompletionModel:
+    """Imputer.fit (pkg/recommender/recommender/recommender.py:15-22) on the GPU."""
+    X = np.ascontiguousarray(X, dtype=np.float64)
+    h = C.c_void_p()
+    sched._check(sched._L.gs_complete_fit(sched._h, _ptr(X), int(X.shape[0]), int(X.shape[1]), C.byref(h)))
+    return CompletionModel(sched, h)
+
+
 MIG_CONFIGS = ["all-4g.24gb", "all-2g.12gb", "all-1g.6gb"]  # gpu_plugins.go:52

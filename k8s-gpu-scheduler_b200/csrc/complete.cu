@@ -1,18 +1,681 @@
-// complete.cu — recommender completion (IterativeImputer + BayesianRidge) entry points.
-// Placeholder bodies until the CUDA path lands: they fail loudly, never fall back.
+// complete.cu — recommender completion on the GPU: fit / transform of the reference's
+// Imputer = sklearn IterativeImputer(max_iter=10, random_state=0) with BayesianRidge
+// (pkg/recommender/recommender/recommender.py:15-27).  The arithmetic restated here is
+// scikit-learn's (impute/_iterative.py:723-927, linear_model/_bayes.py:217-428 in 1.9.0),
+// reformulated for the GPU:
+//   * per feature j the estimator needs only second moments of the rows where j is observed:
+//     the centred Gram matrix G of ALL d columns over those rows (gram_* kernels, float64).
+//     X^T X = G[others][others], X^T y = G[others][j], y^T y = G[j][j], var(y) = G[j][j]/n;
+//   * the SVD of X in BayesianRidge.fit becomes the symmetric eigendecomposition of X^T X
+//     (parallel cyclic Jacobi, one CTA): eigen_vals = S^2, Vh = V^T;
+//   * the alpha/lambda fixed-point iteration (<= 300 rounds) then costs O(d^2) per round in
+//     one CTA: coef~ = (V^T X^T y)/(s + lambda/alpha), coef = V coef~,
+//     sse = y^T y - 2 coef~.b~ + sum(coef~^2 s);
+//   * rows where j is missing get x.coef + intercept (predict_kernel).
+// Everything is float64; parity bar: 1e-5 relative against Imputer.predict (tests/golden).
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <mutex>
+#include <new>
+#include <vector>
+
 #include "../../include/gpusched.h"
+#include "context.h"
+
+namespace gs {
+
+constexpr int kMaxFeatures = 256;  // d - 1 <= 255: the one-CTA Jacobi's range
+constexpr int kGramTile = 32;
+constexpr int kRounds = 10;        // IterativeImputer(max_iter=10), recommender.py:16
+constexpr double kRoundTol = 1e-3; // IterativeImputer tol
+constexpr int kBrMaxIter = 300;    // BayesianRidge defaults
+constexpr double kBrTol = 1e-3;
+constexpr double kBrPrior = 1e-6;  // alpha_1 = alpha_2 = lambda_1 = lambda_2
+
+// ---- initial imputation: column means over the observed entries (SimpleImputer "mean") ----
+__global__ void __launch_bounds__(256) column_stats_kernel(const double* __restrict__ X, int n, int d,
+                                                          double* __restrict__ means, int* __restrict__ n_missing,
+                                                          double* __restrict__ max_abs) {
+  __shared__ double s_sum[256];
+  __shared__ double s_max[256];
+  __shared__ int s_cnt[256];
+  const int c = blockIdx.x;
+  double sum = 0.0, mx = 0.0;
+  int cnt = 0;
+  for (int r = threadIdx.x; r < n; r += blockDim.x) {
+    double v = X[(size_t)r * d + c];
+    if (v == v) {
+      sum += v;
+      mx = fmax(mx, fabs(v));
+      ++cnt;
+    }
+  }
+  s_sum[threadIdx.x] = sum;
+  s_max[threadIdx.x] = mx;
+  s_cnt[threadIdx.x] = cnt;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) {
+      s_sum[threadIdx.x] += s_sum[threadIdx.x + s];
+      s_max[threadIdx.x] = fmax(s_max[threadIdx.x], s_max[threadIdx.x + s]);
+      s_cnt[threadIdx.x] += s_cnt[threadIdx.x + s];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    means[c] = s_cnt[0] ? s_sum[0] / (double)s_cnt[0] : 0.0;
+    n_missing[c] = n - s_cnt[0];
+    max_abs[c] = s_max[0];
+  }
+}
+
+__global__ void fill_kernel(const double* __restrict__ X, const double* __restrict__ means, size_t total, int d,
+                            double* __restrict__ Xt, uint8_t* __restrict__ mask) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  double v = X[i];
+  bool miss = !(v == v);
+  mask[i] = miss ? 1 : 0;
+  Xt[i] = miss ? means[i % d] : v;
+}
+
+// ---- moments over the rows where feature j is observed ----
+// column sums (all d columns) + row count; one CTA per column
+__global__ void __launch_bounds__(256) obs_means_kernel(const double* __restrict__ Xt, const uint8_t* __restrict__ mask,
+                                                       int n, int d, int j, double* __restrict__ mu,
+                                                       int* __restrict__ n_obs) {
+  __shared__ double s_sum[256];
+  __shared__ int s_cnt[256];
+  const int c = blockIdx.x;
+  double sum = 0.0;
+  int cnt = 0;
+  for (int r = threadIdx.x; r < n; r += blockDim.x) {
+    if (!mask[(size_t)r * d + j]) {
+      sum += Xt[(size_t)r * d + c];
+      ++cnt;
+    }
+  }
+  s_sum[threadIdx.x] = sum;
+  s_cnt[threadIdx.x] = cnt;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) {
+      s_sum[threadIdx.x] += s_sum[threadIdx.x + s];
+      s_cnt[threadIdx.x] += s_cnt[threadIdx.x + s];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    mu[c] = s_cnt[0] ? s_sum[0] / (double)s_cnt[0] : 0.0;
+    if (c == 0) *n_obs = s_cnt[0];
+  }
+}
+
+// Partial centred Gram: grid = (tiles_b, tiles_a, row_parts); CTA 16x16 threads, each a 2x2
+// block of the 32x32 output tile; rows of the part staged 32 at a time in shared memory,
+// centred, rows where j is missing zeroed.  Only tiles with tile_b >= tile_a are computed.
+__global__ void __launch_bounds__(256) gram_partial_kernel(const double* __restrict__ Xt,
+                                                          const uint8_t* __restrict__ mask, int n, int d, int j,
+                                                          const double* __restrict__ mu, int rows_per_part,
+                                                          double* __restrict__ partial) {
+  if (blockIdx.x < blockIdx.y) return;
+  __shared__ double sa[kGramTile][kGramTile + 1];  // [row][col a]
+  __shared__ double sb[kGramTile][kGramTile + 1];
+  const int a0 = blockIdx.y * kGramTile, b0 = blockIdx.x * kGramTile;
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  const int r_begin = blockIdx.z * rows_per_part;
+  const int r_end = min(n, r_begin + rows_per_part);
+  double acc[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+  for (int r0 = r_begin; r0 < r_end; r0 += kGramTile) {
+    // 256 threads load 32 rows x 32 cols for each tile: thread -> (row = t / 8 .. , 4 cols)
+    for (int e = threadIdx.x; e < kGramTile * kGramTile; e += 256) {
+      const int rr = e / kGramTile, cc = e % kGramTile;
+      const int r = r0 + rr;
+      const bool live = r < r_end && !mask[(size_t)r * d + j];
+      const int ca = a0 + cc, cb = b0 + cc;
+      sa[rr][cc] = (live && ca < d) ? Xt[(size_t)r * d + ca] - mu[ca] : 0.0;
+      sb[rr][cc] = (live && cb < d) ? Xt[(size_t)r * d + cb] - mu[cb] : 0.0;
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int rr = 0; rr < kGramTile; ++rr) {
+      const double x0 = sa[rr][ty * 2], x1 = sa[rr][ty * 2 + 1];
+      const double y0 = sb[rr][tx * 2], y1 = sb[rr][tx * 2 + 1];
+      acc[0][0] = fma(x0, y0, acc[0][0]);
+      acc[0][1] = fma(x0, y1, acc[0][1]);
+      acc[1][0] = fma(x1, y0, acc[1][0]);
+      acc[1][1] = fma(x1, y1, acc[1][1]);
+    }
+    __syncthreads();
+  }
+  double* out = partial + (size_t)blockIdx.z * d * d;
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const int a = a0 + ty * 2 + i, b = b0 + tx * 2 + k;
+      if (a < d && b < d) out[(size_t)a * d + b] = acc[i][k];
+    }
+}
+
+// G[a][b] = sum over parts (fixed order: deterministic), mirrored to the lower triangle
+__global__ void gram_reduce_kernel(const double* __restrict__ partial, int d, int parts, double* __restrict__ G) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= d * d) return;
+  int a = idx / d, b = idx % d;
+  if (b / kGramTile < a / kGramTile) return;  // tile not computed; filled by its mirror
+  double s = 0.0;
+  for (int p = 0; p < parts; ++p) s += partial[(size_t)p * d * d + idx];
+  G[idx] = s;
+  if (a / kGramTile != b / kGramTile) G[(size_t)b * d + a] = s;
+}
+
+// ---- symmetric eigendecomposition: parallel cyclic Jacobi, one CTA ----
+// A (m x m, row-major, destroyed: its diagonal ends as the eigenvalues), V (m x m) the
+// eigenvectors in columns.  Round-robin ordering gives m/2 disjoint rotations per step.
+__global__ void __launch_bounds__(1024) jacobi_eig_kernel(const double* __restrict__ G, int d, int j,
+                                                         double* __restrict__ A, double* __restrict__ V,
+                                                         double* __restrict__ evals, int* __restrict__ sweeps_out) {
+  __shared__ double s_c[kMaxFeatures / 2 + 1], s_s[kMaxFeatures / 2 + 1];
+  __shared__ int s_p[kMaxFeatures / 2 + 1], s_q[kMaxFeatures / 2 + 1];
+  __shared__ double s_red[1024];
+  __shared__ double s_off, s_norm;
+  const int m = d - 1;
+  const int tid = threadIdx.x, nt = blockDim.x;
+  // A = G without row/column j; V = I
+  for (int e = tid; e < m * m; e += nt) {
+    int a = e / m, b = e % m;
+    int ga = a < j ? a : a + 1, gb = b < j ? b : b + 1;
+    A[e] = G[(size_t)ga * d + gb];
+    V[e] = a == b ? 1.0 : 0.0;
+  }
+  __syncthreads();
+  const int M = (m + 1) & ~1;  // players, even
+  const int half = M / 2;
+  int sweep = 0;
+  for (; sweep < 60; ++sweep) {
+    // off-diagonal and total Frobenius norms
+    double off = 0.0, tot = 0.0;
+    for (int e = tid; e < m * m; e += nt) {
+      double v = A[e];
+      tot += v * v;
+      if (e / m != e % m) off += v * v;
+    }
+    s_red[tid] = off;
+    __syncthreads();
+    for (int s = nt >> 1; s > 0; s >>= 1) {
+      if (tid < s) s_red[tid] += s_red[tid + s];
+      __syncthreads();
+    }
+    if (tid == 0) s_off = s_red[0];
+    __syncthreads();
+    s_red[tid] = tot;
+    __syncthreads();
+    for (int s = nt >> 1; s > 0; s >>= 1) {
+      if (tid < s) s_red[tid] += s_red[tid + s];
+      __syncthreads();
+    }
+    if (tid == 0) s_norm = s_red[0];
+    __syncthreads();
+    if (s_off <= 1e-30 * s_norm || s_norm == 0.0) break;  // off/||A|| <= 1e-15
+    for (int step = 0; step < M - 1; ++step) {
+      // pairs of this step
+      if (tid < half) {
+        int p, q;
+        if (tid == 0) {
+          p = M - 1;
+          q = step;
+        } else {
+          p = (step + tid) % (M - 1);
+          q = (step - tid + (M - 1)) % (M - 1);
+        }
+        if (p > q) {
+          int t = p;
+          p = q;
+          q = t;
+        }
+        double c = 1.0, s = 0.0;
+        if (q < m) {
+          const double apq = A[(size_t)p * m + q];
+          const double app = A[(size_t)p * m + p], aqq = A[(size_t)q * m + q];
+          if (fabs(apq) > 1e-300 && fabs(apq) > 1e-18 * sqrt(fabs(app * aqq))) {
+            const double theta = (aqq - app) / (2.0 * apq);
+            const double t = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+            c = 1.0 / sqrt(t * t + 1.0);
+            s = t * c;
+          }
+        } else {
+          q = -1;  // dummy player
+        }
+        s_p[tid] = p;
+        s_q[tid] = q;
+        s_c[tid] = c;
+        s_s[tid] = s;
+      }
+      __syncthreads();
+      // columns: A <- A J, V <- V J
+      for (int e = tid; e < half * m; e += nt) {
+        const int pr = e / m, i = e % m;
+        const int q = s_q[pr];
+        if (q < 0 || s_s[pr] == 0.0) continue;
+        const int p = s_p[pr];
+        const double c = s_c[pr], s = s_s[pr];
+        const double aip = A[(size_t)i * m + p], aiq = A[(size_t)i * m + q];
+        A[(size_t)i * m + p] = c * aip - s * aiq;
+        A[(size_t)i * m + q] = s * aip + c * aiq;
+        const double vip = V[(size_t)i * m + p], viq = V[(size_t)i * m + q];
+        V[(size_t)i * m + p] = c * vip - s * viq;
+        V[(size_t)i * m + q] = s * vip + c * viq;
+      }
+      __syncthreads();
+      // rows: A <- J^T A
+      for (int e = tid; e < half * m; e += nt) {
+        const int pr = e / m, i = e % m;
+        const int q = s_q[pr];
+        if (q < 0 || s_s[pr] == 0.0) continue;
+        const int p = s_p[pr];
+        const double c = s_c[pr], s = s_s[pr];
+        const double api = A[(size_t)p * m + i], aqi = A[(size_t)q * m + i];
+        A[(size_t)p * m + i] = c * api - s * aqi;
+        A[(size_t)q * m + i] = s * api + c * aqi;
+      }
+      __syncthreads();
+    }
+  }
+  for (int k = tid; k < m; k += nt) evals[k] = fmax(A[(size_t)k * m + k], 0.0);  // S^2 >= 0
+  if (tid == 0) *sweeps_out = sweep;
+}
+
+// ---- BayesianRidge's evidence iteration in the eigenbasis, one CTA ----
+__device__ __forceinline__ double block_sum(double v, double* s_red) {
+  const int tid = threadIdx.x;
+  __syncthreads();
+  s_red[tid] = v;
+  __syncthreads();
+  for (int s = blockDim.x >> 1; s > 0; s >>= 1) {
+    if (tid < s) s_red[tid] += s_red[tid + s];
+    __syncthreads();
+  }
+  const double r = s_red[0];
+  __syncthreads();
+  return r;
+}
+
+__global__ void __launch_bounds__(256) bayes_ridge_kernel(const double* __restrict__ G, const double* __restrict__ mu,
+                                                         const int* __restrict__ n_obs_p, int d, int j,
+                                                         const double* __restrict__ V, const double* __restrict__ evals,
+                                                         double* __restrict__ coef_out, double* __restrict__ intercept_out,
+                                                         int* __restrict__ iters_out) {
+  __shared__ double s_red[256];
+  __shared__ double s_b[kMaxFeatures], s_bt[kMaxFeatures], s_ct[kMaxFeatures], s_coef[kMaxFeatures],
+      s_old[kMaxFeatures], s_ev[kMaxFeatures];
+  const int m = d - 1, tid = threadIdx.x, nt = blockDim.x;
+  const double n = (double)*n_obs_p;
+  for (int i = tid; i < m; i += nt) {
+    const int gi = i < j ? i : i + 1;
+    s_b[i] = G[(size_t)gi * d + j];  // X^T y
+    s_ev[i] = evals[i];
+    s_old[i] = 0.0;
+  }
+  __syncthreads();
+  const double yy = G[(size_t)j * d + j];
+  for (int k = tid; k < m; k += nt) {  // b~ = V^T b
+    double acc = 0.0;
+    for (int i = 0; i < m; ++i) acc += V[(size_t)i * m + k] * s_b[i];
+    s_bt[k] = acc;
+  }
+  __syncthreads();
+  const double eps = 2.220446049250313e-16;
+  double alpha = 1.0 / (yy / n + eps);  // 1/(var(y)+eps), population variance
+  double lambda = 1.0;
+  int it = 0;
+  auto update = [&](double al, double la, double* sse) {
+    const double ratio = la / al;
+    for (int k = tid; k < m; k += nt) s_ct[k] = s_bt[k] / (s_ev[k] + ratio);
+    __syncthreads();
+    for (int i = tid; i < m; i += nt) {  // coef = V coef~
+      double acc = 0.0;
+      for (int k = 0; k < m; ++k) acc += V[(size_t)i * m + k] * s_ct[k];
+      s_coef[i] = acc;
+    }
+    double t1 = 0.0, t2 = 0.0;
+    for (int k = tid; k < m; k += nt) {
+      t1 += s_ct[k] * s_bt[k];
+      t2 += s_ct[k] * s_ct[k] * s_ev[k];
+    }
+    const double a = block_sum(t1, s_red), b = block_sum(t2, s_red);
+    *sse = fmax(yy - 2.0 * a + b, 0.0);
+  };
+  for (it = 0; it < kBrMaxIter; ++it) {
+    double sse;
+    update(alpha, lambda, &sse);
+    double g = 0.0, sq = 0.0, dl = 0.0;
+    for (int k = tid; k < m; k += nt) g += (alpha * s_ev[k]) / (lambda + alpha * s_ev[k]);
+    for (int i = tid; i < m; i += nt) {
+      sq += s_coef[i] * s_coef[i];
+      dl += fabs(s_old[i] - s_coef[i]);
+    }
+    const double gamma = block_sum(g, s_red);
+    const double sumsq = block_sum(sq, s_red);
+    const double delta = block_sum(dl, s_red);
+    lambda = (gamma + 2.0 * kBrPrior) / (sumsq + 2.0 * kBrPrior);
+    alpha = (n - gamma + 2.0 * kBrPrior) / (sse + 2.0 * kBrPrior);
+    if (it != 0 && delta < kBrTol) break;
+    for (int i = tid; i < m; i += nt) s_old[i] = s_coef[i];
+    __syncthreads();
+  }
+  double sse;
+  update(alpha, lambda, &sse);
+  double dot = 0.0;
+  for (int i = tid; i < m; i += nt) {
+    const int gi = i < j ? i : i + 1;
+    coef_out[i] = s_coef[i];
+    dot += mu[gi] * s_coef[i];
+  }
+  const double xo = block_sum(dot, s_red);
+  if (tid == 0) {
+    *intercept_out = mu[j] - xo;
+    *iters_out = it < kBrMaxIter ? it + 1 : kBrMaxIter;
+  }
+}
+
+// rows where feature j is missing: Xt[r][j] = Xt[r][others] . coef + intercept; one warp per row
+__global__ void __launch_bounds__(256) predict_kernel(double* __restrict__ Xt, const uint8_t* __restrict__ mask, int n,
+                                                     int d, int j, const double* __restrict__ coef,
+                                                     const double* __restrict__ intercept) {
+  const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (r >= n || !mask[(size_t)r * d + j]) return;
+  double acc = 0.0;
+  for (int c = lane; c < d; c += 32) {
+    if (c == j) continue;
+    acc += Xt[(size_t)r * d + c] * coef[c < j ? c : c - 1];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
+  if (lane == 0) Xt[(size_t)r * d + j] = acc + *intercept;
+}
+
+__global__ void __launch_bounds__(256) max_abs_diff_kernel(const double* __restrict__ a, const double* __restrict__ b,
+                                                          size_t total, double* __restrict__ out) {
+  __shared__ double s_red[256];
+  double mx = 0.0;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x)
+    mx = fmax(mx, fabs(a[i] - b[i]));
+  s_red[threadIdx.x] = mx;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) s_red[threadIdx.x] = fmax(s_red[threadIdx.x], s_red[threadIdx.x + s]);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[blockIdx.x] = s_red[0];
+}
+
+// transform: one warp per row, the row in shared memory, every stored step replayed in order
+// (impute/_iterative.py:907-915); observed entries never change.
+__global__ void __launch_bounds__(128) transform_kernel(const double* __restrict__ X, int m_rows, int d,
+                                                       const double* __restrict__ means, const int* __restrict__ feat,
+                                                       const double* __restrict__ coef,
+                                                       const double* __restrict__ intercept, int n_steps,
+                                                       double* __restrict__ out) {
+  extern __shared__ double s_rows[];  // [4 warps][d] values, then [4 warps][d] mask bytes packed as doubles' tail
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int r = blockIdx.x * 4 + warp;
+  if (r >= m_rows) return;
+  double* row = s_rows + (size_t)warp * d;
+  uint8_t* miss = reinterpret_cast<uint8_t*>(s_rows + (size_t)4 * d) + (size_t)warp * d;
+  for (int c = lane; c < d; c += 32) {
+    const double v = X[(size_t)r * d + c];
+    const bool ms = !(v == v);
+    miss[c] = ms ? 1 : 0;
+    row[c] = ms ? means[c] : v;
+  }
+  __syncwarp();
+  for (int s = 0; s < n_steps; ++s) {
+    const int j = feat[s];
+    if (!miss[j]) continue;
+    const double* cf = coef + (size_t)s * (d - 1);
+    double acc = 0.0;
+    for (int c = lane; c < d; c += 32) {
+      if (c == j) continue;
+      acc += row[c] * cf[c < j ? c : c - 1];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, o);
+    __syncwarp();
+    if (lane == 0) row[j] = acc + intercept[s];
+    __syncwarp();
+  }
+  for (int c = lane; c < d; c += 32) out[(size_t)r * d + c] = row[c];
+}
+
+}  // namespace gs
+
+// ------------------------------------------------------------------------------------------
 
 struct gs_model {
-  int d;
+  int d = 0, n_rounds = 0, n_steps = 0;
+  std::vector<double> means, coef, intercept;
+  std::vector<int> feat;
 };
 
+namespace {
+
+struct DevMem {
+  std::vector<void*> ptrs;
+  ~DevMem() {
+    for (void* p : ptrs) cudaFree(p);
+  }
+  template <typename T>
+  cudaError_t alloc(T** out, size_t count) {
+    void* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, sizeof(T) * (count ? count : 1));
+    if (e == cudaSuccess) ptrs.push_back(p);
+    *out = static_cast<T*>(p);
+    return e;
+  }
+};
+
+#define CK(call)                                              \
+  do {                                                        \
+    cudaError_t _e = (call);                                  \
+    if (_e != cudaSuccess) return c->cuda_fail(_e, #call);    \
+  } while (0)
+
+}  // namespace
+
 extern "C" {
-int gs_complete_fit(gs_ctx*, const double*, int32_t, int32_t, gs_model** out) {
+
+int gs_complete_fit(gs_ctx* c, const double* X, int32_t n, int32_t d, gs_model** out) {
+  using namespace gs;
   if (out) *out = nullptr;
-  return GS_ERR_UNSUPPORTED;
+  if (!c) return GS_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(c->mu);
+  if (!X || !out || n < 1 || d < 1) return c->fail(GS_ERR_INVALID, "gs_complete_fit: null pointer or empty matrix");
+  if (d - 1 >= kMaxFeatures)
+    return c->fail(GS_ERR_UNSUPPORTED, "gs_complete_fit: %d columns; this build's eigen-solver covers at most %d", d,
+                   kMaxFeatures);
+  CK(cudaSetDevice(c->device));
+  cudaStream_t s = c->stream;
+  const size_t total = (size_t)n * d;
+  DevMem mem;
+  double *dX, *dXt, *dPrev, *dMeans, *dMaxAbs, *dMu, *dG, *dPartial, *dA, *dV, *dEv, *dCoef, *dIcpt, *dDiff;
+  uint8_t* dMask;
+  int *dMissing, *dNobs, *dIters, *dSweeps;
+  const int tiles = (d + kGramTile - 1) / kGramTile;
+  int parts = (n + 255) / 256;
+  if (parts > 128) parts = 128;
+  if (parts < 1) parts = 1;
+  int rows_per_part = (n + parts - 1) / parts;
+  rows_per_part = (rows_per_part + kGramTile - 1) / kGramTile * kGramTile;
+  parts = (n + rows_per_part - 1) / rows_per_part;
+  const int max_steps = kRounds * d;
+  CK(mem.alloc(&dX, total));
+  CK(mem.alloc(&dXt, total));
+  CK(mem.alloc(&dPrev, total));
+  CK(mem.alloc(&dMask, total));
+  CK(mem.alloc(&dMeans, d));
+  CK(mem.alloc(&dMaxAbs, d));
+  CK(mem.alloc(&dMissing, d));
+  CK(mem.alloc(&dMu, d));
+  CK(mem.alloc(&dNobs, 1));
+  CK(mem.alloc(&dG, (size_t)d * d));
+  CK(mem.alloc(&dPartial, (size_t)parts * d * d));
+  CK(mem.alloc(&dA, (size_t)d * d));
+  CK(mem.alloc(&dV, (size_t)d * d));
+  CK(mem.alloc(&dEv, d));
+  CK(mem.alloc(&dCoef, (size_t)max_steps * (d > 1 ? d - 1 : 1)));
+  CK(mem.alloc(&dIcpt, max_steps));
+  CK(mem.alloc(&dIters, max_steps));
+  CK(mem.alloc(&dSweeps, max_steps));
+  CK(mem.alloc(&dDiff, 256));
+  CK(cudaMemcpyAsync(dX, X, sizeof(double) * total, cudaMemcpyHostToDevice, s));
+
+  gs_model* m = new (std::nothrow) gs_model();
+  if (!m) return c->fail(GS_ERR_NOMEM, "gs_complete_fit: out of host memory");
+  m->d = d;
+  m->means.resize(d);
+  std::vector<int> missing(d);
+  std::vector<double> max_abs(d);
+
+  column_stats_kernel<<<d, 256, 0, s>>>(dX, n, d, dMeans, dMissing, dMaxAbs);
+  fill_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(dX, dMeans, total, d, dXt, dMask);
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaMemcpyAsync(m->means.data(), dMeans, sizeof(double) * d, cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(missing.data(), dMissing, sizeof(int) * d, cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(max_abs.data(), dMaxAbs, sizeof(double) * d, cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  if (e != cudaSuccess) {
+    delete m;
+    return c->cuda_fail(e, "completion: initial imputation");
+  }
+  bool all_missing = true;
+  for (int k = 0; k < d; ++k) {
+    if (missing[k] == n) {
+      delete m;
+      return c->fail(GS_ERR_UNSUPPORTED, "gs_complete_fit: column %d has no observed value (scikit-learn drops such "
+                     "columns; not served)", k);
+    }
+    if (missing[k] != n) all_missing = false;
+  }
+  if (d == 1 || all_missing) {  // _iterative.py:783-789: nothing to iterate
+    *out = m;
+    return GS_OK;
+  }
+  // ascending missing fraction, stable (np.argsort(kind="mergesort")), all columns (skip_complete=False)
+  std::vector<int> order(d);
+  for (int k = 0; k < d; ++k) order[k] = k;
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return missing[a] < missing[b]; });
+  double mx = 0.0;
+  for (double v : max_abs) mx = std::fmax(mx, v);
+  const double norm_tol = kRoundTol * mx;
+
+  int step = 0;
+  std::vector<double> diff(256);
+  CK(cudaMemcpyAsync(dPrev, dXt, sizeof(double) * total, cudaMemcpyDeviceToDevice, s));
+  for (int rnd = 1; rnd <= kRounds; ++rnd) {
+    m->n_rounds = rnd;
+    for (int oi = 0; oi < d; ++oi, ++step) {
+      const int j = order[oi];
+      obs_means_kernel<<<d, 256, 0, s>>>(dXt, dMask, n, d, j, dMu, dNobs);
+      gram_partial_kernel<<<dim3(tiles, tiles, parts), 256, 0, s>>>(dXt, dMask, n, d, j, dMu, rows_per_part, dPartial);
+      gram_reduce_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dPartial, d, parts, dG);
+      int jt = 32;
+      while (jt < 1024 && jt < (d - 1) * (d - 1) / 4) jt <<= 1;
+      jacobi_eig_kernel<<<1, jt, 0, s>>>(dG, d, j, dA, dV, dEv, dSweeps + step);
+      bayes_ridge_kernel<<<1, 256, 0, s>>>(dG, dMu, dNobs, d, j, dV, dEv, dCoef + (size_t)step * (d - 1), dIcpt + step,
+                                           dIters + step);
+      if (missing[j] > 0)
+        predict_kernel<<<(n + 7) / 8, 256, 0, s>>>(dXt, dMask, n, d, j, dCoef + (size_t)step * (d - 1), dIcpt + step);
+      m->feat.push_back(j);
+    }
+    max_abs_diff_kernel<<<256, 256, 0, s>>>(dXt, dPrev, total, dDiff);
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(diff.data(), dDiff, sizeof(double) * 256, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) {
+      delete m;
+      return c->cuda_fail(e, "completion: round");
+    }
+    double inf_norm = 0.0;
+    for (double v : diff) inf_norm = std::fmax(inf_norm, v);
+    if (inf_norm < norm_tol) break;  // _iterative.py:853-862
+    CK(cudaMemcpyAsync(dPrev, dXt, sizeof(double) * total, cudaMemcpyDeviceToDevice, s));
+  }
+  m->n_steps = step;
+  m->coef.resize((size_t)step * (d - 1));
+  m->intercept.resize(step);
+  std::vector<int> sweeps(step);
+  e = cudaMemcpyAsync(m->coef.data(), dCoef, sizeof(double) * m->coef.size(), cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(m->intercept.data(), dIcpt, sizeof(double) * step, cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(sweeps.data(), dSweeps, sizeof(int) * step, cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  if (e != cudaSuccess) {
+    delete m;
+    return c->cuda_fail(e, "completion: model download");
+  }
+  for (int k = 0; k < step; ++k)
+    if (sweeps[k] >= 60) {
+      delete m;
+      return c->fail(GS_ERR_NOCONV, "gs_complete_fit: the eigen-solver did not converge at step %d", k);
+    }
+  *out = m;
+  return GS_OK;
 }
-int gs_complete_transform(gs_ctx*, const gs_model*, const double*, int32_t, double*) { return GS_ERR_UNSUPPORTED; }
-int gs_model_info(const gs_model*, int32_t*, int32_t*, int32_t*) { return GS_ERR_UNSUPPORTED; }
-int gs_model_step(const gs_model*, int32_t, int32_t*, double*, double*) { return GS_ERR_UNSUPPORTED; }
-void gs_model_destroy(gs_model*) {}
+
+int gs_complete_transform(gs_ctx* c, const gs_model* m, const double* X, int32_t rows, double* out) {
+  using namespace gs;
+  if (!c) return GS_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(c->mu);
+  if (!m || rows < 0 || (rows && (!X || !out))) return c->fail(GS_ERR_INVALID, "gs_complete_transform: null pointer");
+  if (rows == 0) return GS_OK;
+  CK(cudaSetDevice(c->device));
+  cudaStream_t s = c->stream;
+  const int d = m->d;
+  const size_t total = (size_t)rows * d;
+  DevMem mem;
+  double *dX, *dOut, *dMeans, *dCoef, *dIcpt;
+  int* dFeat;
+  CK(mem.alloc(&dX, total));
+  CK(mem.alloc(&dOut, total));
+  CK(mem.alloc(&dMeans, d));
+  CK(mem.alloc(&dCoef, m->coef.size()));
+  CK(mem.alloc(&dIcpt, m->intercept.size()));
+  CK(mem.alloc(&dFeat, m->feat.size()));
+  CK(cudaMemcpyAsync(dX, X, sizeof(double) * total, cudaMemcpyHostToDevice, s));
+  CK(cudaMemcpyAsync(dMeans, m->means.data(), sizeof(double) * d, cudaMemcpyHostToDevice, s));
+  if (m->n_steps) {
+    CK(cudaMemcpyAsync(dCoef, m->coef.data(), sizeof(double) * m->coef.size(), cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(dIcpt, m->intercept.data(), sizeof(double) * m->n_steps, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(dFeat, m->feat.data(), sizeof(int) * m->n_steps, cudaMemcpyHostToDevice, s));
+  }
+  const size_t smem = (size_t)4 * d * sizeof(double) + (size_t)4 * d + 16;
+  CK(cudaFuncSetAttribute(transform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  transform_kernel<<<(rows + 3) / 4, 128, smem, s>>>(dX, rows, d, dMeans, dFeat, dCoef, dIcpt, m->n_steps, dOut);
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(out, dOut, sizeof(double) * total, cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  return GS_OK;
 }
+
+int gs_model_info(const gs_model* m, int32_t* n_features, int32_t* n_rounds, int32_t* n_steps) {
+  if (!m) return GS_ERR_INVALID;
+  if (n_features) *n_features = m->d;
+  if (n_rounds) *n_rounds = m->n_rounds;
+  if (n_steps) *n_steps = m->n_steps;
+  return GS_OK;
+}
+
+int gs_model_step(const gs_model* m, int32_t s, int32_t* feat, double* coef, double* intercept) {
+  if (!m || s < 0 || s >= m->n_steps) return GS_ERR_INVALID;
+  if (feat) *feat = m->feat[s];
+  if (coef)
+    for (int k = 0; k < m->d - 1; ++k) coef[k] = m->coef[(size_t)s * (m->d - 1) + k];
+  if (intercept) *intercept = m->intercept[s];
+  return GS_OK;
+}
+
+void gs_model_destroy(gs_model* m) { delete m; }
+
+}  // extern "C"
