@@ -12,6 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libgpusched.so")
 SOURCES = ["context.cu", "score_kernels.cu", "score_fast.cu", "complete.cu", "noalloc.cu"]
+HOST_SOURCES = ["host/gpu_plugin.cpp"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",
@@ -34,8 +35,9 @@ def needs_build() -> bool:
     if not os.path.exists(LIB):
         return True
     t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [
-        os.path.join(HERE, "..", "include", "gpusched.h"), os.path.abspath(__file__)]
+    deps = [os.path.join(b, f) for b, _, fs in os.walk(CSRC) for f in fs] + [
+        os.path.join(HERE, "..", "include", "gpusched.h"), os.path.join(HERE, "..", "include", "gpusched_host.h"),
+        os.path.abspath(__file__)]
     return any(os.path.getmtime(d) > t for d in deps)
 
 
@@ -50,6 +52,11 @@ def build(force: bool = False, verbose: bool = False) -> str:
     for src in SOURCES:
         obj = os.path.join(HERE, "build", src.replace(".cu", ".o"))
         cmd = [_nvcc(), *NVCC_FLAGS, "-ccbin", "/usr/bin/g++", "-c", os.path.join(CSRC, src), "-o", obj]
+        procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env)))
+        objs.append(obj)
+    for src in HOST_SOURCES:
+        obj = os.path.join(HERE, "build", os.path.basename(src).replace(".cpp", ".o"))
+        cmd = ["/usr/bin/g++", "-std=c++17", "-O2", "-fPIC", "-Wall", "-fvisibility=hidden", "-c", os.path.join(CSRC, src), "-o", obj]
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env)))
         objs.append(obj)
     log = []

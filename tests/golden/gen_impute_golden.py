@@ -37,9 +37,14 @@ def main():
     from recommender.recommender import Imputer
 
     cases = {}
+    names = {}
     for name in ("configurations", "interference"):
         df = pd.read_csv(f"{REF}/recommender/{name}_train.ods", sep="\t").set_index("index")
         cases[name] = df.to_numpy(dtype=np.float64)
+        names[name + "_index"] = np.array(list(df.index), dtype=str)
+        names[name + "_columns"] = np.array(list(df.columns), dtype=str)
+    # index / column names of the two training tables: the recommender's wire contract keys
+    np.savez_compressed(os.path.join(HERE, "recommender_table_names.npz"), **names)
     cases["synth_60x8"] = synthetic(60, 8, 3, 0.30, 1)
     cases["synth_200x12"] = synthetic(200, 12, 4, 0.30, 2)
     cases["synth_40x24_wide"] = synthetic(40, 24, 3, 0.25, 3)   # n_obs < d-1 for most features

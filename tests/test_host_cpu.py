@@ -1,0 +1,129 @@
+"""Host-side mirror of the reference plugin (include/gpusched_host.h): the string world of
+gpu_plugins.go -> structure-of-arrays tables.  No GPU needed: nothing here computes scores."""
+import os
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+# pkg/profiler/test.sh:3 — the profiler's example nvidia-smi list; on a MIG node only MIG UUIDs are kept
+MIG_UUIDS = ["MIG-7a700938-2114-5d88-a93c-167c2a498910", "MIG-c8956631-ac65-59d3-9065-c8764799febf",
+             "MIG-266f4973-a8c6-5697-a549-dfc880e350c1", "MIG-41e35365-768c-587c-a36e-65197e7a7f93"]
+
+
+@pytest.fixture()
+def host(pkg):
+    from k8s_gpu_scheduler_b200 import host as h
+
+    return h
+
+
+@pytest.fixture()
+def tables():
+    names = np.load(os.path.join(GOLD, "recommender_table_names.npz"))
+    conf = np.load(os.path.join(GOLD, "impute_configurations.npz"))["completed"]
+    interf = np.load(os.path.join(GOLD, "impute_interference.npz"))["completed"]
+    return names, conf, interf
+
+
+def json_list(items):
+    return "[" + ",".join('"%s"' % x for x in items) + "]"
+
+
+def test_header_and_binding_agree(host):
+    import ctypes
+    import re
+
+    text = open(os.path.join(ROOT, "include", "gpusched_host.h")).read()
+    declared = sorted(set(re.findall(r"GS_API\s+[\w\s\*]+?\b(gsp_\w+)\s*\(", text)))
+    assert declared == sorted(host.HOST_EXPORTS)
+    lib = ctypes.CDLL(os.path.join(ROOT, "k8s-gpu-scheduler_b200", "libgpusched.so"))
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert host.Plugin.name() == "GPU"   # gpu_plugins.go:50
+
+
+def test_parse_slo_follows_logic(host):
+    # gpu_plugins.go:459-469: "" -> 0; ParseFloat error -> 0; else float32(value)
+    assert host.parse_slo(None) == (0.0, False)
+    assert host.parse_slo("") == (0.0, False)
+    assert host.parse_slo("10") == (10.0, True)            # deploy/busybox/busybox.yaml:26-28
+    assert host.parse_slo("25.37") == (float(np.float32(25.37)), True)
+    assert host.parse_slo("abc") == (0.0, False)
+    assert host.parse_slo("12abc") == (0.0, False)
+    assert host.parse_slo(" 12") == (0.0, False)            # ParseFloat rejects white space
+    assert host.parse_slo("1e40") == (0.0, False)           # out of float32 range: ErrRange -> 0
+    assert host.parse_slo("0") == (0.0, True)
+    v, ok = host.parse_slo("1e-3")
+    assert ok and v == float(np.float32(1e-3))
+
+
+def test_real_recommender_tables_become_soa(host, tables):
+    names, conf, interf = tables
+    b = host.SnapshotBuilder()
+    b.set_configurations(names["configurations_index"], names["configurations_columns"], conf)
+    b.set_interference(names["interference_index"], names["interference_columns"], interf)
+    # app ids: first training index contained in the pod name with '-' -> '_' (recom_server.py:67-71,155-156)
+    assert b.app_of("onnx-mobilenet-1024-7d9f8") == 0
+    assert b.app_of("tensorflow-ssd-mobilenet-4096") == 17
+    assert b.app_of("prefix-onnx-resnet50-2048-x") == list(names["configurations_index"]).index("onnx_resnet50_2048")
+    assert b.app_of("busybox") == 0xFFFFFFFF
+    preds, cl = b.build()
+    assert preds.conf.shape == (18, 6) and np.array_equal(preds.conf, conf.astype(np.float32))
+    cols = list(names["configurations_columns"])
+    assert preds.col_of[0, 1] == cols.index("1P_A30") and preds.col_of[0, 4] == cols.index("4P_A30")
+    assert preds.col_of[1, 2] == cols.index("2P_V100") and preds.col_of[0, 8] == -1 and preds.col_of[1, 3] == -1
+    idx = list(names["interference_index"])
+    icol = list(names["interference_columns"])
+    r = idx.index("onnx_resnet50_1024_A30")
+    c = icol.index("tensorflow_mobilenet_2048")
+    a, bb = list(names["configurations_index"]).index("onnx_resnet50_1024"), list(names["configurations_index"]).index("tensorflow_mobilenet_2048")
+    assert preds.interf[0, a, bb] == np.float32(interf[r, c])        # model A30 = plane 0
+    r = idx.index("onnx_resnet50_1024_V100")
+    assert preds.interf[1, a, bb] == np.float32(interf[r, c])
+    b.close()
+
+
+def test_nodes_redis_values_and_residents(host, tables):
+    names, conf, interf = tables
+    b = host.SnapshotBuilder()
+    b.set_configurations(names["configurations_index"], names["configurations_columns"], conf)
+    b.set_interference(names["interference_index"], names["interference_columns"], interf)
+    n0 = b.add_node("k8s-a30-worker", json_list(MIG_UUIDS))          # "a30" tested first
+    n1 = b.add_node("gpu-a30-node", json_list(["GPU-1"]))            # contains both: A30 wins (:478)
+    n2 = b.add_node("gpu-node-2", json_list(["GPU-2a", "GPU-2b"]))   # "gpu" -> V100
+    n3 = b.add_node("cpu-only", json_list(["GPU-x"]))                # no model
+    n4 = b.add_node("gpu-node-nokey", None)                          # redis.Nil: empty list
+    n5 = b.add_node("gpu-node-badjson", "not json")                  # Unmarshal error ignored: empty list
+    assert (n0, n1, n2, n3, n4, n5) == (0, 1, 2, 3, 4, 5)
+    # GetSLOs (gpu_plugins.go:104-157)
+    b.add_pod("onnx-mobilenet-1024-aaa", "Running", MIG_UUIDS[1], "120.5")
+    b.add_pod("tensorflow-resnet50-2048-bbb", "Running", MIG_UUIDS[1], "0")       # SLO "0": resident with SLO 0
+    b.add_pod("onnx-ssd-mobilenet-1024-ccc", "Pending", MIG_UUIDS[1], "50")       # not Running (:105)
+    b.add_pod("onnx-ssd-mobilenet-1024-ddd", "Running", None, "50")               # no CUDA_VISIBLE_DEVICES (:131)
+    b.add_pod("onnx-ssd-mobilenet-1024-eee", "Running", "GPU-unknown", "50")      # UUID of no node (:135)
+    b.add_pod("onnx-ssd-mobilenet-1024-fff", "Running", "GPU-2b", None)           # no SLO env (:137-140)
+    b.add_pod("unknown-workload", "Running", "GPU-2b", "33")                      # unknown app still resides
+    b.add_pod("onnx-resnet50-4096-ggg", "Running", "GPU-2a", "77", namespace="kube-system")
+    preds, cl = b.build()
+    assert cl.node_model.tolist() == [1, 1, 2, 0, 2, 2]
+    assert cl.node_ngpu.tolist() == [4, 1, 2, 1, 0, 0]
+    assert cl.max_gpus == 4 and cl.gpu_off.size == 6 * 4 + 1
+    off = cl.gpu_off.reshape(-1)
+    # node 0, GPU 1 holds two residents in arrival order
+    assert off[1] == 0 and off[2] == 2
+    assert cl.res_app[:2].tolist() == [0, list(names["configurations_index"]).index("tensorflow_resnet50_2048")]
+    assert cl.res_slo[:2].tolist() == [120.5, 0.0]
+    # node 2, GPU 1 (GPU-2b) holds the unknown-app resident only
+    s = 2 * 4 + 1
+    assert off[s + 1] - off[s] == 1 and cl.res_app[off[s]] == 0xFFFFFFFF and cl.res_slo[off[s]] == 33.0
+    assert cl.res_app.size == 3
+    b.close()
+
+
+def test_more_than_31_uuids_is_refused(host):
+    b = host.SnapshotBuilder()
+    with pytest.raises(ValueError):
+        b.add_node("gpu-big", json_list([f"GPU-{i}" for i in range(32)]))
+    b.close()
