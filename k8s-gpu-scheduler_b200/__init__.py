@@ -18,7 +18,7 @@ from . import synth  # noqa: F401  (re-export)
 from .synth import APP_UNKNOWN, MODEL_A30, MODEL_NONE, MODEL_V100, Cluster, Pods, Predictions  # noqa: F401
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgpusched.so")
+LIB_PATH = os.environ.get("GS_LIB_PATH") or os.path.join(_HERE, "libgpusched.so")
 
 GS_OK = 0
 SCORE_RAW, SCORE_NORMALIZE, SCORE_DIRECT = 0, 1, 2

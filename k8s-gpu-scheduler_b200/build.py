@@ -41,7 +41,13 @@ def needs_build() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, tag: str = "", defines=()) -> str:
+    """tag/defines: tuning variants (libgpusched_<tag>.so built with extra -D flags; pick one at run
+    time with GS_LIB_PATH)."""
+    global LIB
+    if tag:
+        LIB = os.path.join(HERE, f"libgpusched_{tag}.so")
+        force = True
     if not force and not needs_build():
         return LIB
     env = dict(os.environ)
@@ -50,8 +56,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
     procs = []
     for src in SOURCES:
-        obj = os.path.join(HERE, "build", src.replace(".cu", ".o"))
-        cmd = [_nvcc(), *NVCC_FLAGS, "-ccbin", "/usr/bin/g++", "-c", os.path.join(CSRC, src), "-o", obj]
+        obj = os.path.join(HERE, "build", (tag + "_" if tag else "") + src.replace(".cu", ".o"))
+        cmd = [_nvcc(), *NVCC_FLAGS, *defines, "-ccbin", "/usr/bin/g++", "-c", os.path.join(CSRC, src), "-o", obj]
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env)))
         objs.append(obj)
     for src in HOST_SOURCES:
@@ -78,4 +84,6 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))
+    _tag = next((a.split("=", 1)[1] for a in sys.argv if a.startswith("--tag=")), "")
+    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv, tag=_tag,
+                defines=[a for a in sys.argv if a.startswith("-D")]))

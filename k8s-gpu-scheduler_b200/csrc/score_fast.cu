@@ -161,7 +161,7 @@ cudaError_t launch_transpose_interf(const float* interf, float* interf_t, int n_
 // ------------------------------------------------------------------ main kernel ------
 
 template <bool kTable>
-__global__ void __launch_bounds__(kTile, 4) score_fast_kernel(DevTables T, StageA stage, const PodRec* __restrict__ pods,
+__global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTables T, StageA stage, const PodRec* __restrict__ pods,
                                                              const ChunkDesc* __restrict__ chunks,
                                                              const uint32_t* __restrict__ n_chunks,
                                                              uint8_t* __restrict__ out_score,
@@ -194,50 +194,113 @@ __global__ void __launch_bounds__(kTile, 4) score_fast_kernel(DevTables T, Stage
   int nocand = (int)kSelNone;  // score << 8 | sel for pods without a candidate term (:667-696)
   bool thr_general = false;    // this node's sums/counts fall outside the streamlined domain
 
-  // Step 1+2, one GPU at a time (a rolled loop: its results go through thread-local arrays
-  // and are picked up into registers below).  GPUs a node does not have (and lanes without a
-  // node) keep constants that evaluate to tmp = 0 + 100*((0*(0+v))/1) = 0: they can never
-  // win (a GPU needs int64(tmp) >= 1), so the streamlined loop needs no guard.
-  double l_bn[kFastMaxGpus], l_bp[kFastMaxGpus];
-  float l_ci[kFastMaxGpus];
-  uint32_t l_off[kFastMaxGpus];
+  // Steps 1+2.  GPUs a node does not have (and lanes without a node) keep constants that
+  // evaluate to tmp = 0 + 100*((0*(0+v))/1) = 0: they can never win (a GPU needs
+  // int64(tmp) >= 1), so the streamlined loop needs no guard.
+  // register-resident per-GPU state of the streamlined loop
+  double base_n[kFastMaxGpus], base_p[kFastMaxGpus];
+  float cand_interf[kFastMaxGpus];
+  uint32_t lut_off[kFastMaxGpus];  // byte offsets of the neg (low half) / pos (high half) count in lut
 #pragma unroll
   for (int g = 0; g < kFastMaxGpus; ++g) {
-    l_bn[g] = 0.0;
-    l_bp[g] = 0.0;
-    l_ci[g] = 0.f;
-    l_off[g] = 16u | (16u << 16);
+    base_n[g] = 0.0;
+    base_p[g] = 0.0;
+    cand_interf[g] = 0.f;
+    lut_off[g] = 16u | (16u << 16);
     sm->kkcst[g][0][tid] = make_double2(0.0, 0.0);
     sm->kkcst[g][1][tid] = make_double2(0.0, 0.0);
     sm->zinf[g][tid] = 0;
   }
   __syncthreads();  // lut
-  if (scored) {
-    const float* itab = T.interf + (size_t)(model - 1) * A * A;
+  int nc_score = 0;
+  unsigned nc_sel = kSelNone;
+  // fold one GPU's sums into the per-branch constants (same operations, same order as combine())
+  auto fold = [&](int g, const GpuAcc& acc, float ci, uint32_t* off_out) {
     const double2* lut = sm->lut;
+    const int cn0 = acc.cnt_neg, cp0 = acc.cnt_pos;
+    const int si = score_int(combine_lut(acc.neg_sum, acc.pos_sum, cn0, cp0, lut));
+    if (si > nc_score) {
+      nc_score = si;
+      nc_sel = (unsigned)g;
+    }
+    double kk_n = 1.0, cst_n = 0.0, kk_p = 1.0, cst_p = 0.0;
+    if (cp0 > 0) {  // candidate lands on the negative side, positives exist
+      const double kq = div_count((double)(cn0 + 1), cn0 + 1 + cp0, lut);
+      kk_n = kq;
+      cst_n = __dmul_rn(100.0, div_count(__dmul_rn(__dsub_rn(1.0, kq), acc.pos_sum), cp0, lut));
+    }
+    if (cn0 > 0) {  // candidate lands on the positive side, negatives exist
+      const double kq = div_count((double)cn0, cn0 + cp0 + 1, lut);
+      kk_p = __dsub_rn(1.0, kq);
+      cst_p = __dmul_rn(100.0, div_count(__dmul_rn(kq, acc.neg_sum), cn0, lut));
+    }
+    sm->kkcst[g][0][tid] = make_double2(kk_n, cst_n);
+    sm->kkcst[g][1][tid] = make_double2(kk_p, cst_p);
+    {  // a candidate term of exactly 0 on either side
+      const double tn = __dadd_rn(cst_n, __dmul_rn(100.0, div_count(__dmul_rn(kk_n, __dadd_rn(acc.neg_sum, 0.0)),
+                                                                   cn0 + 1, lut)));
+      const double tp = __dadd_rn(cst_p, __dmul_rn(100.0, div_count(__dmul_rn(kk_p, __dadd_rn(acc.pos_sum, 0.0)),
+                                                                   cp0 + 1, lut)));
+      sm->zinf[g][tid] = (uint16_t)((unsigned)score_int(tn) | ((unsigned)score_int(tp) << 8));
+    }
+    *off_out = (uint32_t)((cn0 + 1) * 16) | ((uint32_t)((cp0 + 1) * 16) << 16);
+    ci_max = fmaxf(ci_max, fabsf(ci));
+    // streamlined domain: finite sums and candidate interference, counts inside the table
+    const bool fin = fabs(acc.neg_sum) <= 1e300 && fabs(acc.pos_sum) <= 1e300 && fabs(cst_n) <= 1e300 &&
+                     fabs(cst_p) <= 1e300 && fabsf(ci) <= 3.0e38f;
+    if (!fin || cn0 + 1 >= kLutSize || cp0 + 1 >= kLutSize) {
+      thr_general = true;
+      *off_out = 16u | (16u << 16);  // keep the table reads in range; the result is discarded
+    }
+  };
+  if (scored) {
     if (model == kModelA30) {
       float v;
       bool ok = conf_lookup(T, app, model, k, &v);
       conf_a30 = ok ? v : 0.0f;  // missing key -> Go zero value, gpu_plugins.go:637
       if (ok) node_flags |= kFlagF6;
     }
-    int nc_score = 0;
-    unsigned nc_sel = kSelNone;
-    const uint32_t* offp = T.gpu_off + (size_t)node * T.max_gpus;
-    uint32_t lo = kTable ? 0u : offp[0];
-    const size_t st_row = (size_t)(app_known ? app : (uint32_t)T.n_apps) * stage.stride + (size_t)node * T.max_gpus;
+    if (kTable) {
+      // sums written by stage_a_kernel, slot-contiguous (coalesced across the tile): all loads
+      // first, then the folds as eight independent chains
+      const size_t st_row = (size_t)(app_known ? app : (uint32_t)T.n_apps) * stage.stride + (size_t)node * T.max_gpus;
+      uint32_t cntr[kFastMaxGpus];
+#pragma unroll
+      for (int g = 0; g < kFastMaxGpus; ++g) {
+        cntr[g] = 0;
+        if (g < k) {
+          base_n[g] = stage.n0[st_row + g];
+          base_p[g] = stage.p0[st_row + g];
+          cand_interf[g] = stage.ci[st_row + g];
+          cntr[g] = stage.cnt[st_row + g];
+        }
+      }
+#pragma unroll
+      for (int g = 0; g < kFastMaxGpus; ++g) {
+        if (g < k) {
+          GpuAcc acc = {base_n[g], base_p[g], (int)(cntr[g] & 0xFFFFu), (int)(cntr[g] >> 16)};
+          fold(g, acc, cand_interf[g], &lut_off[g]);
+        }
+      }
+    } else {
+      // walk the resident lists (a rolled loop: its results go through thread-local arrays)
+      const float* itab = T.interf + (size_t)(model - 1) * A * A;
+      double l_bn[kFastMaxGpus], l_bp[kFastMaxGpus];
+      float l_ci[kFastMaxGpus];
+      uint32_t l_off[kFastMaxGpus];
+#pragma unroll
+      for (int g = 0; g < kFastMaxGpus; ++g) {
+        l_bn[g] = 0.0;
+        l_bp[g] = 0.0;
+        l_ci[g] = 0.f;
+        l_off[g] = 16u | (16u << 16);
+      }
+      const uint32_t* offp = T.gpu_off + (size_t)node * T.max_gpus;
+      uint32_t lo = offp[0];
 #pragma unroll 1
-    for (int g = 0; g < k; ++g) {
-      GpuAcc acc = {0.0, 0.0, 0, 0};
-      float ci = 0.f;
-      if (kTable) {  // written by stage_a_kernel, slot-contiguous: coalesced across the tile
-        acc.neg_sum = stage.n0[st_row + g];
-        acc.pos_sum = stage.p0[st_row + g];
-        ci = stage.ci[st_row + g];
-        const uint32_t c = stage.cnt[st_row + g];
-        acc.cnt_neg = (int)(c & 0xFFFFu);
-        acc.cnt_pos = (int)(c >> 16);
-      } else {
+      for (int g = 0; g < k; ++g) {
+        GpuAcc acc = {0.0, 0.0, 0, 0};
+        float ci = 0.f;
         const uint32_t hi = offp[g + 1];
         for (uint32_t r = lo; r < hi; ++r) {
           const uint32_t ar = T.res_app[r];
@@ -250,59 +313,20 @@ __global__ void __launch_bounds__(kTile, 4) score_fast_kernel(DevTables T, Stage
           }
         }
         lo = hi;
+        fold(g, acc, ci, &l_off[g]);
+        l_bn[g] = acc.neg_sum;
+        l_bp[g] = acc.pos_sum;
+        l_ci[g] = ci;
       }
-      const int cn0 = acc.cnt_neg, cp0 = acc.cnt_pos;
-      const int si = score_int(combine_lut(acc.neg_sum, acc.pos_sum, cn0, cp0, lut));
-      if (si > nc_score) {
-        nc_score = si;
-        nc_sel = (unsigned)g;
-      }
-      // constants of the two branches (same operations, same order as combine())
-      double kk_n = 1.0, cst_n = 0.0, kk_p = 1.0, cst_p = 0.0;
-      if (cp0 > 0) {  // candidate lands on the negative side, positives exist
-        const double kq = div_count((double)(cn0 + 1), cn0 + 1 + cp0, lut);
-        kk_n = kq;
-        cst_n = __dmul_rn(100.0, div_count(__dmul_rn(__dsub_rn(1.0, kq), acc.pos_sum), cp0, lut));
-      }
-      if (cn0 > 0) {  // candidate lands on the positive side, negatives exist
-        const double kq = div_count((double)cn0, cn0 + cp0 + 1, lut);
-        kk_p = __dsub_rn(1.0, kq);
-        cst_p = __dmul_rn(100.0, div_count(__dmul_rn(kq, acc.neg_sum), cn0, lut));
-      }
-      sm->kkcst[g][0][tid] = make_double2(kk_n, cst_n);
-      sm->kkcst[g][1][tid] = make_double2(kk_p, cst_p);
-      {  // a candidate term of exactly 0 on either side
-        const double tn = __dadd_rn(cst_n, __dmul_rn(100.0, div_count(__dmul_rn(kk_n, __dadd_rn(acc.neg_sum, 0.0)),
-                                                                     cn0 + 1, lut)));
-        const double tp = __dadd_rn(cst_p, __dmul_rn(100.0, div_count(__dmul_rn(kk_p, __dadd_rn(acc.pos_sum, 0.0)),
-                                                                     cp0 + 1, lut)));
-        sm->zinf[g][tid] = (uint16_t)((unsigned)score_int(tn) | ((unsigned)score_int(tp) << 8));
-      }
-      l_bn[g] = acc.neg_sum;
-      l_bp[g] = acc.pos_sum;
-      l_ci[g] = ci;
-      l_off[g] = (uint32_t)((cn0 + 1) * 16) | ((uint32_t)((cp0 + 1) * 16) << 16);
-      ci_max = fmaxf(ci_max, fabsf(ci));
-      // streamlined domain: finite sums and candidate interference, counts inside the table
-      const bool fin = fabs(acc.neg_sum) <= 1e300 && fabs(acc.pos_sum) <= 1e300 && fabs(cst_n) <= 1e300 &&
-                       fabs(cst_p) <= 1e300 && fabsf(ci) <= 3.0e38f;
-      if (!fin || cn0 + 1 >= kLutSize || cp0 + 1 >= kLutSize) {
-        thr_general = true;
-        l_off[g] = 16u | (16u << 16);  // keep the table reads in range; the result is discarded
+#pragma unroll
+      for (int g = 0; g < kFastMaxGpus; ++g) {
+        base_n[g] = l_bn[g];
+        base_p[g] = l_bp[g];
+        cand_interf[g] = l_ci[g];
+        lut_off[g] = l_off[g];
       }
     }
     nocand = (nc_score << 8) | (int)nc_sel;
-  }
-  // register-resident per-GPU state of the streamlined loop
-  double base_n[kFastMaxGpus], base_p[kFastMaxGpus];
-  float cand_interf[kFastMaxGpus];
-  uint32_t lut_off[kFastMaxGpus];  // byte offsets of the neg (low half) / pos (high half) count in lut
-#pragma unroll
-  for (int g = 0; g < kFastMaxGpus; ++g) {
-    base_n[g] = l_bn[g];
-    base_p[g] = l_bp[g];
-    cand_interf[g] = l_ci[g];
-    lut_off[g] = l_off[g];
   }
 
   const int warp = tid >> 5;

@@ -48,7 +48,13 @@ struct ChunkDesc {
   uint32_t pad;
 };
 
-constexpr int kChunk = 256;      // pods per work item (one app); staged kStage at a time
+#ifndef GS_KCHUNK
+#define GS_KCHUNK 256
+#endif
+#ifndef GS_MIN_CTAS
+#define GS_MIN_CTAS 4
+#endif
+constexpr int kChunk = GS_KCHUNK; // pods per work item (one app); staged kStage at a time
 constexpr int kStage = 128;      // pods staged in shared memory at once (= kTile)
 constexpr int kFastMaxGpus = 8;  // GPUs per node the register-resident kernel covers
 constexpr int kTile = 128;       // nodes per CTA
