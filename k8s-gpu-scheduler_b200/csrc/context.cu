@@ -1,5 +1,6 @@
 // context.cu — the C ABI of include/gpusched.h: context, table uploads, scoring entry
 // points.  Host logic only; kernels live in score_kernels.cu.
+#include <algorithm>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -113,6 +114,28 @@ int Ctx::ensure_scratch(int n_pods) {
   return GS_OK;
 }
 
+PodScratch Ctx::scratch_view(int n_pods) const {
+  PodScratch sc;
+  sc.counts = (uint32_t*)sc_counts.p;
+  sc.cursor = (uint32_t*)sc_cursor.p;
+  sc.n_chunks = (uint32_t*)sc_nchunks.p;
+  sc.chunks = (ChunkDesc*)sc_chunks.p;
+  sc.sorted = (PodRec*)sc_sorted.p;
+  sc.max_chunks = max_chunks_for(n_pods, n_apps);
+  sc.stage = StageA{nullptr, nullptr, nullptr, nullptr, 0};
+  const size_t entries = (size_t)(n_apps + 1) * (size_t)n_nodes * (size_t)max_gpus;
+  const size_t e8 = (entries + 31) / 32 * 32;  // keep every array 256-byte aligned
+  if (entries * 24 <= stage_budget && e8 * 24 <= sc_stage.cap) {
+    char* base = (char*)sc_stage.p;
+    sc.stage.n0 = (double*)base;
+    sc.stage.p0 = (double*)(base + e8 * 8);
+    sc.stage.ci = (float*)(base + e8 * 16);
+    sc.stage.cnt = (uint32_t*)(base + e8 * 20);
+    sc.stage.stride = (size_t)n_nodes * (size_t)max_gpus;
+  }
+  return sc;
+}
+
 }  // namespace gs
 
 using gs::Ctx;
@@ -160,9 +183,12 @@ void gs_destroy(gs_ctx* c) {
     cudaStreamSynchronize(c->stream);
     gs::DevBuf* bufs[] = {&c->node_model, &c->node_ngpu, &c->gpu_off,   &c->res_app,   &c->res_slo, &c->conf,
                           &c->interf,     &c->interf_t,  &c->sc_stage,  &c->col_of,    &c->res_rec,   &c->sc_counts, &c->sc_cursor,
-                          &c->sc_nchunks, &c->sc_chunks, &c->sc_sorted, &c->b_pod_app, &c->b_pod_slo,
+                          &c->sc_nchunks, &c->sc_chunks, &c->sc_sorted, &c->sc_counts_all, &c->b_pod_app, &c->b_pod_slo,
                           &c->b_pod_self, &c->b_score,   &c->b_sel,     &c->b_extrema, &c->b_best,  &c->b_misc};
     for (gs::DevBuf* b : bufs) c->release(*b);
+    for (auto& ev : c->ev_chunk)
+      if (ev) cudaEventDestroy(ev);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->ev_begin) cudaEventDestroy(c->ev_begin);
     if (c->ev_end) cudaEventDestroy(c->ev_end);
     cudaStreamDestroy(c->stream);
@@ -265,28 +291,7 @@ static int score_raw_locked(gs_ctx* c, const uint32_t* d_app, const float* d_slo
     c->ev_valid = false;
   }
   if (fast) {
-    gs::PodScratch sc;
-    sc.counts = (uint32_t*)c->sc_counts.p;
-    sc.cursor = (uint32_t*)c->sc_cursor.p;
-    sc.n_chunks = (uint32_t*)c->sc_nchunks.p;
-    sc.chunks = (gs::ChunkDesc*)c->sc_chunks.p;
-    sc.sorted = (gs::PodRec*)c->sc_sorted.p;
-    sc.max_chunks = gs::max_chunks_for(P, c->n_apps);
-    sc.stage = gs::StageA{nullptr, nullptr, nullptr, nullptr, 0};
-    {
-      const size_t entries = (size_t)(c->n_apps + 1) * (size_t)c->n_nodes * (size_t)c->max_gpus;
-      if (entries * 24 <= c->stage_budget && c->sc_stage.cap >= entries * 24) {
-        const size_t e8 = (entries + 31) / 32 * 32;  // keep every array 256-byte aligned
-        char* base = (char*)c->sc_stage.p;
-        if (e8 * 24 <= c->sc_stage.cap) {
-          sc.stage.n0 = (double*)base;
-          sc.stage.p0 = (double*)(base + e8 * 8);
-          sc.stage.ci = (float*)(base + e8 * 16);
-          sc.stage.cnt = (uint32_t*)(base + e8 * 20);
-          sc.stage.stride = (size_t)c->n_nodes * (size_t)c->max_gpus;
-        }
-      }
-    }
+    gs::PodScratch sc = c->scratch_view(P);
     e = gs::launch_score_fast(T, d_app, d_slo, P, sc, d_score, d_sel, (unsigned long long*)d_hi,
                               (unsigned long long*)d_neg, s, c->profiling ? c->ev_begin : nullptr);
   } else {
@@ -362,12 +367,69 @@ int gs_score_batch(gs_ctx* c, const uint32_t* pod_app, const float* pod_slo, con
   if ((rc = c->reserve(c->b_best, sizeof(int32_t) * (size_t)P, "best"))) return rc;
   uint64_t* d_hi = (uint64_t*)c->b_extrema.p;
   uint64_t* d_neg = d_hi + P;
+  const int rescale = (flags & GS_SCORE_NORMALIZE) ? 1 : 0;
+
+  // Large batches through the restructured path: score the pods in a few slices and copy each
+  // slice's rows to the host on a second stream while the next slice is being scored (the
+  // results are 2 bytes per (pod,node): the PCIe copy, not the arithmetic, bounds this call).
+  const bool fast = !(flags & GS_SCORE_DIRECT) && !pod_self && c->max_gpus <= gs::kFastMaxGpus;
+  int n_slices = 1;
+  if (fast && N && out_score && out_sel && P >= 8192 && PN * 2 >= ((size_t)64 << 20)) {
+    n_slices = (int)std::min<size_t>(6, std::max<size_t>(2, PN * 2 / ((size_t)80 << 20)));  // measured: 6 slices best at 500 MB
+    if (const char* ov = getenv("GS_SLICES")) n_slices = std::max(1, std::min(8, atoi(ov)));
+  }
+  if (n_slices > 1) {
+    if ((rc = c->ensure_prepared())) return rc;
+    if ((rc = c->ensure_scratch(P))) return rc;
+    if ((rc = c->reserve(c->sc_counts_all, sizeof(uint32_t) * (size_t)(c->n_apps + 2), "bucket counts (batch)"))) return rc;
+    if (!c->copy_stream) {
+      GS_CUDA(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+      for (auto& ev : c->ev_chunk) GS_CUDA(c, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    }
+    gs::DevTables T = c->tables();
+    const uint32_t* d_app = (const uint32_t*)c->b_pod_app.p;
+    const float* d_slo = (const float*)c->b_pod_slo.p;
+    uint8_t* d_score = (uint8_t*)c->b_score.p;
+    uint8_t* d_sel = (uint8_t*)c->b_sel.p;
+    int32_t* d_best = (int32_t*)c->b_best.p;
+    GS_CUDA(c, cudaMemsetAsync(d_hi, 0, sizeof(uint64_t) * 2 * (size_t)P, s));
+    // the residents' sums once, for every app bucket present anywhere in the batch
+    gs::PodScratch whole = c->scratch_view(P);
+    cudaError_t e = gs::launch_pod_histogram(d_app, P, c->n_apps, (uint32_t*)c->sc_counts_all.p, s);
+    if (e == cudaSuccess) e = gs::launch_stage_a(T, (const uint32_t*)c->sc_counts_all.p, whole.stage, s);
+    if (e != cudaSuccess) return c->cuda_fail(e, "stage_a (batch)");
+    const int per = (P + n_slices - 1) / n_slices;
+    for (int k = 0; k < n_slices; ++k) {
+      const int p0 = k * per, np = std::min(per, P - p0);
+      if (np <= 0) break;
+      gs::PodScratch sc = c->scratch_view(np);
+      const size_t row0 = (size_t)p0 * N;
+      e = gs::launch_pod_bucketing(T, d_app + p0, d_slo + p0, np, sc, s);
+      if (e == cudaSuccess)
+        e = gs::launch_score_main(T, sc, d_score + row0, d_sel + row0, (unsigned long long*)(d_hi + p0),
+                                  (unsigned long long*)(d_neg + p0), s);
+      if (e == cudaSuccess)
+        e = gs::launch_normalize(np, c->n_nodes, rescale, d_score + row0, (const unsigned long long*)(d_hi + p0),
+                                 (const unsigned long long*)(d_neg + p0), d_best + p0, s);
+      if (e != cudaSuccess) return c->cuda_fail(e, "score slice");
+      GS_CUDA(c, cudaEventRecord(c->ev_chunk[k], s));
+      GS_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_chunk[k], 0));
+      GS_CUDA(c, cudaMemcpyAsync(out_score + row0, d_score + row0, (size_t)np * N, cudaMemcpyDeviceToHost, c->copy_stream));
+      GS_CUDA(c, cudaMemcpyAsync(out_sel + row0, d_sel + row0, (size_t)np * N, cudaMemcpyDeviceToHost, c->copy_stream));
+    }
+    if (out_best)
+      GS_CUDA(c, cudaMemcpyAsync(out_best, d_best, sizeof(int32_t) * (size_t)P, cudaMemcpyDeviceToHost, s));
+    GS_CUDA(c, cudaStreamSynchronize(s));
+    GS_CUDA(c, cudaStreamSynchronize(c->copy_stream));
+    return GS_OK;
+  }
+
   rc = score_raw_locked(c, (const uint32_t*)c->b_pod_app.p, (const float*)c->b_pod_slo.p,
                         pod_self ? (const int32_t*)c->b_pod_self.p : nullptr, P, flags, (uint8_t*)c->b_score.p,
                         (uint8_t*)c->b_sel.p, d_hi, d_neg, s);
   if (rc) return rc;
   if (N) {
-    cudaError_t e = gs::launch_normalize(P, c->n_nodes, (flags & GS_SCORE_NORMALIZE) ? 1 : 0, (uint8_t*)c->b_score.p,
+    cudaError_t e = gs::launch_normalize(P, c->n_nodes, rescale, (uint8_t*)c->b_score.p,
                                          (const unsigned long long*)d_hi, (const unsigned long long*)d_neg,
                                          (int32_t*)c->b_best.p, s);
     if (e != cudaSuccess) return c->cuda_fail(e, "normalize");

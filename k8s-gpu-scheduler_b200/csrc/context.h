@@ -32,7 +32,11 @@ struct Ctx {
   bool prep_dirty = true;
   DevBuf res_rec;
   // scratch of the restructured scoring path
-  DevBuf sc_counts, sc_cursor, sc_nchunks, sc_chunks, sc_sorted, sc_stage;
+  DevBuf sc_counts, sc_cursor, sc_nchunks, sc_chunks, sc_sorted, sc_stage, sc_counts_all;
+  // host-buffer entry point: second stream + events to overlap the device->host copies with compute
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_chunk[8] = {};
+  cudaEvent_t ev_copy_done = nullptr;
   size_t stage_budget = (size_t)4 << 30;  // largest per-batch residents-sum table (GS_STAGE_TABLE_MB)
   // staging for the host-pointer entry points
   DevBuf b_pod_app, b_pod_slo, b_pod_self, b_score, b_sel, b_extrema, b_best, b_misc;
@@ -50,6 +54,7 @@ struct Ctx {
   DevTables tables() const;
   int ensure_prepared();
   int ensure_scratch(int n_pods);
+  PodScratch scratch_view(int n_pods) const;
 };
 
 cudaError_t launch_normalize_i64(long long* scores, int n, cudaStream_t s);

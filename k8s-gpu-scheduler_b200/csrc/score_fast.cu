@@ -428,6 +428,28 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
   }
 }
 
+// stage A for every app bucket that `counts` (pods per bucket) marks as present
+cudaError_t launch_stage_a(const DevTables& T, const uint32_t* counts, const StageA& stage, cudaStream_t s) {
+  const int slots = T.n_nodes * T.max_gpus;
+  if (slots == 0 || !stage.n0) return cudaSuccess;
+  dim3 ga((unsigned)((slots + kStageTile - 1) / kStageTile), (unsigned)((T.n_apps + 1 + kStageTile - 1) / kStageTile));
+  stage_a_kernel<<<ga, 256, 0, s>>>(T, counts, stage);
+  return cudaGetLastError();
+}
+
+// the scoring kernel over the work items that launch_pod_bucketing left in `sc`
+cudaError_t launch_score_main(const DevTables& T, const PodScratch& sc, uint8_t* score, uint8_t* sel,
+                              unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s) {
+  dim3 grid(sc.max_chunks, (unsigned)((T.n_nodes + kTile - 1) / kTile));
+  if (sc.stage.n0)
+    score_fast_kernel<true><<<grid, kTile, 0, s>>>(T, sc.stage, sc.sorted, sc.chunks, sc.n_chunks, score, sel, hi_arg,
+                                                   neg_lo);
+  else
+    score_fast_kernel<false><<<grid, kTile, 0, s>>>(T, sc.stage, sc.sorted, sc.chunks, sc.n_chunks, score, sel,
+                                                    hi_arg, neg_lo);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_score_fast(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
                               const PodScratch& sc, uint8_t* score, uint8_t* sel, unsigned long long* hi_arg,
                               unsigned long long* neg_lo, cudaStream_t s, cudaEvent_t before_main) {
@@ -435,18 +457,8 @@ cudaError_t launch_score_fast(const DevTables& T, const uint32_t* pod_app, const
   cudaError_t e = launch_pod_bucketing(T, pod_app, pod_slo, n_pods, sc, s);
   if (e != cudaSuccess) return e;
   if (before_main && (e = cudaEventRecord(before_main, s)) != cudaSuccess) return e;
-  dim3 grid(sc.max_chunks, (unsigned)((T.n_nodes + kTile - 1) / kTile));
-  if (sc.stage.n0) {
-    const int slots = T.n_nodes * T.max_gpus;
-    dim3 ga((unsigned)((slots + kStageTile - 1) / kStageTile), (unsigned)((T.n_apps + 1 + kStageTile - 1) / kStageTile));
-    stage_a_kernel<<<ga, 256, 0, s>>>(T, sc.counts, sc.stage);
-    score_fast_kernel<true><<<grid, kTile, 0, s>>>(T, sc.stage, sc.sorted, sc.chunks, sc.n_chunks, score, sel, hi_arg,
-                                                   neg_lo);
-  } else {
-    score_fast_kernel<false><<<grid, kTile, 0, s>>>(T, sc.stage, sc.sorted, sc.chunks, sc.n_chunks, score, sel,
-                                                    hi_arg, neg_lo);
-  }
-  return cudaGetLastError();
+  if ((e = launch_stage_a(T, sc.counts, sc.stage, s)) != cudaSuccess) return e;
+  return launch_score_main(T, sc, score, sel, hi_arg, neg_lo, s);
 }
 
 // ------------------------------------------------------------------ self test --------

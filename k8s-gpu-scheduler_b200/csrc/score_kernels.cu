@@ -213,6 +213,14 @@ __global__ void pod_scatter_kernel(DevTables T, const uint32_t* __restrict__ pod
   sorted[pos] = rec;
 }
 
+// pods per app bucket (counts must hold n_apps + 2 words; zeroed here)
+cudaError_t launch_pod_histogram(const uint32_t* pod_app, int n_pods, int n_apps, uint32_t* counts, cudaStream_t s) {
+  cudaError_t e = cudaMemsetAsync(counts, 0, sizeof(uint32_t) * (size_t)(n_apps + 2), s);
+  if (e != cudaSuccess) return e;
+  pod_hist_kernel<<<(n_pods + 255) / 256, 256, 0, s>>>(pod_app, n_pods, n_apps, counts);
+  return cudaGetLastError();
+}
+
 // Bucket the pods by app: histogram -> scan (cursors + work items) -> scatter.
 cudaError_t launch_pod_bucketing(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
                                  const PodScratch& sc, cudaStream_t s) {

@@ -97,6 +97,10 @@ cudaError_t launch_score_fast(const DevTables& T, const uint32_t* pod_app, const
 cudaError_t launch_transpose_interf(const float* interf, float* interf_t, int n_apps, cudaStream_t s);
 cudaError_t launch_selftest(unsigned long long seed, int blocks, int iters, unsigned long long* d_mismatches,
                             cudaStream_t s);
+cudaError_t launch_pod_histogram(const uint32_t* pod_app, int n_pods, int n_apps, uint32_t* counts, cudaStream_t s);
+cudaError_t launch_stage_a(const DevTables& T, const uint32_t* counts, const StageA& stage, cudaStream_t s);
+cudaError_t launch_score_main(const DevTables& T, const PodScratch& sc, uint8_t* score, uint8_t* sel,
+                              unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s);
 cudaError_t launch_normalize(int n_pods, int n_nodes, int rescale, uint8_t* score,
                              const unsigned long long* hi_arg, const unsigned long long* neg_lo,
                              int32_t* best, cudaStream_t s);

@@ -227,3 +227,20 @@ def test_without_residents_sum_table(pkg, oracle_mod, synth, monkeypatch):
             _check(s, oracle_mod, preds, cluster, pods)
     finally:
         s.close()
+
+
+def test_sliced_host_path_large_batch(sched, oracle_mod, synth):
+    """gs_score_batch slices large batches (>= 8192 pods, >= 64 MB of results) and overlaps the
+    device->host copies with the scoring of the next slice: same bytes as the one-shot op-for-op
+    kernel, and sampled rows match the oracle."""
+    preds, cluster, pods = synth.make_workload(9000, 4000, gpus_per_node=8, n_apps=300, p_unknown_app=0.01)
+    sched.upload_predictions(preds)
+    sched.upload_cluster(cluster)
+    for normalize in (False, True):
+        fast = sched.score_batch(pods, normalize=normalize)
+        slow = sched.score_batch(pods, normalize=normalize, direct=True)
+        for a, b, name in zip(fast, slow, ("score", "sel", "best")):
+            assert np.array_equal(a, b), name
+    rows = np.random.default_rng(3).choice(9000, size=24, replace=False)
+    w = oracle_mod.Oracle(preds, cluster).score_batch(synth.Pods(app=pods.app[rows], slo=pods.slo[rows]), normalize=True)
+    assert np.array_equal(w[0], fast[0][rows]) and np.array_equal(w[1], fast[1][rows]) and np.array_equal(w[2], fast[2][rows])
