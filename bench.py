@@ -306,13 +306,18 @@ def main():
                        "distinct_app_slo_classes": pkg.synth.distinct_classes(pods), "seed": hex(pkg.synth.SEED),
                        "l2": "flushed between timed iterations (256 MB memset, untimed); outputs 500 MB > L2",
                        "timing": "CUDA events per step on the launching stream, summed; max over ranks"},
-            "gpu_launches": 5 * args.steps,
+            "gpu_launches": 6 * args.steps,  # hist, scan, scatter, stage_a, score_fast, normalize
             "wall_ms_per_step_incl_flush": t_wall * 1e3 / args.steps,
             "clocks": clocks.summary(),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "peak_kind": peak_kind, "kernel": "score_fast_kernel",
                          "kernel_ms": kernel_ms, "algorithmic_bytes": abytes,
-                         "note": "kernel is FP64/FP32-ALU bound, not HBM bound (see DESIGN.md)"},
+                         "note": "kernel is FP64-pipe / issue bound, not HBM bound (see DESIGN.md 4.2)"},
+            # the roofline that actually binds: 16 float64 operations per (pod,node,GPU) against the
+            # measured DFMA rate of this pool's B200 (profiles/r1/ub_alu_b200.txt: 17.19 Tlane-op/s)
+            "roofline_fp64": {"bound": "fp64_pipe", "achieved": 16.0 * GPUS_PER_NODE * P * NL / (kernel_ms * 1e-3) / 1e12,
+                              "peak": 17.19, "unit": "Tlane-op/s",
+                              "frac": 16.0 * GPUS_PER_NODE * P * NL / (kernel_ms * 1e-3) / 1e12 / 17.19},
         }
         if e2e:
             line["e2e"] = e2e
