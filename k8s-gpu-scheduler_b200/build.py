@@ -72,7 +72,7 @@ def build(force: bool = False, verbose: bool = False, tag: str = "", defines=())
         if p.returncode != 0:
             raise RuntimeError(f"nvcc failed on {src}:\n{out}")
     cmd = [_nvcc(), "-shared", "-ccbin", "/usr/bin/g++", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB, *objs,
-           "-Xcompiler", "-fPIC", "-cudart", "static"]
+           "-Xcompiler", "-fPIC", "-cudart", "static", "-ldl"]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}")

@@ -13,6 +13,8 @@
 //     sse = y^T y - 2 coef~.b~ + sum(coef~^2 s);
 //   * rows where j is missing get x.coef + intercept (predict_kernel).
 // Everything is float64; parity bar: 1e-5 relative against Imputer.predict (tests/golden).
+#include <dlfcn.h>
+
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -20,12 +22,15 @@
 #include <new>
 #include <vector>
 
+#include <cusolverDn.h>  // types and prototypes only: the library is dlopen'ed when a large fit needs it
+
 #include "../../include/gpusched.h"
 #include "context.h"
 
 namespace gs {
 
-constexpr int kMaxFeatures = 256;  // d - 1 <= 255: the one-CTA Jacobi's range
+constexpr int kMaxFeatures = 1024; // d - 1 <= 1023 (shared arrays of the evidence iteration)
+constexpr int kJacobiMax = 64;     // d - 1 <= 64: hand-written one-CTA Jacobi; beyond: cuSOLVER's syevd
 constexpr int kGramTile = 32;
 constexpr int kRounds = 10;        // IterativeImputer(max_iter=10), recommender.py:16
 constexpr double kRoundTol = 1e-3; // IterativeImputer tol
@@ -177,8 +182,8 @@ __global__ void gram_reduce_kernel(const double* __restrict__ partial, int d, in
 __global__ void __launch_bounds__(1024) jacobi_eig_kernel(const double* __restrict__ G, int d, int j,
                                                          double* __restrict__ A, double* __restrict__ V,
                                                          double* __restrict__ evals, int* __restrict__ sweeps_out) {
-  __shared__ double s_c[kMaxFeatures / 2 + 1], s_s[kMaxFeatures / 2 + 1];
-  __shared__ int s_p[kMaxFeatures / 2 + 1], s_q[kMaxFeatures / 2 + 1];
+  __shared__ double s_c[kJacobiMax / 2 + 1], s_s[kJacobiMax / 2 + 1];
+  __shared__ int s_p[kJacobiMax / 2 + 1], s_q[kJacobiMax / 2 + 1];
   __shared__ double s_red[1024];
   __shared__ double s_off, s_norm;
   const int m = d - 1;
@@ -194,6 +199,7 @@ __global__ void __launch_bounds__(1024) jacobi_eig_kernel(const double* __restri
   const int M = (m + 1) & ~1;  // players, even
   const int half = M / 2;
   int sweep = 0;
+  bool last = false;
   for (; sweep < 60; ++sweep) {
     // off-diagonal and total Frobenius norms
     double off = 0.0, tot = 0.0;
@@ -218,7 +224,10 @@ __global__ void __launch_bounds__(1024) jacobi_eig_kernel(const double* __restri
     }
     if (tid == 0) s_norm = s_red[0];
     __syncthreads();
-    if (s_off <= 1e-30 * s_norm || s_norm == 0.0) break;  // off/||A|| <= 1e-15
+    // converged at off/||A|| <= 1e-15; Jacobi converges quadratically, so once a sweep starts
+    // below 1e-9 it is the last one needed (it lands on the rounding floor)
+    if (last || s_off <= 1e-30 * s_norm || s_norm == 0.0) break;
+    if (s_off <= 1e-18 * s_norm) last = true;
     for (int step = 0; step < M - 1; ++step) {
       // pairs of this step
       if (tid < half) {
@@ -287,6 +296,15 @@ __global__ void __launch_bounds__(1024) jacobi_eig_kernel(const double* __restri
   if (tid == 0) *sweeps_out = sweep;
 }
 
+// A = G without row/column j (input of the library eigensolver)
+__global__ void extract_minor_kernel(const double* __restrict__ G, int d, int j, double* __restrict__ A) {
+  const int m = d - 1;
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= m * m) return;
+  int a = e / m, b = e % m;
+  A[e] = G[(size_t)(a < j ? a : a + 1) * d + (b < j ? b : b + 1)];
+}
+
 // ---- BayesianRidge's evidence iteration in the eigenbasis, one CTA ----
 __device__ __forceinline__ double block_sum(double v, double* s_red) {
   const int tid = threadIdx.x;
@@ -304,25 +322,27 @@ __device__ __forceinline__ double block_sum(double v, double* s_red) {
 
 __global__ void __launch_bounds__(256) bayes_ridge_kernel(const double* __restrict__ G, const double* __restrict__ mu,
                                                          const int* __restrict__ n_obs_p, int d, int j,
-                                                         const double* __restrict__ V, const double* __restrict__ evals,
+                                                         const double* __restrict__ V, int v_si, int v_sk,
+                                                         const double* __restrict__ evals,
                                                          double* __restrict__ coef_out, double* __restrict__ intercept_out,
                                                          int* __restrict__ iters_out) {
   __shared__ double s_red[256];
-  __shared__ double s_b[kMaxFeatures], s_bt[kMaxFeatures], s_ct[kMaxFeatures], s_coef[kMaxFeatures],
-      s_old[kMaxFeatures], s_ev[kMaxFeatures];
+  extern __shared__ double s_dyn[];  // 6 vectors of m doubles
   const int m = d - 1, tid = threadIdx.x, nt = blockDim.x;
+  double *s_b = s_dyn, *s_bt = s_dyn + m, *s_ct = s_dyn + 2 * m, *s_coef = s_dyn + 3 * m, *s_old = s_dyn + 4 * m,
+         *s_ev = s_dyn + 5 * m;
   const double n = (double)*n_obs_p;
   for (int i = tid; i < m; i += nt) {
     const int gi = i < j ? i : i + 1;
     s_b[i] = G[(size_t)gi * d + j];  // X^T y
-    s_ev[i] = evals[i];
+    s_ev[i] = fmax(evals[i], 0.0);  // S^2 >= 0
     s_old[i] = 0.0;
   }
   __syncthreads();
   const double yy = G[(size_t)j * d + j];
   for (int k = tid; k < m; k += nt) {  // b~ = V^T b
     double acc = 0.0;
-    for (int i = 0; i < m; ++i) acc += V[(size_t)i * m + k] * s_b[i];
+    for (int i = 0; i < m; ++i) acc += V[(size_t)i * v_si + (size_t)k * v_sk] * s_b[i];
     s_bt[k] = acc;
   }
   __syncthreads();
@@ -336,7 +356,7 @@ __global__ void __launch_bounds__(256) bayes_ridge_kernel(const double* __restri
     __syncthreads();
     for (int i = tid; i < m; i += nt) {  // coef = V coef~
       double acc = 0.0;
-      for (int k = 0; k < m; ++k) acc += V[(size_t)i * m + k] * s_ct[k];
+      for (int k = 0; k < m; ++k) acc += V[(size_t)i * v_si + (size_t)k * v_sk] * s_ct[k];
       s_coef[i] = acc;
     }
     double t1 = 0.0, t2 = 0.0;
@@ -397,19 +417,26 @@ __global__ void __launch_bounds__(256) predict_kernel(double* __restrict__ Xt, c
   if (lane == 0) Xt[(size_t)r * d + j] = acc + *intercept;
 }
 
-__global__ void __launch_bounds__(256) max_abs_diff_kernel(const double* __restrict__ a, const double* __restrict__ b,
-                                                          size_t total, double* __restrict__ out) {
-  __shared__ double s_red[256];
+// np.linalg.norm(Xt - Xt_prev, ord=inf, axis=None) of a 2-D array = the largest row sum of
+// absolute differences (_iterative.py:853).  One warp per row; out[block] = max over its rows.
+__global__ void __launch_bounds__(256) max_row_diff_kernel(const double* __restrict__ a, const double* __restrict__ b,
+                                                          int n, int d, double* __restrict__ out) {
+  __shared__ double s_red[8];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   double mx = 0.0;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x)
-    mx = fmax(mx, fabs(a[i] - b[i]));
-  s_red[threadIdx.x] = mx;
-  __syncthreads();
-  for (int s = 128; s > 0; s >>= 1) {
-    if (threadIdx.x < s) s_red[threadIdx.x] = fmax(s_red[threadIdx.x], s_red[threadIdx.x + s]);
-    __syncthreads();
+  for (int r = blockIdx.x * 8 + warp; r < n; r += gridDim.x * 8) {
+    double sum = 0.0;
+    for (int c = lane; c < d; c += 32) sum += fabs(a[(size_t)r * d + c] - b[(size_t)r * d + c]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, o);
+    mx = fmax(mx, sum);
   }
-  if (threadIdx.x == 0) out[blockIdx.x] = s_red[0];
+  if (lane == 0) s_red[warp] = mx;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < 8; ++w) mx = fmax(mx, s_red[w]);
+    out[blockIdx.x] = mx;
+  }
 }
 
 // transform: one warp per row, the row in shared memory, every stored step replayed in order
@@ -462,6 +489,37 @@ struct gs_model {
 
 namespace {
 
+// cuSOLVER's symmetric eigensolver for the larger Gram matrices, bound at run time so that the
+// library loads (and everything else works) without it.
+struct Cusolver {
+  void* lib = nullptr;
+  cusolverDnHandle_t h = nullptr;
+  decltype(&cusolverDnCreate) create = nullptr;
+  decltype(&cusolverDnDestroy) destroy = nullptr;
+  decltype(&cusolverDnSetStream) set_stream = nullptr;
+  decltype(&cusolverDnDsyevd_bufferSize) bufsize = nullptr;
+  decltype(&cusolverDnDsyevd) syevd = nullptr;
+  bool open(cudaStream_t s) {
+    const char* names[] = {"libcusolver.so.11", "/usr/local/cuda/lib64/libcusolver.so.11", "libcusolver.so.12",
+                           "libcusolver.so"};
+    for (const char* n : names)
+      if ((lib = dlopen(n, RTLD_NOW | RTLD_LOCAL))) break;
+    if (!lib) return false;
+    create = (decltype(create))dlsym(lib, "cusolverDnCreate");
+    destroy = (decltype(destroy))dlsym(lib, "cusolverDnDestroy");
+    set_stream = (decltype(set_stream))dlsym(lib, "cusolverDnSetStream");
+    bufsize = (decltype(bufsize))dlsym(lib, "cusolverDnDsyevd_bufferSize");
+    syevd = (decltype(syevd))dlsym(lib, "cusolverDnDsyevd");
+    if (!create || !destroy || !set_stream || !bufsize || !syevd) return false;
+    if (create(&h) != CUSOLVER_STATUS_SUCCESS) return false;
+    return set_stream(h, s) == CUSOLVER_STATUS_SUCCESS;
+  }
+  ~Cusolver() {
+    if (h && destroy) destroy(h);
+    // the library stays loaded for the life of the process
+  }
+};
+
 struct DevMem {
   std::vector<void*> ptrs;
   ~DevMem() {
@@ -494,8 +552,7 @@ int gs_complete_fit(gs_ctx* c, const double* X, int32_t n, int32_t d, gs_model**
   std::lock_guard<std::mutex> lk(c->mu);
   if (!X || !out || n < 1 || d < 1) return c->fail(GS_ERR_INVALID, "gs_complete_fit: null pointer or empty matrix");
   if (d - 1 >= kMaxFeatures)
-    return c->fail(GS_ERR_UNSUPPORTED, "gs_complete_fit: %d columns; this build's eigen-solver covers at most %d", d,
-                   kMaxFeatures);
+    return c->fail(GS_ERR_UNSUPPORTED, "gs_complete_fit: %d columns; this build covers at most %d", d, kMaxFeatures);
   CK(cudaSetDevice(c->device));
   cudaStream_t s = c->stream;
   const size_t total = (size_t)n * d;
@@ -531,6 +588,27 @@ int gs_complete_fit(gs_ctx* c, const double* X, int32_t n, int32_t d, gs_model**
   CK(mem.alloc(&dSweeps, max_steps));
   CK(mem.alloc(&dDiff, 256));
   CK(cudaMemcpyAsync(dX, X, sizeof(double) * total, cudaMemcpyHostToDevice, s));
+  // eigen-solver: hand-written Jacobi up to kJacobiMax, cuSOLVER's syevd beyond
+  const int mm = d - 1;
+  const bool use_lib = mm > kJacobiMax;
+  Cusolver cus;
+  double* dWork = nullptr;
+  int* dInfo = nullptr;
+  int lwork = 0;
+  if (use_lib) {
+    if (!cus.open(s))
+      return c->fail(GS_ERR_UNSUPPORTED, "gs_complete_fit: %d columns need cuSOLVER (libcusolver.so.11), which could "
+                     "not be loaded: %s", d, dlerror() ? dlerror() : "symbol or handle error");
+    if (cus.bufsize(cus.h, CUSOLVER_EIG_MODE_VECTOR, CUBLAS_FILL_MODE_LOWER, mm, dA, mm, dEv, &lwork) !=
+        CUSOLVER_STATUS_SUCCESS)
+      return c->fail(GS_ERR_CUDA, "cusolverDnDsyevd_bufferSize failed");
+    CK(mem.alloc(&dWork, (size_t)lwork));
+    CK(mem.alloc(&dInfo, max_steps));
+    CK(cudaMemsetAsync(dInfo, 0, sizeof(int) * max_steps, s));
+    CK(cudaMemsetAsync(dSweeps, 0, sizeof(int) * max_steps, s));
+  }
+  const size_t bayes_smem = sizeof(double) * 6 * (size_t)(mm > 0 ? mm : 1);
+  CK(cudaFuncSetAttribute(bayes_ridge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bayes_smem));
 
   gs_model* m = new (std::nothrow) gs_model();
   if (!m) return c->fail(GS_ERR_NOMEM, "gs_complete_fit: out of host memory");
@@ -581,16 +659,28 @@ int gs_complete_fit(gs_ctx* c, const double* X, int32_t n, int32_t d, gs_model**
       obs_means_kernel<<<d, 256, 0, s>>>(dXt, dMask, n, d, j, dMu, dNobs);
       gram_partial_kernel<<<dim3(tiles, tiles, parts), 256, 0, s>>>(dXt, dMask, n, d, j, dMu, rows_per_part, dPartial);
       gram_reduce_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dPartial, d, parts, dG);
-      int jt = 32;
-      while (jt < 1024 && jt < (d - 1) * (d - 1) / 4) jt <<= 1;
-      jacobi_eig_kernel<<<1, jt, 0, s>>>(dG, d, j, dA, dV, dEv, dSweeps + step);
-      bayes_ridge_kernel<<<1, 256, 0, s>>>(dG, dMu, dNobs, d, j, dV, dEv, dCoef + (size_t)step * (d - 1), dIcpt + step,
-                                           dIters + step);
+      if (use_lib) {
+        extract_minor_kernel<<<(mm * mm + 255) / 256, 256, 0, s>>>(dG, d, j, dA);
+        if (cus.syevd(cus.h, CUSOLVER_EIG_MODE_VECTOR, CUBLAS_FILL_MODE_LOWER, mm, dA, mm, dEv, dWork, lwork,
+                      dInfo + step) != CUSOLVER_STATUS_SUCCESS) {
+          delete m;
+          return c->fail(GS_ERR_CUDA, "cusolverDnDsyevd failed at step %d", step);
+        }
+        // eigenvectors come back column-major in dA: V[i][k] = dA[i + k*mm]
+        bayes_ridge_kernel<<<1, 256, bayes_smem, s>>>(dG, dMu, dNobs, d, j, dA, 1, mm, dEv,
+                                                      dCoef + (size_t)step * (d - 1), dIcpt + step, dIters + step);
+      } else {
+        int jt = 32;
+        while (jt < 1024 && jt < mm * mm / 4) jt <<= 1;
+        jacobi_eig_kernel<<<1, jt, 0, s>>>(dG, d, j, dA, dV, dEv, dSweeps + step);
+        bayes_ridge_kernel<<<1, 256, bayes_smem, s>>>(dG, dMu, dNobs, d, j, dV, mm, 1, dEv,
+                                                      dCoef + (size_t)step * (d - 1), dIcpt + step, dIters + step);
+      }
       if (missing[j] > 0)
         predict_kernel<<<(n + 7) / 8, 256, 0, s>>>(dXt, dMask, n, d, j, dCoef + (size_t)step * (d - 1), dIcpt + step);
       m->feat.push_back(j);
     }
-    max_abs_diff_kernel<<<256, 256, 0, s>>>(dXt, dPrev, total, dDiff);
+    max_row_diff_kernel<<<256, 256, 0, s>>>(dXt, dPrev, n, d, dDiff);
     e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaMemcpyAsync(diff.data(), dDiff, sizeof(double) * 256, cudaMemcpyDeviceToHost, s);
     if (e == cudaSuccess) e = cudaStreamSynchronize(s);
@@ -600,7 +690,7 @@ int gs_complete_fit(gs_ctx* c, const double* X, int32_t n, int32_t d, gs_model**
     }
     double inf_norm = 0.0;
     for (double v : diff) inf_norm = std::fmax(inf_norm, v);
-    if (inf_norm < norm_tol) break;  // _iterative.py:853-862
+    if (inf_norm < norm_tol) break;  // _iterative.py:853-862 (matrix infinity norm)
     CK(cudaMemcpyAsync(dPrev, dXt, sizeof(double) * total, cudaMemcpyDeviceToDevice, s));
   }
   m->n_steps = step;
@@ -615,8 +705,13 @@ int gs_complete_fit(gs_ctx* c, const double* X, int32_t n, int32_t d, gs_model**
     delete m;
     return c->cuda_fail(e, "completion: model download");
   }
+  if (use_lib) e = cudaMemcpy(sweeps.data(), dInfo, sizeof(int) * step, cudaMemcpyDeviceToHost);
+  if (e != cudaSuccess) {
+    delete m;
+    return c->cuda_fail(e, "completion: eigen-solver status download");
+  }
   for (int k = 0; k < step; ++k)
-    if (sweeps[k] >= 60) {
+    if (use_lib ? sweeps[k] != 0 : sweeps[k] >= 60) {
       delete m;
       return c->fail(GS_ERR_NOCONV, "gs_complete_fit: the eigen-solver did not converge at step %d", k);
     }

@@ -49,6 +49,7 @@ def main():
     cases["synth_200x12"] = synthetic(200, 12, 4, 0.30, 2)
     cases["synth_40x24_wide"] = synthetic(40, 24, 3, 0.25, 3)   # n_obs < d-1 for most features
     cases["synth_500x32"] = synthetic(500, 32, 6, 0.30, 4)
+    cases["synth_400x72"] = synthetic(400, 72, 8, 0.30, 6)      # beyond the Jacobi range: library eigensolver path
     for name, X in cases.items():
         with warnings.catch_warnings():
             warnings.simplefilter("ignore")
