@@ -30,7 +30,7 @@
 namespace gs {
 
 constexpr int kMaxFeatures = 1024; // d - 1 <= 1023 (shared arrays of the evidence iteration)
-constexpr int kJacobiMax = 64;     // d - 1 <= 64: hand-written one-CTA Jacobi; beyond: cuSOLVER's syevd
+constexpr int kJacobiMax = 24;     // d - 1 <= 24: hand-written one-CTA Jacobi (covers the reference tables); beyond: cuSOLVER syevd
 constexpr int kGramTile = 32;
 constexpr int kRounds = 10;        // IterativeImputer(max_iter=10), recommender.py:16
 constexpr double kRoundTol = 1e-3; // IterativeImputer tol
@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(1024) jacobi_eig_kernel(const double* __restri
   const int M = (m + 1) & ~1;  // players, even
   const int half = M / 2;
   int sweep = 0;
-  bool last = false;
+  double prev_off = -1.0;
   for (; sweep < 60; ++sweep) {
     // off-diagonal and total Frobenius norms
     double off = 0.0, tot = 0.0;
@@ -224,10 +224,11 @@ __global__ void __launch_bounds__(1024) jacobi_eig_kernel(const double* __restri
     }
     if (tid == 0) s_norm = s_red[0];
     __syncthreads();
-    // converged at off/||A|| <= 1e-15; Jacobi converges quadratically, so once a sweep starts
-    // below 1e-9 it is the last one needed (it lands on the rounding floor)
-    if (last || s_off <= 1e-30 * s_norm || s_norm == 0.0) break;
-    if (s_off <= 1e-18 * s_norm) last = true;
+    // converged at off/||A|| <= 1e-15, or stagnating on the rounding floor (below 1e-12 and no
+    // longer halving per sweep)
+    if (s_off <= 1e-30 * s_norm || s_norm == 0.0) break;
+    if (s_off <= 1e-24 * s_norm && prev_off >= 0.0 && s_off > 0.25 * prev_off) break;
+    prev_off = s_off;
     for (int step = 0; step < M - 1; ++step) {
       // pairs of this step
       if (tid < half) {
