@@ -34,8 +34,8 @@ METRIC = "pod x node Filter+Score+NormalizeScore evals/sec (50k pods x 5k nodes 
 UNIT = "evals/s"
 
 
-def workload_name(n_ranks):
-    return (f"batched Filter+Score+NormalizeScore, {N_PODS} pods x {N_NODES} nodes x {GPUS_PER_NODE} GPUs/node per rank"
+def workload_name(n_ranks, pods=N_PODS, nodes=N_NODES):
+    return (f"batched Filter+Score+NormalizeScore, {pods} pods x {nodes} nodes x {GPUS_PER_NODE} GPUs/node per rank"
             f" ({n_ranks} rank(s), nodes sharded)")
 
 
@@ -301,7 +301,7 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32+f64", "data": "synthetic",
-            "config": {"workload": workload_name(world), "pods": P, "nodes_per_rank": NL, "gpus_per_node": GPUS_PER_NODE,
+            "config": {"workload": workload_name(world, P, NL), "pods": P, "nodes_per_rank": NL, "gpus_per_node": GPUS_PER_NODE,
                        "apps": N_APPS, "residents_rank0": int(cluster.res_app.size),
                        "distinct_app_slo_classes": pkg.synth.distinct_classes(pods), "seed": hex(pkg.synth.SEED),
                        "l2": "flushed between timed iterations (256 MB memset, untimed); outputs 500 MB > L2",
