@@ -8,6 +8,7 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <vector>
 
 #include "../../include/gpusched.h"
 #include "context.h"
@@ -70,6 +71,8 @@ DevTables Ctx::tables() const {
   T.node_base = node_base;
   T.node_model = (const uint8_t*)node_model.p;
   T.node_ngpu = (const uint8_t*)node_ngpu.p;
+  T.node_orig = (const uint32_t*)node_orig.p;
+  T.res_new = (const uint32_t*)res_new.p;
   T.gpu_off = (const uint32_t*)gpu_off.p;
   T.res_app = (const uint32_t*)res_app.p;
   T.res_slo = (const float*)res_slo.p;
@@ -181,7 +184,7 @@ void gs_destroy(gs_ctx* c) {
     GS_LOCK(c);
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    gs::DevBuf* bufs[] = {&c->node_model, &c->node_ngpu, &c->gpu_off,   &c->res_app,   &c->res_slo, &c->conf,
+    gs::DevBuf* bufs[] = {&c->node_orig, &c->res_new, &c->node_model, &c->node_ngpu, &c->gpu_off,   &c->res_app,   &c->res_slo, &c->conf,
                           &c->interf,     &c->interf_t,  &c->sc_stage,  &c->col_of,    &c->res_rec,   &c->sc_counts, &c->sc_cursor,
                           &c->sc_nchunks, &c->sc_chunks, &c->sc_sorted, &c->sc_counts_all, &c->b_pod_app, &c->b_pod_slo,
                           &c->b_pod_self, &c->b_score,   &c->b_sel,     &c->b_extrema, &c->b_best,  &c->b_misc};
@@ -202,6 +205,9 @@ int gs_upload_cluster(gs_ctx* c, const gs_cluster* cl, int32_t node_base) {
   if (!c) return GS_ERR_INVALID;
   GS_LOCK(c);
   if (!cl) return c->fail(GS_ERR_INVALID, "gs_upload_cluster: null cluster");
+  if (cl->n_nodes > (1 << 24))
+    return c->fail(GS_ERR_INVALID, "gs_upload_cluster: %d nodes in one context; at most 2^24 (shard the cluster)",
+                   cl->n_nodes);
   if (cl->n_nodes < 0 || cl->max_gpus < 1 || cl->max_gpus > GS_MAX_GPUS_PER_NODE)
     return c->fail(GS_ERR_INVALID, "gs_upload_cluster: n_nodes=%d max_gpus=%d out of range (max_gpus 1..%d)",
                    cl->n_nodes, cl->max_gpus, GS_MAX_GPUS_PER_NODE);
@@ -225,12 +231,48 @@ int gs_upload_cluster(gs_ctx* c, const gs_cluster* cl, int32_t node_base) {
   const size_t R = cl->gpu_off[slots];
   if (R && (!cl->res_app || !cl->res_slo)) return c->fail(GS_ERR_INVALID, "gs_upload_cluster: null resident table");
   GS_CUDA(c, cudaSetDevice(c->device));
+  // Internal node order: nodes whose GPU loop runs (model and >= 1 UUID) grouped by model, the
+  // rest last — a stable partition, so that the 32 nodes of a warp share a model and a warp
+  // can skip what none of its nodes needs.  Results are written in the CALLER's node order
+  // (node_orig maps back); residents move with their nodes, order within a GPU unchanged.
+  std::vector<uint32_t> order(N), res_new(R ? R : 1);
+  {
+    size_t w = 0;
+    for (int pass = 0; pass < 3; ++pass)
+      for (size_t n = 0; n < N; ++n) {
+        const bool scored = cl->node_model[n] != GS_MODEL_NONE && cl->node_ngpu[n] > 0;
+        const int cls = !scored ? 2 : (cl->node_model[n] == GS_MODEL_A30 ? 0 : 1);
+        if (cls == pass) order[w++] = (uint32_t)n;
+      }
+  }
+  std::vector<uint8_t> p_model(N ? N : 1), p_ngpu(N ? N : 1);
+  std::vector<uint32_t> p_off(slots + 1), p_app(R ? R : 1);
+  std::vector<float> p_slo(R ? R : 1);
+  const size_t G = (size_t)cl->max_gpus;
+  p_off[0] = 0;
+  for (size_t i = 0; i < N; ++i) {
+    const size_t n = order[i];
+    p_model[i] = cl->node_model[n];
+    p_ngpu[i] = cl->node_ngpu[n];
+    for (size_t g = 0; g < G; ++g) {
+      const uint32_t lo = cl->gpu_off[n * G + g], hi = cl->gpu_off[n * G + g + 1];
+      uint32_t w = p_off[i * G + g];
+      for (uint32_t r = lo; r < hi; ++r, ++w) {
+        p_app[w] = cl->res_app[r];
+        p_slo[w] = cl->res_slo[r];
+        res_new[r] = w;
+      }
+      p_off[i * G + g + 1] = w;
+    }
+  }
   int rc;
-  if ((rc = c->upload(c->node_model, cl->node_model, N, "node_model"))) return rc;
-  if ((rc = c->upload(c->node_ngpu, cl->node_ngpu, N, "node_ngpu"))) return rc;
-  if ((rc = c->upload(c->gpu_off, cl->gpu_off, sizeof(uint32_t) * (slots + 1), "gpu_off"))) return rc;
-  if ((rc = c->upload(c->res_app, cl->res_app, sizeof(uint32_t) * R, "res_app"))) return rc;
-  if ((rc = c->upload(c->res_slo, cl->res_slo, sizeof(float) * R, "res_slo"))) return rc;
+  if ((rc = c->upload(c->node_model, p_model.data(), N, "node_model"))) return rc;
+  if ((rc = c->upload(c->node_ngpu, p_ngpu.data(), N, "node_ngpu"))) return rc;
+  if ((rc = c->upload(c->gpu_off, p_off.data(), sizeof(uint32_t) * (slots + 1), "gpu_off"))) return rc;
+  if ((rc = c->upload(c->res_app, p_app.data(), sizeof(uint32_t) * R, "res_app"))) return rc;
+  if ((rc = c->upload(c->res_slo, p_slo.data(), sizeof(float) * R, "res_slo"))) return rc;
+  if ((rc = c->upload(c->node_orig, order.data(), sizeof(uint32_t) * N, "node_orig"))) return rc;
+  if ((rc = c->upload(c->res_new, res_new.data(), sizeof(uint32_t) * R, "res_new"))) return rc;
   GS_CUDA(c, cudaStreamSynchronize(c->stream));  // caller may free its buffers on return
   c->n_nodes = cl->n_nodes;
   c->max_gpus = cl->max_gpus;

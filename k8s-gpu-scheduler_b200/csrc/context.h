@@ -23,7 +23,7 @@ struct Ctx {
   bool have_cluster = false;
   int n_nodes = 0, max_gpus = 1, redis_reachable = 1, node_base = 0;
   int64_t n_res = 0;
-  DevBuf node_model, node_ngpu, gpu_off, res_app, res_slo;
+  DevBuf node_model, node_ngpu, gpu_off, res_app, res_slo, node_orig, res_new;
   // prediction tables
   bool have_preds = false;
   int n_apps = 0, n_cols = 0;

@@ -7,18 +7,20 @@ namespace gs {
 
 // ------------------------------------------------------------------ helpers ----------
 
-// Fold one pod's per-lane (score, node) into per-pod extrema.  key orders by score, then
-// by lowest thread id; 0 = lane holds no node.
-__device__ __forceinline__ uint32_t lane_key(int score, int tid_in_tile) {
-  return (((uint32_t)score << 7) | (uint32_t)(kTile - 1 - tid_in_tile)) + 1u;
+// Fold one pod's per-lane (score, node) into per-pod extrema.  key orders by score, then by
+// the lowest node index in the CALLER's order (24 bits: shards of up to 16M nodes); 0 = lane
+// holds no node.
+constexpr uint32_t kNodeKeyMask = 0x00FFFFFFu;
+
+__device__ __forceinline__ uint32_t lane_key(int score, uint32_t node_orig) {
+  return (((uint32_t)score << 24) | (kNodeKeyMask - node_orig)) + 1u;
 }
 
-__device__ __forceinline__ void publish_extrema(uint32_t key, uint32_t negmax, uint32_t tile_node0, int node_base,
-                                                uint32_t pod, unsigned long long* hi_arg,
-                                                unsigned long long* neg_lo) {
+__device__ __forceinline__ void publish_extrema(uint32_t key, uint32_t negmax, int node_base, uint32_t pod,
+                                                unsigned long long* hi_arg, unsigned long long* neg_lo) {
   uint32_t k = key - 1u;
-  uint32_t score = k >> 7;
-  uint32_t node = tile_node0 + (uint32_t)(kTile - 1) - (k & 127u) + (uint32_t)node_base;
+  uint32_t score = k >> 24;
+  uint32_t node = kNodeKeyMask - (k & kNodeKeyMask) + (uint32_t)node_base;
   unsigned long long packed = ((unsigned long long)score << 32) | (unsigned long long)(0xFFFFFFFFu - node);
   atomicMax(&hi_arg[pod], packed);
   atomicMax(&neg_lo[pod], (unsigned long long)negmax);
@@ -50,8 +52,10 @@ __device__ __forceinline__ float conf_v100_for(const DevTables& T, uint32_t app,
 // Logic() for one (pod, node), op for op, any input (gpu_plugins.go:455-777).  Returns the
 // raw score and writes the packed selection byte.  Used by score_direct_kernel for every
 // pair and by score_fast_kernel for the pairs outside its streamlined domain.
+// `node` is an internal node index; `self` the CALLER's resident index (or -1).
 static __device__ __noinline__ int logic_eval(const DevTables& T, uint32_t app, float cur_slo, int32_t self, int node,
                                               unsigned* out_sel) {
+  if (self >= 0) self = (int32_t)T.res_new[self];
   int score = 0;
   unsigned sel = kSelNone, flags = 0;
   const size_t A = (size_t)T.n_apps;

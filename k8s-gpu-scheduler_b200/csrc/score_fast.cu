@@ -178,6 +178,7 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
   const uint32_t tile_node0 = blockIdx.y * kTile;
   const int node = (int)tile_node0 + tid;
   const bool in_range = node < T.n_nodes;
+  const uint32_t norig = in_range ? T.node_orig[node] : 0u;  // the caller's index of this node
   const uint32_t app = cd.app;
   const bool app_known = app < (uint32_t)T.n_apps;
   const size_t A = (size_t)T.n_apps;
@@ -347,7 +348,11 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
       }
       const bool has_cand = scored && conf != -1.0f;
       int packed = nocand;  // also right for !scored lanes: score 0, nothing selected
-      if (pr.orig & kPodInfInv) {
+      // nodes are grouped by model (gs_upload_cluster), so whole warps have no candidate term:
+      // warps of nodes without model/GPUs, and V100 warps when no configuration exceeds the SLO
+      if (!__any_sync(0xFFFFFFFFu, has_cand)) {
+        // nothing to evaluate: every lane keeps its residents-only result
+      } else if (pr.orig & kPodInfInv) {
         // t = +-Inf * (slo - d): 1/(1+Inf) = 0 on either side, NaN when slo - d is 0 or NaN
         int score = 0;
         unsigned sel = kSelNone;
@@ -406,11 +411,11 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
       if (has_cand) flags |= kFlagF7;
       const int score = packed >> 8;
       if (in_range) {
-        const size_t o = (size_t)orig * T.n_nodes + node;
+        const size_t o = (size_t)orig * T.n_nodes + norig;
         out_score[o] = (uint8_t)score;
         out_sel[o] = (uint8_t)((unsigned)(packed & 0xFF) | flags);
       }
-      uint32_t key = in_range ? lane_key(score, tid) : 0u;
+      uint32_t key = in_range ? lane_key(score, norig) : 0u;
       uint32_t ngm = in_range ? (uint32_t)(100 - score) : 0u;
       key = __reduce_max_sync(0xFFFFFFFFu, key);
       ngm = __reduce_max_sync(0xFFFFFFFFu, ngm);
@@ -427,7 +432,7 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
         key = max(key, sm->key[w][tid]);
         ngm = max(ngm, sm->neg[w][tid]);
       }
-      publish_extrema(key, ngm, tile_node0, T.node_base, sm->pods[tid].orig & kPodIndexMask, hi_arg, neg_lo);
+      publish_extrema(key, ngm, T.node_base, sm->pods[tid].orig & kPodIndexMask, hi_arg, neg_lo);
     }
   }
 }

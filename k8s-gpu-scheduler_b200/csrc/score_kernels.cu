@@ -75,15 +75,17 @@ __global__ void __launch_bounds__(kTile) score_direct_kernel(DevTables T, const 
   const int node = blockIdx.y * kTile + threadIdx.x;
   const bool in_range = node < T.n_nodes;
   int score = 0;
+  uint32_t norig = 0;
   if (in_range) {
     unsigned selbyte;
+    norig = T.node_orig[node];
     score = logic_eval(T, pod_app[p], pod_slo[p], pod_self ? pod_self[p] : -1, node, &selbyte);
-    size_t o = (size_t)p * T.n_nodes + node;
+    size_t o = (size_t)p * T.n_nodes + norig;
     out_score[o] = (uint8_t)score;
     out_sel[o] = (uint8_t)selbyte;
   }
   // per-pod extrema over this tile
-  uint32_t key = in_range ? lane_key(score, threadIdx.x) : 0u;
+  uint32_t key = in_range ? lane_key(score, norig) : 0u;
   uint32_t neg = in_range ? (uint32_t)(100 - score) : 0u;
   key = __reduce_max_sync(0xFFFFFFFFu, key);
   neg = __reduce_max_sync(0xFFFFFFFFu, neg);
@@ -98,7 +100,7 @@ __global__ void __launch_bounds__(kTile) score_direct_kernel(DevTables T, const 
       key = max(key, s_key[w]);
       neg = max(neg, s_neg[w]);
     }
-    publish_extrema(key, neg, blockIdx.y * kTile, T.node_base, p, hi_arg, neg_lo);
+    publish_extrema(key, neg, T.node_base, p, hi_arg, neg_lo);
   }
 }
 

@@ -13,8 +13,13 @@ struct DevTables {
   int n_cols;
   int redis_reachable;
   int node_base;
+  // node tables are in the library's internal order (grouped by model, see gs_upload_cluster);
+  // node_orig[i] = the caller's index of internal node i, res_new[r] = internal index of the
+  // caller's resident r
   const uint8_t* node_model;  // [N]
   const uint8_t* node_ngpu;   // [N]
+  const uint32_t* node_orig;  // [N]
+  const uint32_t* res_new;    // [R]
   const uint32_t* gpu_off;    // [N*G+1]
   const uint32_t* res_app;    // [R]
   const float* res_slo;       // [R]
