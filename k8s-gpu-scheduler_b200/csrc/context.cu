@@ -231,19 +231,26 @@ int gs_upload_cluster(gs_ctx* c, const gs_cluster* cl, int32_t node_base) {
   const size_t R = cl->gpu_off[slots];
   if (R && (!cl->res_app || !cl->res_slo)) return c->fail(GS_ERR_INVALID, "gs_upload_cluster: null resident table");
   GS_CUDA(c, cudaSetDevice(c->device));
-  // Internal node order: nodes whose GPU loop runs (model and >= 1 UUID) grouped by model, the
-  // rest last — a stable partition, so that the 32 nodes of a warp share a model and a warp
-  // can skip what none of its nodes needs.  Results are written in the CALLER's node order
-  // (node_orig maps back); residents move with their nodes, order within a GPU unchanged.
+  // Internal node order: within every block of kGroupBlock consecutive nodes, the nodes whose
+  // GPU loop runs (model and >= 1 UUID) are grouped by model, the rest last — a stable
+  // partition, so that most warps hold 32 nodes of one model and can skip what none of them
+  // needs.  Results are written in the CALLER's node order (node_orig maps back); grouping
+  // inside blocks rather than globally keeps the writers of one 32-byte output sector close in
+  // time, so L2 merges them (a global grouping measured 2.2 GB of extra DRAM read-modify-write).
+  // Residents move with their nodes, order within a GPU unchanged.
+  constexpr size_t kGroupBlock = 256;
   std::vector<uint32_t> order(N), res_new(R ? R : 1);
   {
     size_t w = 0;
-    for (int pass = 0; pass < 3; ++pass)
-      for (size_t n = 0; n < N; ++n) {
-        const bool scored = cl->node_model[n] != GS_MODEL_NONE && cl->node_ngpu[n] > 0;
-        const int cls = !scored ? 2 : (cl->node_model[n] == GS_MODEL_A30 ? 0 : 1);
-        if (cls == pass) order[w++] = (uint32_t)n;
-      }
+    for (size_t b0 = 0; b0 < N; b0 += kGroupBlock) {
+      const size_t b1 = std::min(N, b0 + kGroupBlock);
+      for (int pass = 0; pass < 3; ++pass)
+        for (size_t n = b0; n < b1; ++n) {
+          const bool scored = cl->node_model[n] != GS_MODEL_NONE && cl->node_ngpu[n] > 0;
+          const int cls = !scored ? 2 : (cl->node_model[n] == GS_MODEL_A30 ? 0 : 1);
+          if (cls == pass) order[w++] = (uint32_t)n;
+        }
+    }
   }
   std::vector<uint8_t> p_model(N ? N : 1), p_ngpu(N ? N : 1);
   std::vector<uint32_t> p_off(slots + 1), p_app(R ? R : 1);

@@ -270,10 +270,12 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
       for (int g = 0; g < kFastMaxGpus; ++g) {
         cntr[g] = 0;
         if (g < k) {
-          base_n[g] = stage.n0[st_row + g];
-          base_p[g] = stage.p0[st_row + g];
-          cand_interf[g] = stage.ci[st_row + g];
-          cntr[g] = stage.cnt[st_row + g];
+          // read once: streaming loads, so that the table does not push half-written output
+          // sectors out of L2
+          base_n[g] = __ldcs(stage.n0 + st_row + g);
+          base_p[g] = __ldcs(stage.p0 + st_row + g);
+          cand_interf[g] = __ldcs(stage.ci + st_row + g);
+          cntr[g] = __ldcs(stage.cnt + st_row + g);
         }
       }
 #pragma unroll
