@@ -95,7 +95,7 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": reasons, "samples": len(self.rows)}
 
 
-def cpu_reference_leg(preds, cluster, pods, budget_evals_per_thread=1_500_000, steps=1, warmup=0):
+def cpu_reference_leg(preds, cluster, pods, budget_evals_per_thread=3_000_000, steps=1, warmup=0):
     """The CPU restatement of the reference algorithm on a bounded sample (first pods of the batch)."""
     from oracle.score_oracle import Oracle, num_threads
 

@@ -244,3 +244,37 @@ def test_sliced_host_path_large_batch(sched, oracle_mod, synth):
     rows = np.random.default_rng(3).choice(9000, size=24, replace=False)
     w = oracle_mod.Oracle(preds, cluster).score_batch(synth.Pods(app=pods.app[rows], slo=pods.slo[rows]), normalize=True)
     assert np.array_equal(w[0], fast[0][rows]) and np.array_equal(w[1], fast[1][rows]) and np.array_equal(w[2], fast[2][rows])
+
+
+def test_baseline_config2_full_size_properties(sched, oracle_mod, synth):
+    """BASELINE.json configs[1] at full size (50 000 pods x 5 000 nodes x 8 GPUs): too large for the
+    oracle, so parity is carried by size-independent properties — the restructured and the
+    op-for-op kernels agree on all 2.5*10^8 (score, selection) pairs and on every best node,
+    NormalizeScore's integer rescale is reproduced from the raw scores, a GPU is selected iff the
+    score is >= 1, F-bits are consistent with the node tables — plus 32 sampled pods against the
+    oracle."""
+    preds, cluster, pods = synth.make_workload(50_000, 5_000, gpus_per_node=8)
+    sched.upload_predictions(preds)
+    sched.upload_cluster(cluster)
+    raw, sel, best = sched.score_batch(pods, normalize=False)
+    raw_d, sel_d, best_d = sched.score_batch(pods, normalize=False, direct=True)
+    assert np.array_equal(raw, raw_d) and np.array_equal(sel, sel_d) and np.array_equal(best, best_d)
+    del raw_d, sel_d
+    nrm, sel_n, best_n = sched.score_batch(pods, normalize=True)
+    assert np.array_equal(sel, sel_n) and np.array_equal(best, best_n)
+    lo = raw.min(axis=1).astype(np.int32)
+    hi = raw.max(axis=1).astype(np.int32)
+    for rows in np.array_split(np.arange(50_000), 10):          # bounded temporaries
+        r = raw[rows].astype(np.int32)
+        rg = (hi[rows] - lo[rows])[:, None]
+        want = np.where(rg == 0, 0, (r - lo[rows, None]) * 100 // np.where(rg == 0, 1, rg))
+        assert np.array_equal(nrm[rows], want.astype(np.uint8))
+        assert np.array_equal(best[rows], r.argmax(axis=1).astype(np.int32))
+        assert np.array_equal((sel[rows] & 31) == 31, raw[rows] == 0)
+    eligible = (cluster.node_model != 0) & (cluster.node_ngpu > 0)
+    assert np.array_equal((sel >> 7).astype(bool), np.broadcast_to(eligible, sel.shape))
+    assert not raw[:, ~eligible].any()
+    assert raw.max() <= 100
+    pick = np.random.default_rng(2).choice(50_000, size=32, replace=False)
+    w = oracle_mod.Oracle(preds, cluster).score_batch(synth.Pods(app=pods.app[pick], slo=pods.slo[pick]), normalize=True)
+    assert np.array_equal(w[0], nrm[pick]) and np.array_equal(w[1], sel[pick]) and np.array_equal(w[2], best[pick])
