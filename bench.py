@@ -54,27 +54,55 @@ def measured_peak_gbs():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region."""
+    """SM clock and throttle reasons DURING the timed region: NVML polled every few ms from a thread
+    (nvidia-smi as a fallback, which is too slow for short regions)."""
 
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    REASONS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
 
     def __init__(self, index):
-        self.index, self.rows, self._stop, self._t = index, [], threading.Event(), None
+        self.index, self.sm, self.mask, self.max_sm = index, [], 0, None
+        self._stop, self._t, self._nvml, self._h = threading.Event(), None, None, None
+        try:
+            import pynvml
 
-    def _run(self):
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and all(x.strip().isdigit() for x in vis.split(",")) else index
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_sm = float(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+            self._nvml = pynvml
+        except Exception:
+            self._nvml = None
+
+    def _poll_nvml(self):
+        n = self._nvml
         while not self._stop.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                self.sm.append(float(n.nvmlDeviceGetClockInfo(self._h, n.NVML_CLOCK_SM)))
+                self.mask |= int(n.nvmlDeviceGetCurrentClocksEventReasons(self._h))
+            except Exception:
+                try:
+                    self.mask |= int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self._h))
+                except Exception:
+                    pass
+            self._stop.wait(0.003)
+
+    def _poll_smi(self):
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.active"
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i",
                                       str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([x.strip() for x in out.splitlines()[0].split(",")])
+                f = [x.strip() for x in out.splitlines()[0].split(",")]
+                self.sm.append(float(f[0]))
+                self.max_sm = float(f[1])
+                self.mask |= int(f[2], 16)
             except Exception:
                 pass
-            self._stop.wait(0.1)
+            self._stop.wait(0.05)
 
     def __enter__(self):
-        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t = threading.Thread(target=self._poll_nvml if self._nvml else self._poll_smi, daemon=True)
         self._t.start()
         return self
 
@@ -83,16 +111,12 @@ class ClockSampler:
         self._t.join(timeout=10)
 
     def summary(self):
-        if not self.rows:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
-        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in self.rows if len(r) > 3 + i)]
-        try:
-            mx = float(self.rows[0][1])
-        except Exception:
-            mx = None
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": reasons, "samples": len(self.rows)}
+        if not self.sm:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_sm, "reasons": ["unsampled"], "samples": 0}
+        sm = sorted(self.sm)
+        reasons = [k for k, bit in self.REASONS.items() if self.mask & bit]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": self.max_sm, "reasons": reasons, "samples": len(sm),
+                "source": "nvml" if self._nvml else "nvidia-smi"}
 
 
 def cpu_reference_leg(preds, cluster, pods, budget_evals_per_thread=3_000_000, steps=1, warmup=0):
@@ -310,7 +334,10 @@ def main():
             "wall_ms_per_step_incl_flush": t_wall * 1e3 / args.steps,
             "clocks": clocks.summary(),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_kind": peak_kind, "kernel": "score_fast_kernel",
+                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the ncu capture in
+                         # profiles/r1/ncu_traffic_score_fast_grouped256.csv (default workload only): 1.05 GB of
+                         # it is the per-batch residents-sum table, the rest results + partial-sector merges
+                         "traffic": 2019169280 if (P, NL) == (N_PODS, N_NODES) else None, "peak_kind": peak_kind, "kernel": "score_fast_kernel",
                          "kernel_ms": kernel_ms, "algorithmic_bytes": abytes,
                          "note": "kernel is FP64-pipe / issue bound, not HBM bound (see DESIGN.md 4.2)"},
             # the roofline that actually binds: 16 float64 operations per (pod,node,GPU) against the
