@@ -259,6 +259,21 @@ typedef struct gs_model gs_model;
  * Replaces Imputer.fit, pkg/recommender/recommender/recommender.py:15-22. */
 GS_API int gs_complete_fit(gs_ctx* ctx, const double* X, int32_t n, int32_t d, gs_model** out);
 
+/* The same fit with the ROWS of X sharded over several contexts (one per GPU / rank): every
+ * rank passes its own rows and a callback that all-reduces a float64 device buffer in place
+ * over the ranks (sum or max).  The callback is the path's only exchange: per feature the
+ * column sums (d+1 values) and the centred Gram matrix (d*d values) of the rows where the
+ * feature is observed, per round one scalar; every rank then solves the same small system and
+ * imputes its own rows, so all ranks return identical models.  The buffer is ready on `stream`
+ * when the callback is invoked; the reduced values must be visible to work submitted to
+ * `stream` after it returns (enqueue the collective on that stream, or synchronise).  Return 0
+ * for success.  No counterpart in the reference (row-sharded completion). */
+#define GS_REDUCE_SUM 0
+#define GS_REDUCE_MAX 1
+typedef int (*gs_allreduce_fn)(double* device_buffer, int64_t count, int op, void* stream, void* user);
+GS_API int gs_complete_fit_sharded(gs_ctx* ctx, const double* X_local, int32_t n_local, int32_t d,
+                                   gs_allreduce_fn reduce, void* user, gs_model** out);
+
 /* Impute X [m x d] (NaN = missing) into out [m x d]; observed entries are returned
  * unchanged.  Replaces Imputer.predict, recommender.py:24-27. */
 GS_API int gs_complete_transform(gs_ctx* ctx, const gs_model* model, const double* X, int32_t m,

@@ -31,7 +31,7 @@ ERR_NAMES = {-1: "GS_ERR_INVALID", -2: "GS_ERR_CUDA", -3: "GS_ERR_STATE", -4: "G
 EXPORTS = [
     "gs_create", "gs_destroy", "gs_last_error", "gs_version", "gs_upload_cluster", "gs_upload_predictions",
     "gs_score_batch", "gs_score_raw_dev", "gs_score_raw_dev_noalloc", "gs_normalize_dev", "gs_normalize_scores", "gs_select_mig",
-    "gs_set_profiling", "gs_last_score_kernel_ms", "gs_selftest", "gs_complete_fit", "gs_complete_transform", "gs_model_info", "gs_model_step", "gs_model_destroy",
+    "gs_set_profiling", "gs_last_score_kernel_ms", "gs_selftest", "gs_complete_fit", "gs_complete_fit_sharded", "gs_complete_transform", "gs_model_info", "gs_model_step", "gs_model_destroy",
 ]
 
 
@@ -51,6 +51,10 @@ class _GsPredictions(C.Structure):
     _fields_ = [("n_apps", C.c_int32), ("n_cols", C.c_int32), ("conf", C.c_void_p), ("interf", C.c_void_p),
                 ("col_of", C.c_void_p)]
 
+
+# int (*gs_allreduce_fn)(double* device_buffer, int64_t count, int op, void* stream, void* user)
+ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p)
+REDUCE_SUM, REDUCE_MAX = 0, 1
 
 _lib = None
 
@@ -83,6 +87,7 @@ def load_library():
     L.gs_last_score_kernel_ms.argtypes = [vp, C.POINTER(C.c_float)]
     L.gs_selftest.argtypes = [vp, C.c_uint64, i32, C.POINTER(C.c_uint64)]
     L.gs_complete_fit.argtypes = [vp, vp, i32, i32, C.POINTER(vp)]
+    L.gs_complete_fit_sharded.argtypes = [vp, vp, i32, i32, ALLREDUCE_FN, vp, C.POINTER(vp)]
     L.gs_complete_transform.argtypes = [vp, vp, vp, i32, vp]
     L.gs_model_info.argtypes = [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]
     L.gs_model_step.argtypes = [vp, i32, C.POINTER(i32), vp, C.POINTER(C.c_double)]
@@ -260,6 +265,49 @@ def complete_fit(sched: "Scheduler", X) -> CompletionModel:
     h = C.c_void_p()
     sched._check(sched._L.gs_complete_fit(sched._h, _ptr(X), int(X.shape[0]), int(X.shape[1]), C.byref(h)))
     return CompletionModel(sched, h)
+
+
+def complete_fit_sharded(sched: "Scheduler", X_local, allreduce) -> CompletionModel:
+    """Row-sharded Imputer.fit: `allreduce(ptr, count, op, stream)` must all-reduce the float64
+    device buffer at `ptr` in place over the ranks (op REDUCE_SUM / REDUCE_MAX) and return 0."""
+    X = np.ascontiguousarray(X_local, dtype=np.float64)
+
+    def _cb(ptr, count, op, stream, _user):
+        try:
+            return int(allreduce(int(ptr), int(count), int(op), int(stream) if stream else 0) or 0)
+        except Exception:  # noqa: BLE001  (never let an exception cross the C boundary)
+            import traceback
+
+            traceback.print_exc()
+            return 1
+
+    cb = ALLREDUCE_FN(_cb)
+    h = C.c_void_p()
+    sched._check(sched._L.gs_complete_fit_sharded(sched._h, _ptr(X), int(X.shape[0]), int(X.shape[1]), cb, None,
+                                                  C.byref(h)))
+    return CompletionModel(sched, h)
+
+
+class DevicePointer:
+    """A raw device address as a __cuda_array_interface__ object (zero-copy torch.as_tensor)."""
+
+    def __init__(self, ptr: int, count: int, typestr: str = "<f8"):
+        self.__cuda_array_interface__ = {"shape": (count,), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+def torch_allreduce(group=None):
+    """An `allreduce` for complete_fit_sharded over torch.distributed (NCCL): the collective is
+    enqueued on the library's stream."""
+    import torch
+    import torch.distributed as dist
+
+    def _ar(ptr, count, op, stream):
+        t = torch.as_tensor(DevicePointer(ptr, count), device="cuda")
+        with torch.cuda.stream(torch.cuda.ExternalStream(stream)):
+            dist.all_reduce(t, op=dist.ReduceOp.SUM if op == REDUCE_SUM else dist.ReduceOp.MAX, group=group)
+        return 0
+
+    return _ar
 
 
 MIG_CONFIGS = ["all-4g.24gb", "all-2g.12gb", "all-1g.6gb"]  # gpu_plugins.go:52

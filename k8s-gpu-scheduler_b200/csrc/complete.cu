@@ -39,9 +39,10 @@ constexpr double kBrTol = 1e-3;
 constexpr double kBrPrior = 1e-6;  // alpha_1 = alpha_2 = lambda_1 = lambda_2
 
 // ---- initial imputation: column means over the observed entries (SimpleImputer "mean") ----
+// stats = [sum(d) | count(d) | n_rows(1) | max_abs(d)]: the first 2d+1 are summed over ranks,
+// the last d maximised, before finish_means_kernel turns them into means.
 __global__ void __launch_bounds__(256) column_stats_kernel(const double* __restrict__ X, int n, int d,
-                                                          double* __restrict__ means, int* __restrict__ n_missing,
-                                                          double* __restrict__ max_abs) {
+                                                          double* __restrict__ stats) {
   __shared__ double s_sum[256];
   __shared__ double s_max[256];
   __shared__ int s_cnt[256];
@@ -69,10 +70,16 @@ __global__ void __launch_bounds__(256) column_stats_kernel(const double* __restr
     __syncthreads();
   }
   if (threadIdx.x == 0) {
-    means[c] = s_cnt[0] ? s_sum[0] / (double)s_cnt[0] : 0.0;
-    n_missing[c] = n - s_cnt[0];
-    max_abs[c] = s_max[0];
+    stats[c] = s_sum[0];
+    stats[d + c] = (double)s_cnt[0];
+    stats[2 * d + 1 + c] = s_max[0];
+    if (c == 0) stats[2 * d] = (double)n;
   }
+}
+
+__global__ void finish_means_kernel(const double* __restrict__ stats, int d, double* __restrict__ means) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < d) means[c] = stats[d + c] > 0.0 ? stats[c] / stats[d + c] : 0.0;
 }
 
 __global__ void fill_kernel(const double* __restrict__ X, const double* __restrict__ means, size_t total, int d,
@@ -86,10 +93,10 @@ __global__ void fill_kernel(const double* __restrict__ X, const double* __restri
 }
 
 // ---- moments over the rows where feature j is observed ----
-// column sums (all d columns) + row count; one CTA per column
-__global__ void __launch_bounds__(256) obs_means_kernel(const double* __restrict__ Xt, const uint8_t* __restrict__ mask,
-                                                       int n, int d, int j, double* __restrict__ mu,
-                                                       int* __restrict__ n_obs) {
+// column sums (all d columns) + row count as sums[d]; one CTA per column.  Summed over ranks
+// before finish_mu_kernel divides.
+__global__ void __launch_bounds__(256) obs_sums_kernel(const double* __restrict__ Xt, const uint8_t* __restrict__ mask,
+                                                      int n, int d, int j, double* __restrict__ sums) {
   __shared__ double s_sum[256];
   __shared__ int s_cnt[256];
   const int c = blockIdx.x;
@@ -112,9 +119,31 @@ __global__ void __launch_bounds__(256) obs_means_kernel(const double* __restrict
     __syncthreads();
   }
   if (threadIdx.x == 0) {
-    mu[c] = s_cnt[0] ? s_sum[0] / (double)s_cnt[0] : 0.0;
-    if (c == 0) *n_obs = s_cnt[0];
+    sums[c] = s_sum[0];
+    if (c == 0) sums[d] = (double)s_cnt[0];
   }
+}
+
+__global__ void finish_mu_kernel(const double* __restrict__ sums, int d, double* __restrict__ mu,
+                                 int* __restrict__ n_obs) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const double cnt = sums[d];
+  if (c < d) mu[c] = cnt > 0.0 ? sums[c] / cnt : 0.0;
+  if (c == 0) *n_obs = (int)cnt;
+}
+
+// out[0] = max(in[0..n))
+__global__ void __launch_bounds__(256) max_small_kernel(double* __restrict__ v, int n) {
+  __shared__ double s_red[256];
+  double mx = 0.0;
+  for (int i = threadIdx.x; i < n; i += 256) mx = fmax(mx, v[i]);
+  s_red[threadIdx.x] = mx;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) s_red[threadIdx.x] = fmax(s_red[threadIdx.x], s_red[threadIdx.x + s]);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) v[0] = s_red[0];
 }
 
 // Partial centred Gram: grid = (tiles_b, tiles_a, row_parts); CTA 16x16 threads, each a 2x2
@@ -547,20 +576,31 @@ struct DevMem {
 extern "C" {
 
 int gs_complete_fit(gs_ctx* c, const double* X, int32_t n, int32_t d, gs_model** out) {
+  return gs_complete_fit_sharded(c, X, n, d, nullptr, nullptr, out);
+}
+
+int gs_complete_fit_sharded(gs_ctx* c, const double* X, int32_t n, int32_t d, gs_allreduce_fn reduce, void* user,
+                            gs_model** out) {
   using namespace gs;
   if (out) *out = nullptr;
   if (!c) return GS_ERR_INVALID;
   std::lock_guard<std::mutex> lk(c->mu);
   if (!X || !out || n < 1 || d < 1) return c->fail(GS_ERR_INVALID, "gs_complete_fit: null pointer or empty matrix");
+  // the path's exchange steps: sums / maxima of small float64 buffers over the row shards
+  auto exchange = [&](double* buf, int64_t count, int op, cudaStream_t st) -> int {
+    if (!reduce) return GS_OK;
+    int rc = reduce(buf, count, op, (void*)st, user);
+    return rc == 0 ? GS_OK : c->fail(GS_ERR_CUDA, "gs_complete_fit_sharded: the all-reduce callback failed (%d)", rc);
+  };
   if (d - 1 >= kMaxFeatures)
     return c->fail(GS_ERR_UNSUPPORTED, "gs_complete_fit: %d columns; this build covers at most %d", d, kMaxFeatures);
   CK(cudaSetDevice(c->device));
   cudaStream_t s = c->stream;
   const size_t total = (size_t)n * d;
   DevMem mem;
-  double *dX, *dXt, *dPrev, *dMeans, *dMaxAbs, *dMu, *dG, *dPartial, *dA, *dV, *dEv, *dCoef, *dIcpt, *dDiff;
+  double *dX, *dXt, *dPrev, *dMeans, *dStats, *dSums, *dMu, *dG, *dPartial, *dA, *dV, *dEv, *dCoef, *dIcpt, *dDiff;
   uint8_t* dMask;
-  int *dMissing, *dNobs, *dIters, *dSweeps;
+  int *dNobs, *dIters, *dSweeps;
   const int tiles = (d + kGramTile - 1) / kGramTile;
   int parts = (n + 255) / 256;
   if (parts > 128) parts = 128;
@@ -574,8 +614,8 @@ int gs_complete_fit(gs_ctx* c, const double* X, int32_t n, int32_t d, gs_model**
   CK(mem.alloc(&dPrev, total));
   CK(mem.alloc(&dMask, total));
   CK(mem.alloc(&dMeans, d));
-  CK(mem.alloc(&dMaxAbs, d));
-  CK(mem.alloc(&dMissing, d));
+  CK(mem.alloc(&dStats, 3 * (size_t)d + 1));
+  CK(mem.alloc(&dSums, (size_t)d + 1));
   CK(mem.alloc(&dMu, d));
   CK(mem.alloc(&dNobs, 1));
   CK(mem.alloc(&dG, (size_t)d * d));
@@ -615,28 +655,36 @@ int gs_complete_fit(gs_ctx* c, const double* X, int32_t n, int32_t d, gs_model**
   if (!m) return c->fail(GS_ERR_NOMEM, "gs_complete_fit: out of host memory");
   m->d = d;
   m->means.resize(d);
-  std::vector<int> missing(d);
-  std::vector<double> max_abs(d);
+  std::vector<long long> missing(d);
+  std::vector<double> stats(3 * (size_t)d + 1);
 
-  column_stats_kernel<<<d, 256, 0, s>>>(dX, n, d, dMeans, dMissing, dMaxAbs);
+  column_stats_kernel<<<d, 256, 0, s>>>(dX, n, d, dStats);
+  int xrc;
+  if ((xrc = exchange(dStats, 2 * (int64_t)d + 1, GS_REDUCE_SUM, s)) || (xrc = exchange(dStats + 2 * d + 1, d, GS_REDUCE_MAX, s))) {
+    delete m;
+    return xrc;
+  }
+  finish_means_kernel<<<(d + 255) / 256, 256, 0, s>>>(dStats, d, dMeans);
   fill_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(dX, dMeans, total, d, dXt, dMask);
   cudaError_t e = cudaGetLastError();
   if (e == cudaSuccess) e = cudaMemcpyAsync(m->means.data(), dMeans, sizeof(double) * d, cudaMemcpyDeviceToHost, s);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(missing.data(), dMissing, sizeof(int) * d, cudaMemcpyDeviceToHost, s);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(max_abs.data(), dMaxAbs, sizeof(double) * d, cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(stats.data(), dStats, sizeof(double) * stats.size(), cudaMemcpyDeviceToHost, s);
   if (e == cudaSuccess) e = cudaStreamSynchronize(s);
   if (e != cudaSuccess) {
     delete m;
     return c->cuda_fail(e, "completion: initial imputation");
   }
+  const long long n_all = (long long)stats[2 * d];  // rows over all shards
+  for (int k = 0; k < d; ++k) missing[k] = n_all - (long long)stats[d + k];
+  const double* max_abs = stats.data() + 2 * d + 1;
   bool all_missing = true;
   for (int k = 0; k < d; ++k) {
-    if (missing[k] == n) {
+    if (missing[k] == n_all) {
       delete m;
       return c->fail(GS_ERR_UNSUPPORTED, "gs_complete_fit: column %d has no observed value (scikit-learn drops such "
                      "columns; not served)", k);
     }
-    if (missing[k] != n) all_missing = false;
+    if (missing[k] != n_all) all_missing = false;
   }
   if (d == 1 || all_missing) {  // _iterative.py:783-789: nothing to iterate
     *out = m;
@@ -647,7 +695,7 @@ int gs_complete_fit(gs_ctx* c, const double* X, int32_t n, int32_t d, gs_model**
   for (int k = 0; k < d; ++k) order[k] = k;
   std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return missing[a] < missing[b]; });
   double mx = 0.0;
-  for (double v : max_abs) mx = std::fmax(mx, v);
+  for (int k = 0; k < d; ++k) mx = std::fmax(mx, max_abs[k]);
   const double norm_tol = kRoundTol * mx;
 
   int step = 0;
@@ -657,9 +705,18 @@ int gs_complete_fit(gs_ctx* c, const double* X, int32_t n, int32_t d, gs_model**
     m->n_rounds = rnd;
     for (int oi = 0; oi < d; ++oi, ++step) {
       const int j = order[oi];
-      obs_means_kernel<<<d, 256, 0, s>>>(dXt, dMask, n, d, j, dMu, dNobs);
+      obs_sums_kernel<<<d, 256, 0, s>>>(dXt, dMask, n, d, j, dSums);
+      if ((xrc = exchange(dSums, (int64_t)d + 1, GS_REDUCE_SUM, s))) {
+        delete m;
+        return xrc;
+      }
+      finish_mu_kernel<<<(d + 255) / 256, 256, 0, s>>>(dSums, d, dMu, dNobs);
       gram_partial_kernel<<<dim3(tiles, tiles, parts), 256, 0, s>>>(dXt, dMask, n, d, j, dMu, rows_per_part, dPartial);
       gram_reduce_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dPartial, d, parts, dG);
+      if ((xrc = exchange(dG, (int64_t)d * d, GS_REDUCE_SUM, s))) {
+        delete m;
+        return xrc;
+      }
       if (use_lib) {
         extract_minor_kernel<<<(mm * mm + 255) / 256, 256, 0, s>>>(dG, d, j, dA);
         if (cus.syevd(cus.h, CUSOLVER_EIG_MODE_VECTOR, CUBLAS_FILL_MODE_LOWER, mm, dA, mm, dEv, dWork, lwork,
@@ -682,15 +739,19 @@ int gs_complete_fit(gs_ctx* c, const double* X, int32_t n, int32_t d, gs_model**
       m->feat.push_back(j);
     }
     max_row_diff_kernel<<<256, 256, 0, s>>>(dXt, dPrev, n, d, dDiff);
+    max_small_kernel<<<1, 256, 0, s>>>(dDiff, 256);
+    if ((xrc = exchange(dDiff, 1, GS_REDUCE_MAX, s))) {
+      delete m;
+      return xrc;
+    }
     e = cudaGetLastError();
-    if (e == cudaSuccess) e = cudaMemcpyAsync(diff.data(), dDiff, sizeof(double) * 256, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(diff.data(), dDiff, sizeof(double), cudaMemcpyDeviceToHost, s);
     if (e == cudaSuccess) e = cudaStreamSynchronize(s);
     if (e != cudaSuccess) {
       delete m;
       return c->cuda_fail(e, "completion: round");
     }
-    double inf_norm = 0.0;
-    for (double v : diff) inf_norm = std::fmax(inf_norm, v);
+    const double inf_norm = diff[0];
     if (inf_norm < norm_tol) break;  // _iterative.py:853-862 (matrix infinity norm)
     CK(cudaMemcpyAsync(dPrev, dXt, sizeof(double) * total, cudaMemcpyDeviceToDevice, s));
   }

@@ -63,3 +63,113 @@ def test_fit_errors(pkg, sched):
     m = pkg.complete_fit(sched, np.arange(6.0).reshape(6, 1))   # a single column: nothing to iterate
     assert m.n_steps == 0 and m.n_rounds == 0
     m.close()
+
+
+def test_row_sharded_fit_two_contexts_one_gpu(pkg):
+    """gs_complete_fit_sharded with the rows split over two contexts (two host threads standing in for
+    two ranks; the all-reduce callback sums / maximises their buffers on the device): both ranks
+    return the same model, and it matches the reference's Imputer like the unsharded fit does."""
+    import threading
+
+    import torch
+
+    g = np.load([p for p in GOLD if "synth_500x32" in p][0])
+    X = g["X"]
+    halves = [X[:230], X[230:]]
+    scheds = [pkg.Scheduler(0), pkg.Scheduler(0)]
+    barrier = threading.Barrier(2)
+    bufs = [None, None]
+    models, errors = [None, None], []
+
+    def make_allreduce(r):
+        def allreduce(ptr, count, op, stream):
+            torch.cuda.ExternalStream(stream).synchronize()          # this rank's buffer is complete
+            bufs[r] = torch.as_tensor(pkg.DevicePointer(ptr, count), device="cuda")
+            barrier.wait()
+            if r == 0:
+                res = bufs[0] + bufs[1] if op == pkg.REDUCE_SUM else torch.maximum(bufs[0], bufs[1])
+                bufs[0].copy_(res)
+                bufs[1].copy_(res)
+                torch.cuda.synchronize()
+            barrier.wait()
+            return 0
+        return allreduce
+
+    def run(r):
+        try:
+            models[r] = pkg.complete_fit_sharded(scheds[r], halves[r], make_allreduce(r))
+        except Exception as ex:  # noqa: BLE001
+            errors.append(ex)
+            barrier.abort()
+
+    threads = [threading.Thread(target=run, args=(r,)) for r in range(2)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=300)
+    assert not errors, errors
+    a, b = models
+    assert (a.n_rounds, a.n_steps) == (b.n_rounds, b.n_steps) == (int(g["n_iter"]), len(g["feats"]))
+    for (fa, ca, ia), (fb, cb, ib) in zip(a.steps(), b.steps()):
+        assert fa == fb and np.array_equal(ca, cb) and ia == ib          # identical on both ranks
+    assert rel_err(a.transform(X), g["completed"]) < RTOL
+    assert rel_err(b.transform(g["Xq"]), g["q_out"]) < RTOL
+    for m in models:
+        m.close()
+    for s in scheds:
+        s.close()
+
+
+def _fit_worker(rank, world, port, errs):
+    try:
+        import sys
+
+        sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+        import torch
+        import torch.distributed as dist
+
+        import __graft_entry__ as entry
+
+        pkg = entry.load_package()
+        torch.cuda.set_device(rank)
+        dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world,
+                                device_id=torch.device("cuda", rank))
+        g = np.load([p for p in GOLD if "synth_400x72" in p][0])
+        X = g["X"]
+        lo, hi = (0, 170) if rank == 0 else (170, 400)
+        sch = pkg.Scheduler(rank)
+        m = pkg.complete_fit_sharded(sch, X[lo:hi], pkg.torch_allreduce())
+        assert m.n_rounds == int(g["n_iter"]) and m.n_steps == len(g["feats"])
+        assert rel_err(m.transform(X), g["completed"]) < RTOL
+        m.close()
+        sch.close()
+        dist.destroy_process_group()
+    except Exception as ex:  # noqa: BLE001
+        errs.put(f"rank {rank}: {type(ex).__name__}: {ex}")
+        raise
+
+
+def test_row_sharded_fit_two_ranks_nccl():
+    import socket
+
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    errs = ctx.Queue()
+    procs = [ctx.Process(target=_fit_worker, args=(r, 2, port, errs)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=600)
+    msgs = []
+    while not errs.empty():
+        msgs.append(errs.get())
+    assert not msgs, msgs
+    assert all(p.exitcode == 0 for p in procs)
