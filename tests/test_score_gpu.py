@@ -278,3 +278,57 @@ def test_baseline_config2_full_size_properties(sched, oracle_mod, synth):
     pick = np.random.default_rng(2).choice(50_000, size=32, replace=False)
     w = oracle_mod.Oracle(preds, cluster).score_batch(synth.Pods(app=pods.app[pick], slo=pods.slo[pick]), normalize=True)
     assert np.array_equal(w[0], nrm[pick]) and np.array_equal(w[1], sel[pick]) and np.array_equal(w[2], best[pick])
+
+
+def test_exact_integer_boundaries(sched, oracle_mod, synth):
+    """Scores that land EXACTLY on integers: SLO == conf - interf gives t = 0, so the term is 1 (pos:
+    tmp = 100, 50, 33.33.., 25 ...) — and near misses one float32 ulp away.  Truncation must agree bit
+    for bit wherever the float64 value sits relative to the integer."""
+    rng = np.random.default_rng(17)
+    A = 48
+    preds = synth.make_predictions(A)
+    # round the tables to few bits so that many exact cancellations occur
+    preds.conf = np.round(preds.conf / 8).astype(np.float32) * 8
+    preds.interf = np.round(preds.interf / 4).astype(np.float32) * 4
+    cluster = synth.make_cluster(200, A, 8, seed=23)
+    cluster.res_slo = (np.round(cluster.res_slo / 8) * 8).astype(np.float32)
+    app = rng.integers(0, A, size=1500).astype(np.uint32)
+    # candidate SLOs drawn from the set {conf - k*4}: hits t == 0 on empty GPUs and small multiples elsewhere
+    col = rng.integers(0, preds.conf.shape[1], size=1500)
+    slo = preds.conf[app, col] - 4.0 * rng.integers(-3, 4, size=1500)
+    slo = np.where(rng.random(1500) < 0.3, np.nextafter(slo.astype(np.float32), np.float32(np.inf)), slo)
+    slo = np.where(rng.random(1500) < 0.3, np.nextafter(slo.astype(np.float32), np.float32(-np.inf)), slo)
+    pods = synth.Pods(app=app, slo=np.maximum(slo, 1.0).astype(np.float32))
+    _check(sched, oracle_mod, preds, cluster, pods)
+    raw, _, _ = sched.score_batch(pods, normalize=False)
+    assert (raw == 100).any() and (raw == 50).any()      # the exact cases are really present
+
+
+def test_best_only_and_thread_safety(pkg, sched, oracle_mod, synth):
+    """out_score/out_sel may be NULL (decisions only); entry points are safe to call from several
+    threads on one context (the framework calls Score from 16 goroutines)."""
+    import threading
+
+    preds, cluster, pods = synth.make_workload(400, 120, gpus_per_node=8, n_apps=40)
+    sched.upload_predictions(preds)
+    sched.upload_cluster(cluster)
+    want = oracle_mod.Oracle(preds, cluster).score_batch(pods, normalize=True)
+    score, sel, best = sched.score_batch(pods, normalize=True, want_matrices=False)
+    assert score is None and sel is None and np.array_equal(best, want[2])
+    errors = []
+
+    def worker(seed):
+        try:
+            for _ in range(5):
+                got = sched.score_batch(pods, normalize=True, direct=bool(seed & 1))
+                assert all(np.array_equal(a, b) for a, b in zip(want, got))
+                assert sched.normalize_scores([3, 9, 6]).tolist() == [0, 100, 50]
+        except Exception as ex:  # noqa: BLE001
+            errors.append(ex)
+
+    threads = [threading.Thread(target=worker, args=(i,)) for i in range(8)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=120)
+    assert not errors, errors
