@@ -35,15 +35,16 @@ namespace gs {
 
 constexpr int kLutSize = 64;  // counts the {1/c, c} table covers
 
+template <int GT>
 struct FastSmem {
-  double2 kkcst[kFastMaxGpus][2][kTile];  // [g][0 = neg, 1 = pos][thread] = {kk, cst}
-  uint16_t zinf[kFastMaxGpus][kTile];     // int64(tmp) when the candidate's term is 0: neg | pos << 8
-  double2 lut[kLutSize];                  // {RN(1/c), (double)c}
+  double2 kkcst[GT][2][kTile];  // [g][0 = neg, 1 = pos][thread] = {kk, cst}
+  uint16_t zinf[GT][kTile];     // int64(tmp) when the candidate's term is 0: neg | pos << 8
+  double2 lut[kLutSize];        // {RN(1/c), (double)c}
   PodRec pods[kStage];
   uint32_t key[kTile / 32][kStage];
   uint32_t neg[kTile / 32][kStage];
 };
-static_assert(sizeof(FastSmem) <= 48 * 1024, "static shared memory");
+static_assert(sizeof(FastSmem<kFastMaxGpus>) <= 48 * 1024, "static shared memory");
 static_assert(kStage == kTile, "a CTA stages its pods with one thread each");
 
 // m / c for a count c: the table form where its preconditions hold, IEEE division otherwise
@@ -160,7 +161,9 @@ cudaError_t launch_transpose_interf(const float* interf, float* interf_t, int n_
 
 // ------------------------------------------------------------------ main kernel ------
 
-template <bool kTable>
+// GT = GPU slots the unrolled loops cover: the smallest of 2, 4, 8 that holds max_gpus, so that
+// clusters with few GPUs per node do not pay for eight.
+template <bool kTable, int GT>
 __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTables T, StageA stage, const PodRec* __restrict__ pods,
                                                              const ChunkDesc* __restrict__ chunks,
                                                              const uint32_t* __restrict__ n_chunks,
@@ -168,8 +171,8 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
                                                              uint8_t* __restrict__ out_sel,
                                                              unsigned long long* hi_arg,
                                                              unsigned long long* neg_lo) {
-  __shared__ FastSmem sm_storage;
-  FastSmem* sm = &sm_storage;
+  __shared__ FastSmem<GT> sm_storage;
+  FastSmem<GT>* sm = &sm_storage;
   if (blockIdx.x >= *n_chunks) return;
   const int tid = threadIdx.x;
   const ChunkDesc cd = chunks[blockIdx.x];
@@ -199,11 +202,11 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
   // evaluate to tmp = 0 + 100*((0*(0+v))/1) = 0: they can never win (a GPU needs
   // int64(tmp) >= 1), so the streamlined loop needs no guard.
   // register-resident per-GPU state of the streamlined loop
-  double base_n[kFastMaxGpus], base_p[kFastMaxGpus];
-  float cand_interf[kFastMaxGpus];
-  uint32_t lut_off[kFastMaxGpus];  // byte offsets of the neg (low half) / pos (high half) count in lut
+  double base_n[GT], base_p[GT];
+  float cand_interf[GT];
+  uint32_t lut_off[GT];  // byte offsets of the neg (low half) / pos (high half) count in lut
 #pragma unroll
-  for (int g = 0; g < kFastMaxGpus; ++g) {
+  for (int g = 0; g < GT; ++g) {
     base_n[g] = 0.0;
     base_p[g] = 0.0;
     cand_interf[g] = 0.f;
@@ -265,9 +268,9 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
       // sums written by stage_a_kernel, slot-contiguous (coalesced across the tile): all loads
       // first, then the folds as eight independent chains
       const size_t st_row = (size_t)(app_known ? app : (uint32_t)T.n_apps) * stage.stride + (size_t)node * T.max_gpus;
-      uint32_t cntr[kFastMaxGpus];
+      uint32_t cntr[GT];
 #pragma unroll
-      for (int g = 0; g < kFastMaxGpus; ++g) {
+      for (int g = 0; g < GT; ++g) {
         cntr[g] = 0;
         if (g < k) {
           // read once: streaming loads, so that the table does not push half-written output
@@ -279,7 +282,7 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
         }
       }
 #pragma unroll
-      for (int g = 0; g < kFastMaxGpus; ++g) {
+      for (int g = 0; g < GT; ++g) {
         if (g < k) {
           GpuAcc acc = {base_n[g], base_p[g], (int)(cntr[g] & 0xFFFFu), (int)(cntr[g] >> 16)};
           fold(g, acc, cand_interf[g], &lut_off[g]);
@@ -288,11 +291,11 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
     } else {
       // walk the resident lists (a rolled loop: its results go through thread-local arrays)
       const float* itab = T.interf + (size_t)(model - 1) * A * A;
-      double l_bn[kFastMaxGpus], l_bp[kFastMaxGpus];
-      float l_ci[kFastMaxGpus];
-      uint32_t l_off[kFastMaxGpus];
+      double l_bn[GT], l_bp[GT];
+      float l_ci[GT];
+      uint32_t l_off[GT];
 #pragma unroll
-      for (int g = 0; g < kFastMaxGpus; ++g) {
+      for (int g = 0; g < GT; ++g) {
         l_bn[g] = 0.0;
         l_bp[g] = 0.0;
         l_ci[g] = 0.f;
@@ -322,7 +325,7 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
         l_ci[g] = ci;
       }
 #pragma unroll
-      for (int g = 0; g < kFastMaxGpus; ++g) {
+      for (int g = 0; g < GT; ++g) {
         base_n[g] = l_bn[g];
         base_p[g] = l_bp[g];
         cand_interf[g] = l_ci[g];
@@ -359,7 +362,7 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
         int score = 0;
         unsigned sel = kSelNone;
 #pragma unroll
-        for (int g = 0; g < kFastMaxGpus; ++g) {
+        for (int g = 0; g < GT; ++g) {
           const float d = __fsub_rn(conf, cand_interf[g]);
           const float e = __fsub_rn(pr.slo, d);
           const unsigned z = sm->zinf[g][tid];
@@ -386,7 +389,7 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
           const float2 nconf2 = make_float2(-conf, -conf);
           const float2 slo2 = make_float2(pr.slo, pr.slo), inv2 = make_float2(pr.inv_slo, pr.inv_slo);
 #pragma unroll
-          for (int gp = 0; gp < kFastMaxGpus / 2; ++gp) {
+          for (int gp = 0; gp < GT / 2; ++gp) {
             const float2 nd2 = __fadd2_rn(make_float2(cand_interf[2 * gp], cand_interf[2 * gp + 1]), nconf2);
             const float2 t2 = __fmul2_rn(inv2, __fadd2_rn(slo2, nd2));
 #pragma unroll
@@ -408,11 +411,11 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
               const double S = __dadd_rn(neg ? base_n[g] : base_p[g], v);
               const double q = div_small_int(__dmul_rn(kc.x, S), rc.x, rc.y);
               const int si = floor_nonneg(__dadd_rn(kc.y, __dmul_rn(100.0, q)));
-              best = max(best, si * 8 + (kFastMaxGpus - 1 - g));
+              best = max(best, si * 8 + (GT - 1 - g));
             }
           }
           const int score = best >> 3;
-          const unsigned sel = score > 0 ? (unsigned)(kFastMaxGpus - 1 - (best & 7)) : kSelNone;
+          const unsigned sel = score > 0 ? (unsigned)(GT - 1 - (best & 7)) : kSelNone;
           if (has_cand) packed = (score << 8) | (int)sel;
         } else if (has_cand) {
           unsigned selbyte;
@@ -462,12 +465,18 @@ cudaError_t launch_stage_a(const DevTables& T, const uint32_t* counts, const Sta
 cudaError_t launch_score_main(const DevTables& T, const PodScratch& sc, uint8_t* score, uint8_t* sel,
                               unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s) {
   dim3 grid(sc.max_chunks, (unsigned)((T.n_nodes + kTile - 1) / kTile));
-  if (sc.stage.n0)
-    score_fast_kernel<true><<<grid, kTile, 0, s>>>(T, sc.stage, sc.sorted, sc.chunks, sc.n_chunks, score, sel, hi_arg,
-                                                   neg_lo);
-  else
-    score_fast_kernel<false><<<grid, kTile, 0, s>>>(T, sc.stage, sc.sorted, sc.chunks, sc.n_chunks, score, sel,
-                                                    hi_arg, neg_lo);
+#define GS_LAUNCH_FAST(TABLE, GT)                                                                                  \
+  score_fast_kernel<TABLE, GT><<<grid, kTile, 0, s>>>(T, sc.stage, sc.sorted, sc.chunks, sc.n_chunks, score, sel, \
+                                                      hi_arg, neg_lo)
+  const bool table = sc.stage.n0 != nullptr;
+  if (T.max_gpus <= 2) {
+    if (table) GS_LAUNCH_FAST(true, 2); else GS_LAUNCH_FAST(false, 2);
+  } else if (T.max_gpus <= 4) {
+    if (table) GS_LAUNCH_FAST(true, 4); else GS_LAUNCH_FAST(false, 4);
+  } else {
+    if (table) GS_LAUNCH_FAST(true, 8); else GS_LAUNCH_FAST(false, 8);
+  }
+#undef GS_LAUNCH_FAST
   return cudaGetLastError();
 }
 
