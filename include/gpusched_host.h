@@ -84,6 +84,9 @@ GS_API int gsp_plugin_prescore(gsp_plugin* p, const char* pod_name, const char* 
  * node, :798-801; GetSLOs failure, :544-548). */
 GS_API int gsp_plugin_score(gsp_plugin* p, const char* node_name, int64_t* out_score, char* out_uuid,
                             int uuid_cap);
+/* Score for every node of the builder, in node order: what the framework's 16 workers collect
+ * by calling Score once per node (nodes whose Score fails get -1).  For replay drivers. */
+GS_API int gsp_plugin_score_all(gsp_plugin* p, int64_t* out_scores, int n);
 /* NormalizeScore (gpu_plugins.go:816-841) on the framework's list; always succeeds (:840). */
 GS_API int gsp_plugin_normalize_score(gsp_plugin* p, int64_t* scores, int n);
 

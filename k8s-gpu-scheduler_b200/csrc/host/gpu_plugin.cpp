@@ -374,6 +374,13 @@ int gsp_plugin_score(gsp_plugin* p, const char* node_name, int64_t* out_score, c
   return GSP_SUCCESS;
 }
 
+int gsp_plugin_score_all(gsp_plugin* p, int64_t* out_scores, int n) {
+  if (!p || !out_scores || n != (int)p->b->nodes.size() || !p->have_row) return GSP_ERROR;
+  for (int i = 0; i < n; ++i)
+    out_scores[i] = (p->b->nodes[i].slo_error && p->b->redis_reachable) ? -1 : (int64_t)p->row_score[i];
+  return GSP_SUCCESS;
+}
+
 int gsp_plugin_normalize_score(gsp_plugin* p, int64_t* scores, int n) {
   if (!p) return GSP_ERROR;
   gs_normalize_scores(p->ctx, scores, n);  // the reference's NormalizeScore always returns nil (:840)

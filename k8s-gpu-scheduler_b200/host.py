@@ -45,6 +45,7 @@ def _lib():
     L.gsp_plugin_prescore.argtypes = [vp, cp, cp]
     L.gsp_plugin_score.argtypes = [vp, cp, C.POINTER(C.c_int64), C.c_char_p, C.c_int]
     L.gsp_plugin_normalize_score.argtypes = [vp, vp, C.c_int]
+    L.gsp_plugin_score_all.argtypes = [vp, vp, C.c_int]
     L._gsp_ready = True
     return L
 
@@ -54,7 +55,7 @@ HOST_EXPORTS = [
     "gsp_builder_add_node", "gsp_builder_add_pod", "gsp_builder_set_redis_reachable", "gsp_builder_app_of",
     "gsp_parse_slo", "gsp_builder_build", "gsp_builder_cluster", "gsp_builder_predictions", "gsp_builder_last_error",
     "gsp_plugin_create", "gsp_plugin_destroy", "gsp_plugin_name", "gsp_plugin_last_status", "gsp_plugin_prescore",
-    "gsp_plugin_score", "gsp_plugin_normalize_score",
+    "gsp_plugin_score", "gsp_plugin_score_all", "gsp_plugin_normalize_score",
 ]
 
 
@@ -160,6 +161,13 @@ class Plugin:
         buf = C.create_string_buffer(128)
         rc = self._L.gsp_plugin_score(self._h, _enc(node_name), C.byref(s), buf, 128)
         return int(s.value), rc, self._L.gsp_plugin_last_status(self._h).decode(), buf.value.decode()
+
+    def score_all(self, n_nodes, out=None):
+        a = out if out is not None else np.empty(n_nodes, dtype=np.int64)
+        rc = self._L.gsp_plugin_score_all(self._h, a.ctypes.data_as(C.c_void_p), int(n_nodes))
+        if rc != 0:
+            raise RuntimeError("gsp_plugin_score_all: " + self._L.gsp_plugin_last_status(self._h).decode())
+        return a
 
     def normalize_score(self, scores):
         a = np.ascontiguousarray(scores, dtype=np.int64).copy()
