@@ -17,7 +17,7 @@ def _write_tsv(path, index, columns, X):
 
 
 def test_find_index_for_request(pkg):
-    from k8s_gpu_scheduler_b200 import recommender as rec
+    from k8s_gpu_scheduler_b200 import recom_service as rec
 
     idx = ["onnx_mobilenet_1024", "onnx_mobilenet_2048", "tensorflow_resnet50_1024"]
     assert rec.find_index_for_request("onnx_mobilenet_2048_abcde", idx) == "onnx_mobilenet_2048"
@@ -28,7 +28,7 @@ def test_find_index_for_request(pkg):
 @pytest.mark.gpu
 def test_replies_match_reference_imputer_and_reload(pkg, sched, oracle_mod, tmp_path):
     from k8s_gpu_scheduler_b200 import host
-    from k8s_gpu_scheduler_b200 import recommender as rec
+    from k8s_gpu_scheduler_b200 import recom_service as rec
 
     names = np.load(os.path.join(GOLD, "recommender_table_names.npz"))
     gc = np.load(os.path.join(GOLD, "impute_configurations.npz"))
