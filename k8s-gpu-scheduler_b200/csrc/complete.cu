@@ -18,6 +18,8 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
+#include <memory>
 #include <mutex>
 #include <new>
 #include <vector>
@@ -194,15 +196,101 @@ __global__ void __launch_bounds__(256) gram_partial_kernel(const double* __restr
 }
 
 // G[a][b] = sum over parts (fixed order: deterministic), mirrored to the lower triangle
-__global__ void gram_reduce_kernel(const double* __restrict__ partial, int d, int parts, double* __restrict__ G) {
+__global__ void gram_reduce_kernel(const double* __restrict__ partial, int d, int parts, int tile,
+                                   double* __restrict__ G) {
   int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= d * d) return;
   int a = idx / d, b = idx % d;
-  if (b / kGramTile < a / kGramTile) return;  // tile not computed; filled by its mirror
+  if (b / tile < a / tile) return;  // tile not computed; filled by its mirror
   double s = 0.0;
   for (int p = 0; p < parts; ++p) s += partial[(size_t)p * d * d + idx];
   G[idx] = s;
-  if (a / kGramTile != b / kGramTile) G[(size_t)b * d + a] = s;
+  if (a / tile != b / tile) G[(size_t)b * d + a] = s;
+}
+
+// The same partial Gram for wide tables (d >= 128): 128x128 output tile per CTA, 8x8 outputs per
+// thread (64 independent DFMA chains), rows streamed 16 at a time through shared memory with the
+// next slab prefetched into registers.  Bound: the FP64 pipe (2*128*128*16 flop per 32 KB staged).
+// Thread (ty,tx) owns rows {2ty,2ty+1}+32i and columns {2tx,2tx+1}+32i, i=0..3, so that every
+// 128-bit shared load of a warp is contiguous (no bank conflicts) or a broadcast.
+constexpr int kBT = 128, kBK = 16;
+
+__global__ void __launch_bounds__(256, 1) gram128_partial_kernel(const double* __restrict__ Xt,
+                                                                const uint8_t* __restrict__ mask, int n, int d,
+                                                                int j, const double* __restrict__ mu,
+                                                                int rows_per_part, double* __restrict__ partial) {
+  if (blockIdx.x < blockIdx.y) return;
+  __shared__ __align__(16) double sa[kBK][kBT];
+  __shared__ __align__(16) double sb[kBK][kBT];
+  const int a0 = blockIdx.y * kBT, b0 = blockIdx.x * kBT;
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int r_begin = blockIdx.z * rows_per_part;
+  const int r_end = min(n, r_begin + rows_per_part);
+  // staging role: 2048 elements per matrix and slab, 8 per thread: row = e / 128, col = e % 128
+  const int lrow = tid >> 4;          // 0..15: one slab row per 16 threads
+  const int lcol = (tid & 15) * 8;    // 8 consecutive columns
+  double acc[8][8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[i][k] = 0.0;
+  double pa[8], pb[8];
+  auto fetch = [&](int r0) {
+    const int r = r0 + lrow;
+    const bool live = r < r_end && !mask[(size_t)r * d + j];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const int ca = a0 + lcol + q, cb = b0 + lcol + q;
+      pa[q] = (live && ca < d) ? Xt[(size_t)r * d + ca] - mu[ca] : 0.0;
+      pb[q] = (live && cb < d) ? Xt[(size_t)r * d + cb] - mu[cb] : 0.0;
+    }
+  };
+  auto stage = [&]() {
+#pragma unroll
+    for (int q = 0; q < 8; q += 2) {
+      *reinterpret_cast<double2*>(&sa[lrow][lcol + q]) = make_double2(pa[q], pa[q + 1]);
+      *reinterpret_cast<double2*>(&sb[lrow][lcol + q]) = make_double2(pb[q], pb[q + 1]);
+    }
+  };
+  if (r_begin < r_end) {
+    fetch(r_begin);
+    stage();
+  }
+  __syncthreads();
+  for (int r0 = r_begin; r0 < r_end; r0 += kBK) {
+    const bool more = r0 + kBK < r_end;
+    if (more) fetch(r0 + kBK);
+#pragma unroll
+    for (int kk = 0; kk < kBK; ++kk) {
+      double av[8], bv[8];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const double2 a2 = *reinterpret_cast<const double2*>(&sa[kk][2 * ty + 32 * i]);
+        const double2 b2 = *reinterpret_cast<const double2*>(&sb[kk][2 * tx + 32 * i]);
+        av[2 * i] = a2.x;
+        av[2 * i + 1] = a2.y;
+        bv[2 * i] = b2.x;
+        bv[2 * i + 1] = b2.y;
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[i][k] = fma(av[i], bv[k], acc[i][k]);
+    }
+    __syncthreads();
+    if (more) stage();
+    __syncthreads();
+  }
+  double* out = partial + (size_t)blockIdx.z * d * d;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int a = a0 + 2 * ty + 32 * (i >> 1) + (i & 1);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int b = b0 + 2 * tx + 32 * (k >> 1) + (k & 1);
+      if (a < d && b < d) out[(size_t)a * d + b] = acc[i][k];
+    }
+  }
 }
 
 // ---- symmetric eigendecomposition: parallel cyclic Jacobi, one CTA ----
@@ -601,12 +689,22 @@ int gs_complete_fit_sharded(gs_ctx* c, const double* X, int32_t n, int32_t d, gs
   double *dX, *dXt, *dPrev, *dMeans, *dStats, *dSums, *dMu, *dG, *dPartial, *dA, *dV, *dEv, *dCoef, *dIcpt, *dDiff;
   uint8_t* dMask;
   int *dNobs, *dIters, *dSweeps;
-  const int tiles = (d + kGramTile - 1) / kGramTile;
-  int parts = (n + 255) / 256;
-  if (parts > 128) parts = 128;
+  // Gram kernel: 128x128 tiles for wide tables, 32x32 otherwise; rows split so that the grid fills the GPU
+  const bool big_gram = d >= 128;
+  const int gtile = big_gram ? kBT : kGramTile;
+  const int tiles = (d + gtile - 1) / gtile;
+  int parts;
+  if (big_gram) {
+    const int upper = tiles * (tiles + 1) / 2;
+    parts = (2 * 148 + upper - 1) / upper;
+    if (parts > (n + 255) / 256) parts = (n + 255) / 256;
+  } else {
+    parts = (n + 255) / 256;
+    if (parts > 128) parts = 128;
+  }
   if (parts < 1) parts = 1;
   int rows_per_part = (n + parts - 1) / parts;
-  rows_per_part = (rows_per_part + kGramTile - 1) / kGramTile * kGramTile;
+  rows_per_part = (rows_per_part + 31) / 32 * 32;
   parts = (n + rows_per_part - 1) / rows_per_part;
   const int max_steps = kRounds * d;
   CK(mem.alloc(&dX, total));
@@ -651,7 +749,8 @@ int gs_complete_fit_sharded(gs_ctx* c, const double* X, int32_t n, int32_t d, gs
   const size_t bayes_smem = sizeof(double) * 6 * (size_t)(mm > 0 ? mm : 1);
   CK(cudaFuncSetAttribute(bayes_ridge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bayes_smem));
 
-  gs_model* m = new (std::nothrow) gs_model();
+  std::unique_ptr<gs_model> owner(new (std::nothrow) gs_model());  // freed on every early return
+  gs_model* m = owner.get();
   if (!m) return c->fail(GS_ERR_NOMEM, "gs_complete_fit: out of host memory");
   m->d = d;
   m->means.resize(d);
@@ -661,7 +760,6 @@ int gs_complete_fit_sharded(gs_ctx* c, const double* X, int32_t n, int32_t d, gs
   column_stats_kernel<<<d, 256, 0, s>>>(dX, n, d, dStats);
   int xrc;
   if ((xrc = exchange(dStats, 2 * (int64_t)d + 1, GS_REDUCE_SUM, s)) || (xrc = exchange(dStats + 2 * d + 1, d, GS_REDUCE_MAX, s))) {
-    delete m;
     return xrc;
   }
   finish_means_kernel<<<(d + 255) / 256, 256, 0, s>>>(dStats, d, dMeans);
@@ -671,7 +769,6 @@ int gs_complete_fit_sharded(gs_ctx* c, const double* X, int32_t n, int32_t d, gs
   if (e == cudaSuccess) e = cudaMemcpyAsync(stats.data(), dStats, sizeof(double) * stats.size(), cudaMemcpyDeviceToHost, s);
   if (e == cudaSuccess) e = cudaStreamSynchronize(s);
   if (e != cudaSuccess) {
-    delete m;
     return c->cuda_fail(e, "completion: initial imputation");
   }
   const long long n_all = (long long)stats[2 * d];  // rows over all shards
@@ -680,14 +777,13 @@ int gs_complete_fit_sharded(gs_ctx* c, const double* X, int32_t n, int32_t d, gs
   bool all_missing = true;
   for (int k = 0; k < d; ++k) {
     if (missing[k] == n_all) {
-      delete m;
       return c->fail(GS_ERR_UNSUPPORTED, "gs_complete_fit: column %d has no observed value (scikit-learn drops such "
                      "columns; not served)", k);
     }
     if (missing[k] != n_all) all_missing = false;
   }
   if (d == 1 || all_missing) {  // _iterative.py:783-789: nothing to iterate
-    *out = m;
+    *out = owner.release();
     return GS_OK;
   }
   // ascending missing fraction, stable (np.argsort(kind="mergesort")), all columns (skip_complete=False)
@@ -701,27 +797,29 @@ int gs_complete_fit_sharded(gs_ctx* c, const double* X, int32_t n, int32_t d, gs
   int step = 0;
   std::vector<double> diff(256);
   CK(cudaMemcpyAsync(dPrev, dXt, sizeof(double) * total, cudaMemcpyDeviceToDevice, s));
-  for (int rnd = 1; rnd <= kRounds; ++rnd) {
+  int max_rounds = kRounds;
+  if (const char* ov = getenv("GS_COMPLETE_MAX_ROUNDS")) max_rounds = std::max(1, std::min(kRounds, atoi(ov)));  // probing only
+  for (int rnd = 1; rnd <= max_rounds; ++rnd) {
     m->n_rounds = rnd;
     for (int oi = 0; oi < d; ++oi, ++step) {
       const int j = order[oi];
       obs_sums_kernel<<<d, 256, 0, s>>>(dXt, dMask, n, d, j, dSums);
       if ((xrc = exchange(dSums, (int64_t)d + 1, GS_REDUCE_SUM, s))) {
-        delete m;
         return xrc;
       }
       finish_mu_kernel<<<(d + 255) / 256, 256, 0, s>>>(dSums, d, dMu, dNobs);
-      gram_partial_kernel<<<dim3(tiles, tiles, parts), 256, 0, s>>>(dXt, dMask, n, d, j, dMu, rows_per_part, dPartial);
-      gram_reduce_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dPartial, d, parts, dG);
+      if (big_gram)
+        gram128_partial_kernel<<<dim3(tiles, tiles, parts), 256, 0, s>>>(dXt, dMask, n, d, j, dMu, rows_per_part, dPartial);
+      else
+        gram_partial_kernel<<<dim3(tiles, tiles, parts), 256, 0, s>>>(dXt, dMask, n, d, j, dMu, rows_per_part, dPartial);
+      gram_reduce_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dPartial, d, parts, gtile, dG);
       if ((xrc = exchange(dG, (int64_t)d * d, GS_REDUCE_SUM, s))) {
-        delete m;
         return xrc;
       }
       if (use_lib) {
         extract_minor_kernel<<<(mm * mm + 255) / 256, 256, 0, s>>>(dG, d, j, dA);
         if (cus.syevd(cus.h, CUSOLVER_EIG_MODE_VECTOR, CUBLAS_FILL_MODE_LOWER, mm, dA, mm, dEv, dWork, lwork,
                       dInfo + step) != CUSOLVER_STATUS_SUCCESS) {
-          delete m;
           return c->fail(GS_ERR_CUDA, "cusolverDnDsyevd failed at step %d", step);
         }
         // eigenvectors come back column-major in dA: V[i][k] = dA[i + k*mm]
@@ -741,14 +839,12 @@ int gs_complete_fit_sharded(gs_ctx* c, const double* X, int32_t n, int32_t d, gs
     max_row_diff_kernel<<<256, 256, 0, s>>>(dXt, dPrev, n, d, dDiff);
     max_small_kernel<<<1, 256, 0, s>>>(dDiff, 256);
     if ((xrc = exchange(dDiff, 1, GS_REDUCE_MAX, s))) {
-      delete m;
       return xrc;
     }
     e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaMemcpyAsync(diff.data(), dDiff, sizeof(double), cudaMemcpyDeviceToHost, s);
     if (e == cudaSuccess) e = cudaStreamSynchronize(s);
     if (e != cudaSuccess) {
-      delete m;
       return c->cuda_fail(e, "completion: round");
     }
     const double inf_norm = diff[0];
@@ -764,20 +860,17 @@ int gs_complete_fit_sharded(gs_ctx* c, const double* X, int32_t n, int32_t d, gs
   if (e == cudaSuccess) e = cudaMemcpyAsync(sweeps.data(), dSweeps, sizeof(int) * step, cudaMemcpyDeviceToHost, s);
   if (e == cudaSuccess) e = cudaStreamSynchronize(s);
   if (e != cudaSuccess) {
-    delete m;
     return c->cuda_fail(e, "completion: model download");
   }
   if (use_lib) e = cudaMemcpy(sweeps.data(), dInfo, sizeof(int) * step, cudaMemcpyDeviceToHost);
   if (e != cudaSuccess) {
-    delete m;
     return c->cuda_fail(e, "completion: eigen-solver status download");
   }
   for (int k = 0; k < step; ++k)
     if (use_lib ? sweeps[k] != 0 : sweeps[k] >= 60) {
-      delete m;
       return c->fail(GS_ERR_NOCONV, "gs_complete_fit: the eigen-solver did not converge at step %d", k);
     }
-  *out = m;
+  *out = owner.release();
   return GS_OK;
 }
 

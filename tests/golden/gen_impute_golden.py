@@ -50,6 +50,7 @@ def main():
     cases["synth_40x24_wide"] = synthetic(40, 24, 3, 0.25, 3)   # n_obs < d-1 for most features
     cases["synth_500x32"] = synthetic(500, 32, 6, 0.30, 4)
     cases["synth_400x72"] = synthetic(400, 72, 8, 0.30, 6)      # beyond the Jacobi range: library eigensolver path
+    cases["synth_300x136"] = synthetic(300, 136, 8, 0.25, 7)    # wide enough for the 128x128-tile Gram kernel
     for name, X in cases.items():
         with warnings.catch_warnings():
             warnings.simplefilter("ignore")
