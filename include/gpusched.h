@@ -274,6 +274,15 @@ typedef int (*gs_allreduce_fn)(double* device_buffer, int64_t count, int op, voi
 GS_API int gs_complete_fit_sharded(gs_ctx* ctx, const double* X_local, int32_t n_local, int32_t d,
                                    gs_allreduce_fn reduce, void* user, gs_model** out);
 
+/* Fit and, in the same pass, return the completed training rows (IterativeImputer.fit_transform,
+ * sklearn/impute/_iterative.py:723-873): out_completed [n_local x d] equals what
+ * gs_complete_transform would return for X_local, without replaying the steps.  reduce/user may be
+ * NULL (one context), out_completed may be NULL.  The recommender serves exactly these rows
+ * (pkg/recommender/recom_server.py:162-164 imputes rows of its own training table). */
+GS_API int gs_complete_fit_transform(gs_ctx* ctx, const double* X_local, int32_t n_local, int32_t d,
+                                     gs_allreduce_fn reduce, void* user, double* out_completed,
+                                     gs_model** out);
+
 /* Impute X [m x d] (NaN = missing) into out [m x d]; observed entries are returned
  * unchanged.  Replaces Imputer.predict, recommender.py:24-27. */
 GS_API int gs_complete_transform(gs_ctx* ctx, const gs_model* model, const double* X, int32_t m,

@@ -31,7 +31,7 @@ ERR_NAMES = {-1: "GS_ERR_INVALID", -2: "GS_ERR_CUDA", -3: "GS_ERR_STATE", -4: "G
 EXPORTS = [
     "gs_create", "gs_destroy", "gs_last_error", "gs_version", "gs_upload_cluster", "gs_upload_predictions",
     "gs_score_batch", "gs_score_raw_dev", "gs_score_raw_dev_noalloc", "gs_normalize_dev", "gs_normalize_scores", "gs_select_mig",
-    "gs_set_profiling", "gs_last_score_kernel_ms", "gs_selftest", "gs_complete_fit", "gs_complete_fit_sharded", "gs_complete_transform", "gs_model_info", "gs_model_step", "gs_model_destroy",
+    "gs_set_profiling", "gs_last_score_kernel_ms", "gs_selftest", "gs_complete_fit", "gs_complete_fit_sharded", "gs_complete_fit_transform", "gs_complete_transform", "gs_model_info", "gs_model_step", "gs_model_destroy",
 ]
 
 
@@ -88,6 +88,7 @@ def load_library():
     L.gs_selftest.argtypes = [vp, C.c_uint64, i32, C.POINTER(C.c_uint64)]
     L.gs_complete_fit.argtypes = [vp, vp, i32, i32, C.POINTER(vp)]
     L.gs_complete_fit_sharded.argtypes = [vp, vp, i32, i32, ALLREDUCE_FN, vp, C.POINTER(vp)]
+    L.gs_complete_fit_transform.argtypes = [vp, vp, i32, i32, ALLREDUCE_FN, vp, vp, C.POINTER(vp)]
     L.gs_complete_transform.argtypes = [vp, vp, vp, i32, vp]
     L.gs_model_info.argtypes = [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]
     L.gs_model_step.argtypes = [vp, i32, C.POINTER(i32), vp, C.POINTER(C.c_double)]
@@ -265,6 +266,16 @@ def complete_fit(sched: "Scheduler", X) -> CompletionModel:
     h = C.c_void_p()
     sched._check(sched._L.gs_complete_fit(sched._h, _ptr(X), int(X.shape[0]), int(X.shape[1]), C.byref(h)))
     return CompletionModel(sched, h)
+
+
+def complete_fit_transform(sched: "Scheduler", X):
+    """Imputer.fit + the completed training matrix in one pass -> (model, completed)."""
+    X = np.ascontiguousarray(X, dtype=np.float64)
+    out = np.empty_like(X)
+    h = C.c_void_p()
+    sched._check(sched._L.gs_complete_fit_transform(sched._h, _ptr(X), int(X.shape[0]), int(X.shape[1]),
+                                                    C.cast(None, ALLREDUCE_FN), None, _ptr(out), C.byref(h)))
+    return CompletionModel(sched, h), out
 
 
 def complete_fit_sharded(sched: "Scheduler", X_local, allreduce) -> CompletionModel:

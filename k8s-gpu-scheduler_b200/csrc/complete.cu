@@ -664,11 +664,16 @@ struct DevMem {
 extern "C" {
 
 int gs_complete_fit(gs_ctx* c, const double* X, int32_t n, int32_t d, gs_model** out) {
-  return gs_complete_fit_sharded(c, X, n, d, nullptr, nullptr, out);
+  return gs_complete_fit_transform(c, X, n, d, nullptr, nullptr, nullptr, out);
 }
 
 int gs_complete_fit_sharded(gs_ctx* c, const double* X, int32_t n, int32_t d, gs_allreduce_fn reduce, void* user,
                             gs_model** out) {
+  return gs_complete_fit_transform(c, X, n, d, reduce, user, nullptr, out);
+}
+
+int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, gs_allreduce_fn reduce, void* user,
+                              double* out_completed, gs_model** out) {
   using namespace gs;
   if (out) *out = nullptr;
   if (!c) return GS_ERR_INVALID;
@@ -783,6 +788,10 @@ int gs_complete_fit_sharded(gs_ctx* c, const double* X, int32_t n, int32_t d, gs
     if (missing[k] != n_all) all_missing = false;
   }
   if (d == 1 || all_missing) {  // _iterative.py:783-789: nothing to iterate
+    if (out_completed) {
+      CK(cudaMemcpyAsync(out_completed, dXt, sizeof(double) * total, cudaMemcpyDeviceToHost, s));
+      CK(cudaStreamSynchronize(s));
+    }
     *out = owner.release();
     return GS_OK;
   }
@@ -870,6 +879,11 @@ int gs_complete_fit_sharded(gs_ctx* c, const double* X, int32_t n, int32_t d, gs
     if (use_lib ? sweeps[k] != 0 : sweeps[k] >= 60) {
       return c->fail(GS_ERR_NOCONV, "gs_complete_fit: the eigen-solver did not converge at step %d", k);
     }
+  // the completed training rows: what transform(X) would return (observed entries are never written)
+  if (out_completed) {
+    CK(cudaMemcpyAsync(out_completed, dXt, sizeof(double) * total, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+  }
   *out = owner.release();
   return GS_OK;
 }

@@ -51,8 +51,8 @@ class Recommender:
 
     # -- training (recom_server.py:215-235) ------------------------------------------------
     def fit_table(self, which: str, index, columns, X):
-        model = self._pkg.complete_fit(self._sched, X)
-        completed = model.transform(X)          # the server only ever imputes rows of its own training table
+        # the server only ever imputes rows of its own training table: fit and completed rows in one pass
+        model, completed = self._pkg.complete_fit_transform(self._sched, X)
         table = _Table(index, columns, np.asarray(X, dtype=np.float64), model, completed)
         with self._lock:
             old, self._tables[which] = self._tables[which], table

@@ -33,6 +33,9 @@ def test_fit_and_transform_match_reference_imputer(pkg, sched, path):
     assert [s[0] for s in steps] == g["feats"].tolist()
     completed = m.transform(X)                       # what the recommender serves: transform(train)
     assert rel_err(completed, g["completed"]) < RTOL
+    m2, completed2 = pkg.complete_fit_transform(sched, X)   # the same rows straight out of the fit
+    assert np.allclose(completed2, completed, rtol=1e-12, atol=0) and m2.n_steps == m.n_steps
+    m2.close()
     assert np.array_equal(completed[~np.isnan(X)], X[~np.isnan(X)])   # observed entries untouched
     assert rel_err(m.transform(g["Xq"]), g["q_out"]) < RTOL
     m.close()
