@@ -468,15 +468,14 @@ __global__ void __launch_bounds__(256) bayes_ridge_kernel(const double* __restri
   double alpha = 1.0 / (yy / n + eps);  // 1/(var(y)+eps), population variance
   double lambda = 1.0;
   int it = 0;
-  auto update = [&](double al, double la, double* sse) {
+  // One round in the eigenbasis costs O(m): coef~ = b~/(s + lambda/alpha), sse, gamma, and
+  // sum(coef^2) = sum(coef~^2) (V is orthonormal).  Only the stopping rule sum|coef_old - coef| < tol
+  // lives in the original basis; since ||x||_2 <= ||x||_1 <= sqrt(m)||x||_2 and ||V x||_2 = ||x||_2,
+  // the O(m^2) product V (coef~ - coef~_old) is needed only when ||coef~ - coef~_old||_2 lies in
+  // [tol/sqrt(m), tol) — the last round or two.
+  auto round_eigen = [&](double al, double la, double* sse) {
     const double ratio = la / al;
     for (int k = tid; k < m; k += nt) s_ct[k] = s_bt[k] / (s_ev[k] + ratio);
-    __syncthreads();
-    for (int i = tid; i < m; i += nt) {  // coef = V coef~
-      double acc = 0.0;
-      for (int k = 0; k < m; ++k) acc += V[(size_t)i * v_si + (size_t)k * v_sk] * s_ct[k];
-      s_coef[i] = acc;
-    }
     double t1 = 0.0, t2 = 0.0;
     for (int k = tid; k < m; k += nt) {
       t1 += s_ct[k] * s_bt[k];
@@ -485,26 +484,50 @@ __global__ void __launch_bounds__(256) bayes_ridge_kernel(const double* __restri
     const double a = block_sum(t1, s_red), b = block_sum(t2, s_red);
     *sse = fmax(yy - 2.0 * a + b, 0.0);
   };
+  const double sqrt_m = sqrt((double)m);
   for (it = 0; it < kBrMaxIter; ++it) {
     double sse;
-    update(alpha, lambda, &sse);
-    double g = 0.0, sq = 0.0, dl = 0.0;
-    for (int k = tid; k < m; k += nt) g += (alpha * s_ev[k]) / (lambda + alpha * s_ev[k]);
-    for (int i = tid; i < m; i += nt) {
-      sq += s_coef[i] * s_coef[i];
-      dl += fabs(s_old[i] - s_coef[i]);
+    round_eigen(alpha, lambda, &sse);
+    double g = 0.0, sq = 0.0, d2 = 0.0;
+    for (int k = tid; k < m; k += nt) {
+      g += (alpha * s_ev[k]) / (lambda + alpha * s_ev[k]);
+      sq += s_ct[k] * s_ct[k];
+      const double df = s_old[k] - s_ct[k];  // s_old holds the previous round's coef~
+      d2 += df * df;
     }
     const double gamma = block_sum(g, s_red);
     const double sumsq = block_sum(sq, s_red);
-    const double delta = block_sum(dl, s_red);
+    const double dnorm = sqrt(block_sum(d2, s_red));
     lambda = (gamma + 2.0 * kBrPrior) / (sumsq + 2.0 * kBrPrior);
     alpha = (n - gamma + 2.0 * kBrPrior) / (sse + 2.0 * kBrPrior);
-    if (it != 0 && delta < kBrTol) break;
-    for (int i = tid; i < m; i += nt) s_old[i] = s_coef[i];
+    if (it != 0) {
+      bool converged = sqrt_m * dnorm < kBrTol;
+      if (!converged && dnorm < kBrTol) {  // undecided: evaluate the rule itself
+        for (int k = tid; k < m; k += nt) s_coef[k] = s_old[k] - s_ct[k];  // difference in the eigenbasis
+        __syncthreads();
+        double dl = 0.0;
+        for (int i = tid; i < m; i += nt) {
+          double acc = 0.0;
+          for (int k = 0; k < m; ++k) acc += V[(size_t)i * v_si + (size_t)k * v_sk] * s_coef[k];
+          dl += fabs(acc);
+        }
+        converged = block_sum(dl, s_red) < kBrTol;
+      }
+      if (converged) break;
+    }
+    __syncthreads();
+    for (int k = tid; k < m; k += nt) s_old[k] = s_ct[k];
     __syncthreads();
   }
   double sse;
-  update(alpha, lambda, &sse);
+  round_eigen(alpha, lambda, &sse);
+  __syncthreads();
+  for (int i = tid; i < m; i += nt) {  // coef = V coef~ with the final alpha, lambda
+    double acc = 0.0;
+    for (int k = 0; k < m; ++k) acc += V[(size_t)i * v_si + (size_t)k * v_sk] * s_ct[k];
+    s_coef[i] = acc;
+  }
+  __syncthreads();
   double dot = 0.0;
   for (int i = tid; i < m; i += nt) {
     const int gi = i < j ? i : i + 1;
