@@ -111,7 +111,7 @@ int Ctx::ensure_scratch(int n_pods) {
   if ((rc = reserve(sc_sorted, sizeof(PodRec) * (size_t)(n_pods ? n_pods : 1), "sorted pods"))) return rc;
   // residents-sum table: 24 bytes per (app bucket, GPU slot), if it fits the budget
   const size_t entries = (size_t)(n_apps + 1) * (size_t)n_nodes * (size_t)max_gpus;
-  if (entries * 24 <= stage_budget) {
+  if (n_pods >= kStageTableMinPods && entries * 24 <= stage_budget) {
     if ((rc = reserve(sc_stage, entries * 24 + 1024, "residents-sum table"))) return rc;
   }
   return GS_OK;
@@ -128,7 +128,7 @@ PodScratch Ctx::scratch_view(int n_pods) const {
   sc.stage = StageA{nullptr, nullptr, nullptr, nullptr, 0};
   const size_t entries = (size_t)(n_apps + 1) * (size_t)n_nodes * (size_t)max_gpus;
   const size_t e8 = (entries + 31) / 32 * 32;  // keep every array 256-byte aligned
-  if (entries * 24 <= stage_budget && e8 * 24 <= sc_stage.cap) {
+  if (n_pods >= kStageTableMinPods && entries * 24 <= stage_budget && e8 * 24 <= sc_stage.cap) {
     char* base = (char*)sc_stage.p;
     sc.stage.n0 = (double*)base;
     sc.stage.p0 = (double*)(base + e8 * 8);

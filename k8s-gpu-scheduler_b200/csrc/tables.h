@@ -85,9 +85,13 @@ struct PodScratch {
   StageA stage;       // n0 == nullptr: score_fast_kernel walks the resident lists itself
 };
 
+// upper bound on the work items a batch can produce: one per started kChunk per app bucket, and
+// never more than there are pods
 inline uint32_t max_chunks_for(int n_pods, int n_apps) {
-  return (uint32_t)(n_pods / kChunk + n_apps + 2);
+  const uint32_t by_buckets = (uint32_t)(n_pods / kChunk + n_apps + 2);
+  return by_buckets < (uint32_t)n_pods ? by_buckets : (uint32_t)(n_pods > 0 ? n_pods : 1);
 }
+constexpr int kStageTableMinPods = 256;  // smaller batches walk the resident lists in the scoring kernel
 
 cudaError_t launch_resident_prep(const DevTables& T, float4* res_rec, cudaStream_t s);
 cudaError_t launch_score_direct(const DevTables& T, const uint32_t* pod_app, const float* pod_slo,
