@@ -382,8 +382,11 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
           // running maximum of key = int64(tmp) * 8 + (7 - g): the highest score wins, the
           // first GPU among equals (the reference's strict `>` in visiting order)
           int best = 0;
-          const double2* kk_neg = &sm->kkcst[0][0][tid];
-          const double2* kk_pos = &sm->kkcst[0][1][tid];
+          // both branch records as 32-bit shared addresses in registers: one select + one load with
+          // an immediate offset per GPU
+          uint32_t kk_neg = (uint32_t)__cvta_generic_to_shared(&sm->kkcst[0][0][tid]);
+          uint32_t kk_pos = (uint32_t)__cvta_generic_to_shared(&sm->kkcst[0][1][tid]);
+          asm volatile("" : "+r"(kk_neg), "+r"(kk_pos));  // keep both materialised (else: select + add per GPU)
           // float32 part for two GPUs at a time with packed FADD2/FMUL2 (each half rounds like the
           // scalar instruction): -d = interf - conf (exactly -(conf - interf)), slo - d = slo + (-d)
           const float2 nconf2 = make_float2(-conf, -conf);
@@ -405,7 +408,10 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
               if (neg) w = __dadd_rn(w, 1.0);
               if (neg) w = __dmul_rn(w, w);
               const double v = rcp_ge1(__dadd_rn(1.0, w));
-              const double2 kc = (neg ? kk_neg : kk_pos)[g * 2 * kTile];
+              double2 kc;
+              asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];"
+                           : "=d"(kc.x), "=d"(kc.y)
+                           : "r"((neg ? kk_neg : kk_pos) + (uint32_t)(g * 2 * kTile * 16)));  // folds into [R+imm]
               const uint32_t off = neg ? (lut_off[g] & 0xFFFFu) : (lut_off[g] >> 16);
               const double2 rc = *reinterpret_cast<const double2*>(lut_bytes + off);
               const double S = __dadd_rn(neg ? base_n[g] : base_p[g], v);
