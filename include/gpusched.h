@@ -162,7 +162,10 @@ GS_API int gs_upload_predictions(gs_ctx* ctx, const gs_predictions* preds);
  *                                 when this is the only score plugin
  *
  * Replaces Score -> Logic (gpu_plugins.go:779-810, 455-777) for all (pod,node) pairs and
- * NormalizeScore (:816-841) for all pods.  Host buffers in, host buffers out. */
+ * NormalizeScore (:816-841) for all pods.  Host buffers in, host buffers out; out_score and
+ * out_sel may be NULL when only out_best is wanted.  Large batches are scored in slices whose
+ * results are copied out on a second stream while the next slice is being scored; pinned
+ * (page-locked) output buffers make those copies truly asynchronous. */
 GS_API int gs_score_batch(gs_ctx* ctx, const uint32_t* pod_app, const float* pod_slo,
                    const int32_t* pod_self, int32_t n_pods, uint32_t flags,
                    uint8_t* out_score, uint8_t* out_sel, int32_t* out_best);
@@ -180,7 +183,11 @@ GS_API int gs_score_batch(gs_ctx* ctx, const uint32_t* pod_app, const float* pod
  *                         concatenated int64 buffer makes them global)
  *   gs_normalize_dev      rescales d_score in place with the (global) extrema, exactly
  *                         NormalizeScore's integer arithmetic, and decodes d_best.
- * d_hi_arg and d_neg_lo are uint64[n_pods] each.  d_best may be NULL. */
+ * d_hi_arg and d_neg_lo are uint64[n_pods] each.  d_best may be NULL.
+ * The context's scratch (bucketing buffers, the per-batch residents-sum table) is shared by all
+ * calls on the context: issue them on one stream, or make sure that the GPU work of two calls does
+ * not overlap.  Growing that scratch for a larger batch allocates (and synchronises the device);
+ * see gs_score_raw_dev_noalloc for callers that cannot have that. */
 GS_API int gs_score_raw_dev(gs_ctx* ctx, const uint32_t* d_pod_app, const float* d_pod_slo,
                      const int32_t* d_pod_self, int32_t n_pods, uint32_t flags,
                      uint8_t* d_score, uint8_t* d_sel, uint64_t* d_hi_arg,
