@@ -239,7 +239,6 @@ def main():
     barrier()
 
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    kern_ms = []
     with ClockSampler(local_rank) as clocks:
         barrier()
         t_wall0 = time.perf_counter()
@@ -248,7 +247,6 @@ def main():
             a.record()
             step()
             b.record()
-            kern_ms.append(None)
         barrier()
         t_wall = time.perf_counter() - t_wall0
     step_ms = [a.elapsed_time(b) for a, b in ev]
