@@ -95,35 +95,54 @@ __global__ void fill_kernel(const double* __restrict__ X, const double* __restri
 }
 
 // ---- moments over the rows where feature j is observed ----
-// column sums (all d columns) + row count as sums[d]; one CTA per column.  Summed over ranks
-// before finish_mu_kernel divides.
-__global__ void __launch_bounds__(256) obs_sums_kernel(const double* __restrict__ Xt, const uint8_t* __restrict__ mask,
-                                                      int n, int d, int j, double* __restrict__ sums) {
-  __shared__ double s_sum[256];
-  __shared__ int s_cnt[256];
-  const int c = blockIdx.x;
-  double sum = 0.0;
-  int cnt = 0;
-  for (int r = threadIdx.x; r < n; r += blockDim.x) {
-    if (!mask[(size_t)r * d + j]) {
-      sum += Xt[(size_t)r * d + c];
-      ++cnt;
-    }
-  }
-  s_sum[threadIdx.x] = sum;
-  s_cnt[threadIdx.x] = cnt;
+// Column sums (all d columns) + row count as sums[d].  Rows are read once, coalesced: a CTA takes
+// a block of rows with thread t on columns t, t+256, ...; per-block partials are then added in
+// block order (deterministic).  Summed over ranks before finish_mu_kernel divides.
+constexpr int kSumRows = 256;  // rows per CTA
+constexpr int kSumColsPerThread = (kMaxFeatures + 255) / 256;
+
+__global__ void __launch_bounds__(256) obs_sums_partial_kernel(const double* __restrict__ Xt,
+                                                              const uint8_t* __restrict__ mask, int n, int d, int j,
+                                                              double* __restrict__ partial /*[blocks][d+1]*/) {
+  __shared__ uint8_t s_live[kSumRows];
+  __shared__ int s_cnt;
+  const int r0 = blockIdx.x * kSumRows;
+  const int rows = min(kSumRows, n - r0);
+  if (threadIdx.x == 0) s_cnt = 0;
   __syncthreads();
-  for (int s = 128; s > 0; s >>= 1) {
-    if (threadIdx.x < s) {
-      s_sum[threadIdx.x] += s_sum[threadIdx.x + s];
-      s_cnt[threadIdx.x] += s_cnt[threadIdx.x + s];
+  int live = 0;
+  if ((int)threadIdx.x < rows) live = !mask[(size_t)(r0 + threadIdx.x) * d + j];
+  s_live[threadIdx.x] = (uint8_t)live;
+  if (live) atomicAdd(&s_cnt, 1);
+  __syncthreads();
+  double acc[kSumColsPerThread];
+#pragma unroll
+  for (int q = 0; q < kSumColsPerThread; ++q) acc[q] = 0.0;
+  for (int r = 0; r < rows; ++r) {
+    if (!s_live[r]) continue;
+    const double* row = Xt + (size_t)(r0 + r) * d;
+#pragma unroll
+    for (int q = 0; q < kSumColsPerThread; ++q) {
+      const int c = threadIdx.x + q * 256;
+      if (c < d) acc[q] += row[c];
     }
-    __syncthreads();
   }
-  if (threadIdx.x == 0) {
-    sums[c] = s_sum[0];
-    if (c == 0) sums[d] = (double)s_cnt[0];
+  double* out = partial + (size_t)blockIdx.x * (d + 1);
+#pragma unroll
+  for (int q = 0; q < kSumColsPerThread; ++q) {
+    const int c = threadIdx.x + q * 256;
+    if (c < d) out[c] = acc[q];
   }
+  if (threadIdx.x == 0) out[d] = (double)s_cnt;
+}
+
+__global__ void obs_sums_reduce_kernel(const double* __restrict__ partial, int blocks, int d,
+                                       double* __restrict__ sums) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c > d) return;
+  double s = 0.0;
+  for (int b = 0; b < blocks; ++b) s += partial[(size_t)b * (d + 1) + c];
+  sums[c] = s;
 }
 
 __global__ void finish_mu_kernel(const double* __restrict__ sums, int d, double* __restrict__ mu,
@@ -714,7 +733,7 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
   cudaStream_t s = c->stream;
   const size_t total = (size_t)n * d;
   DevMem mem;
-  double *dX, *dXt, *dPrev, *dMeans, *dStats, *dSums, *dMu, *dG, *dPartial, *dA, *dV, *dEv, *dCoef, *dIcpt, *dDiff;
+  double *dX, *dXt, *dPrev, *dMeans, *dStats, *dSums, *dSumPart, *dMu, *dG, *dPartial, *dA, *dV, *dEv, *dCoef, *dIcpt, *dDiff;
   uint8_t* dMask;
   int *dNobs, *dIters, *dSweeps;
   // Gram kernel: 128x128 tiles for wide tables, 32x32 otherwise; rows split so that the grid fills the GPU
@@ -742,6 +761,8 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
   CK(mem.alloc(&dMeans, d));
   CK(mem.alloc(&dStats, 3 * (size_t)d + 1));
   CK(mem.alloc(&dSums, (size_t)d + 1));
+  const int sum_blocks = (n + kSumRows - 1) / kSumRows;
+  CK(mem.alloc(&dSumPart, (size_t)sum_blocks * ((size_t)d + 1)));
   CK(mem.alloc(&dMu, d));
   CK(mem.alloc(&dNobs, 1));
   CK(mem.alloc(&dG, (size_t)d * d));
@@ -835,7 +856,8 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
     m->n_rounds = rnd;
     for (int oi = 0; oi < d; ++oi, ++step) {
       const int j = order[oi];
-      obs_sums_kernel<<<d, 256, 0, s>>>(dXt, dMask, n, d, j, dSums);
+      obs_sums_partial_kernel<<<sum_blocks, 256, 0, s>>>(dXt, dMask, n, d, j, dSumPart);
+      obs_sums_reduce_kernel<<<(d + 1 + 255) / 256, 256, 0, s>>>(dSumPart, sum_blocks, d, dSums);
       if ((xrc = exchange(dSums, (int64_t)d + 1, GS_REDUCE_SUM, s))) {
         return xrc;
       }
