@@ -174,6 +174,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--pods", type=int, default=N_PODS)
     ap.add_argument("--nodes", type=int, default=N_NODES)
+    ap.add_argument("--apps", type=int, default=N_APPS, help="sensitivity runs only; the metric is quoted at 1024")
+    ap.add_argument("--app-dist", default="zipf", choices=["zipf", "uniform"], help="sensitivity runs only")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
@@ -199,10 +201,11 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     P, NL = args.pods, args.nodes                   # nodes per rank (weak scaling)
-    preds = pkg.synth.make_predictions(N_APPS)
-    cluster_all = pkg.synth.make_cluster(NL * world, N_APPS, GPUS_PER_NODE)
+    n_apps = args.apps
+    preds = pkg.synth.make_predictions(n_apps)
+    cluster_all = pkg.synth.make_cluster(NL * world, n_apps, GPUS_PER_NODE)
     cluster = cluster_all.shard(rank * NL, (rank + 1) * NL) if world > 1 else cluster_all
-    pods = pkg.synth.make_pods(P, N_APPS)
+    pods = pkg.synth.make_pods(P, n_apps, app_dist=args.app_dist)
 
     sch = pkg.Scheduler(local_rank)
     sch.upload_predictions(preds)
@@ -317,14 +320,14 @@ def main():
     if rank == 0:
         peak, peak_kind = measured_peak_gbs()
         kernel_ms = float(np.median(kms))
-        abytes = algorithmic_bytes(P, NL, int(cluster.res_app.size), N_APPS, preds.conf.shape[1], GPUS_PER_NODE)
+        abytes = algorithmic_bytes(P, NL, int(cluster.res_app.size), n_apps, preds.conf.shape[1], GPUS_PER_NODE)
         achieved = abytes / (kernel_ms * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32+f64", "data": "synthetic",
             "config": {"workload": workload_name(world, P, NL), "pods": P, "nodes_per_rank": NL, "gpus_per_node": GPUS_PER_NODE,
-                       "apps": N_APPS, "residents_rank0": int(cluster.res_app.size),
+                       "apps": n_apps, "app_distribution": args.app_dist, "residents_rank0": int(cluster.res_app.size),
                        "distinct_app_slo_classes": pkg.synth.distinct_classes(pods), "seed": hex(pkg.synth.SEED),
                        "l2": "flushed between timed iterations (256 MB memset, untimed); outputs 500 MB > L2",
                        "timing": "CUDA events per step on the launching stream, summed; max over ranks"},
@@ -335,7 +338,7 @@ def main():
                          # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the ncu capture in
                          # profiles/r1/ncu_traffic_score_fast_grouped256.csv (default workload only): 1.05 GB of
                          # it is the per-batch residents-sum table, the rest results + partial-sector merges
-                         "traffic": 2019169280 if (P, NL) == (N_PODS, N_NODES) else None, "peak_kind": peak_kind, "kernel": "score_fast_kernel",
+                         "traffic": 2019169280 if (P, NL, n_apps, args.app_dist) == (N_PODS, N_NODES, N_APPS, "zipf") else None, "peak_kind": peak_kind, "kernel": "score_fast_kernel",
                          "kernel_ms": kernel_ms, "algorithmic_bytes": abytes,
                          "note": "kernel is FP64-pipe / issue bound, not HBM bound (see DESIGN.md 4.2)"},
             # the roofline that actually binds: 16 float64 operations per (pod,node,GPU) against the

@@ -137,10 +137,14 @@ def make_cluster(
     )
 
 
-def make_pods(n_pods: int, n_apps: int = 1024, seed: int = SEED, p_unknown_app: float = 0.0) -> Pods:
+def make_pods(n_pods: int, n_apps: int = 1024, seed: int = SEED, p_unknown_app: float = 0.0,
+              app_dist: str = "zipf") -> Pods:
     rng = _rng(seed, 3)
-    w = 1.0 / np.arange(1, n_apps + 1, dtype=np.float64) ** 1.1  # Zipf(1.1) over the app ids
-    app = rng.choice(n_apps, size=n_pods, p=w / w.sum()).astype(np.uint32)
+    if app_dist == "uniform":  # sensitivity runs: small, equal app buckets
+        app = rng.integers(0, n_apps, size=n_pods).astype(np.uint32)
+    else:
+        w = 1.0 / np.arange(1, n_apps + 1, dtype=np.float64) ** 1.1  # Zipf(1.1) over the app ids
+        app = rng.choice(n_apps, size=n_pods, p=w / w.sum()).astype(np.uint32)
     if p_unknown_app > 0:
         app[rng.random(n_pods) < p_unknown_app] = APP_UNKNOWN
     slo = rng.uniform(10.0, 600.0, size=n_pods)
