@@ -245,30 +245,37 @@ __global__ void __launch_bounds__(256, 1) gram128_partial_kernel(const double* _
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const int r_begin = blockIdx.z * rows_per_part;
   const int r_end = min(n, r_begin + rows_per_part);
-  // staging role: 2048 elements per matrix and slab, 8 per thread: row = e / 128, col = e % 128
-  const int lrow = tid >> 4;          // 0..15: one slab row per 16 threads
-  const int lcol = (tid & 15) * 8;    // 8 consecutive columns
+  // staging role: 2048 elements per matrix and slab, 8 per thread as 4 rows x 2 adjacent columns:
+  // consecutive threads take consecutive 16-byte chunks of a row, so that the global loads are
+  // coalesced and the 128-bit shared stores conflict-free
+  const int lcol = (tid & 63) * 2;   // 2 adjacent columns
+  const int lrow0 = tid >> 6;        // rows lrow0 + 4q, q = 0..3
   double acc[8][8];
 #pragma unroll
   for (int i = 0; i < 8; ++i)
 #pragma unroll
     for (int k = 0; k < 8; ++k) acc[i][k] = 0.0;
   double pa[8], pb[8];
+  const int ca = a0 + lcol, cb = b0 + lcol;
+  const double mua0 = ca < d ? mu[ca] : 0.0, mua1 = ca + 1 < d ? mu[ca + 1] : 0.0;
+  const double mub0 = cb < d ? mu[cb] : 0.0, mub1 = cb + 1 < d ? mu[cb + 1] : 0.0;
   auto fetch = [&](int r0) {
-    const int r = r0 + lrow;
-    const bool live = r < r_end && !mask[(size_t)r * d + j];
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
-      const int ca = a0 + lcol + q, cb = b0 + lcol + q;
-      pa[q] = (live && ca < d) ? Xt[(size_t)r * d + ca] - mu[ca] : 0.0;
-      pb[q] = (live && cb < d) ? Xt[(size_t)r * d + cb] - mu[cb] : 0.0;
+    for (int q = 0; q < 4; ++q) {
+      const int r = r0 + lrow0 + 4 * q;
+      const bool live = r < r_end && !mask[(size_t)r * d + j];
+      const double* row = Xt + (size_t)r * d;
+      pa[2 * q] = (live && ca < d) ? row[ca] - mua0 : 0.0;
+      pa[2 * q + 1] = (live && ca + 1 < d) ? row[ca + 1] - mua1 : 0.0;
+      pb[2 * q] = (live && cb < d) ? row[cb] - mub0 : 0.0;
+      pb[2 * q + 1] = (live && cb + 1 < d) ? row[cb + 1] - mub1 : 0.0;
     }
   };
   auto stage = [&]() {
 #pragma unroll
-    for (int q = 0; q < 8; q += 2) {
-      *reinterpret_cast<double2*>(&sa[lrow][lcol + q]) = make_double2(pa[q], pa[q + 1]);
-      *reinterpret_cast<double2*>(&sb[lrow][lcol + q]) = make_double2(pb[q], pb[q + 1]);
+    for (int q = 0; q < 4; ++q) {
+      *reinterpret_cast<double2*>(&sa[lrow0 + 4 * q][lcol]) = make_double2(pa[2 * q], pa[2 * q + 1]);
+      *reinterpret_cast<double2*>(&sb[lrow0 + 4 * q][lcol]) = make_double2(pb[2 * q], pb[2 * q + 1]);
     }
   };
   if (r_begin < r_end) {
