@@ -33,9 +33,34 @@ bool parse_json_string_array(const char* s, std::vector<std::string>* out) {
   ++p;
   ws();
   if (*p == ']') return true;
+  auto at_end = [&]() {  // encoding/json validates the whole input first: trailing data -> error, nothing decoded
+    ws();
+    if (*p == '\0') return true;
+    out->clear();
+    return false;
+  };
   for (;;) {
     ws();
-    if (*p != '"') { out->clear(); return false; }
+    if (*p != '"') {
+      // a scalar of another type: encoding/json records an UnmarshalTypeError, leaves the element's zero
+      // value ("") and goes on; nested arrays/objects are not reproduced (list left empty)
+      const char* q = p;
+      while (*q && *q != ',' && *q != ']' && *q != '[' && *q != '{' && *q != '"') ++q;
+      std::string tok(p, q);
+      while (!tok.empty() && isspace((unsigned char)tok.back())) tok.pop_back();
+      bool scalar = tok == "null" || tok == "true" || tok == "false";
+      if (!scalar && !tok.empty()) {
+        char* endp = nullptr;
+        strtod(tok.c_str(), &endp);
+        scalar = endp && *endp == '\0';
+      }
+      if (!scalar || (*q != ',' && *q != ']')) { out->clear(); return false; }
+      out->push_back("");
+      p = q;
+      if (*p == ',') { ++p; continue; }
+      ++p;
+      return at_end();
+    }
     ++p;
     std::string cur;
     while (*p && *p != '"') {
@@ -66,7 +91,7 @@ bool parse_json_string_array(const char* s, std::vector<std::string>* out) {
     out->push_back(cur);
     ws();
     if (*p == ',') { ++p; continue; }
-    if (*p == ']') return true;
+    if (*p == ']') { ++p; return at_end(); }
     out->clear();
     return false;
   }

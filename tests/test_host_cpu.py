@@ -127,3 +127,33 @@ def test_more_than_31_uuids_is_refused(host):
     with pytest.raises(ValueError):
         b.add_node("gpu-big", json_list([f"GPU-{i}" for i in range(32)]))
     b.close()
+
+
+def test_redis_value_parsing_edge_cases(host):
+    """json.Unmarshal of the Redis value (gpu_plugins.go:541-542): arrays of strings only; anything
+    else leaves the node without UUIDs (the reference ignores the Unmarshal error)."""
+    b = host.SnapshotBuilder()
+    b.set_configurations(["app_a"], ["1P_V100"], np.ones((1, 1), np.float32))
+    cases = [
+        ('["GPU-1","GPU-2"]', 2), (' [ "GPU-1" ,\n "GPU-2" ] ', 2), ("[]", 0), ("", 0), ("null", 0), ('{"a":1}', 0),
+        ('["GPU-1", 7]', 2),            # UnmarshalTypeError: the element keeps its zero value "", decoding goes on
+        ('["GPU-\\u0031","MIG-\\"x\\""]', 2), ('["unterminated', 0),
+        ('["a"] trailing', 0),          # invalid JSON: checkValid fails before anything is decoded
+    ]
+    for i, (value, _) in enumerate(cases):
+        b.add_node(f"gpu-node-{i}", value)
+    _, cl = b.build()
+    assert cl.node_ngpu.tolist() == [n for _, n in cases]
+    b.close()
+
+
+def test_recommender_table_reader(tmp_path, pkg):
+    """The training tables are TSV with an `index` column and empty cells for unprofiled entries
+    (recom_server.py:98-102, 218-220)."""
+    from k8s_gpu_scheduler_b200 import recom_service as rec
+
+    p = tmp_path / "t.ods"
+    p.write_text("index\t1P_A30\t2P_A30\nonnx_a\t1.5\t\nonnx_b\t\t2.25\n")
+    index, columns, X = rec.read_table(str(p))
+    assert index == ["onnx_a", "onnx_b"] and columns == ["1P_A30", "2P_A30"]
+    assert X[0, 0] == 1.5 and np.isnan(X[0, 1]) and np.isnan(X[1, 0]) and X[1, 1] == 2.25
