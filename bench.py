@@ -140,7 +140,14 @@ def cpu_reference_leg(preds, cluster, pods, budget_evals_per_thread=3_000_000, s
         ora.score_batch(sub, normalize=True, threads=threads)
         times.append(time.perf_counter() - t0)
     evals = n_sample * cluster.n_nodes
+    # the same restatement on one thread (report 1 thread and all cores)
+    n_one = max(8, n_sample // max(1, threads))
+    one = type(pods)(app=pods.app[:n_one], slo=pods.slo[:n_one])
+    t0 = time.perf_counter()
+    ora.score_batch(one, normalize=True, threads=1)
+    one_thread = n_one * cluster.n_nodes / (time.perf_counter() - t0)
     return {"value": evals * len(times) / sum(times), "unit": UNIT, "cores": threads, "kind": "port",
+            "single_thread_value": one_thread,
             "sample": f"first {n_sample} of {pods.n_pods} pods x all {cluster.n_nodes} nodes ({evals} evals/step), "
                       f"oracle/score_oracle.c -O2, OpenMP over pods"}, sum(times) / len(times)
 
