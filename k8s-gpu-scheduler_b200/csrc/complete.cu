@@ -263,12 +263,17 @@ __global__ void __launch_bounds__(256, 1) gram128_partial_kernel(const double* _
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const int r = r0 + lrow0 + 4 * q;
-      const bool live = r < r_end && !mask[(size_t)r * d + j];
-      const double* row = Xt + (size_t)r * d;
-      pa[2 * q] = (live && ca < d) ? row[ca] - mua0 : 0.0;
-      pa[2 * q + 1] = (live && ca + 1 < d) ? row[ca + 1] - mua1 : 0.0;
-      pb[2 * q] = (live && cb < d) ? row[cb] - mub0 : 0.0;
-      pb[2 * q + 1] = (live && cb + 1 < d) ? row[cb + 1] - mub1 : 0.0;
+      const bool in = r < r_end;
+      const double* row = Xt + (size_t)(in ? r : r_begin) * d;
+      // the row's values are loaded whether or not feature j is observed in it (one level of load
+      // latency instead of mask -> value), and zeroed afterwards
+      const bool live = in && !mask[(size_t)(in ? r : r_begin) * d + j];
+      const double xa0 = ca < d ? row[ca] : 0.0, xa1 = ca + 1 < d ? row[ca + 1] : 0.0;
+      const double xb0 = cb < d ? row[cb] : 0.0, xb1 = cb + 1 < d ? row[cb + 1] : 0.0;
+      pa[2 * q] = (live && ca < d) ? xa0 - mua0 : 0.0;
+      pa[2 * q + 1] = (live && ca + 1 < d) ? xa1 - mua1 : 0.0;
+      pb[2 * q] = (live && cb < d) ? xb0 - mub0 : 0.0;
+      pb[2 * q + 1] = (live && cb + 1 < d) ? xb1 - mub1 : 0.0;
     }
   };
   auto stage = [&]() {
