@@ -1,8 +1,9 @@
 // Package gpusched is the cgo binding of libgpusched.so (include/gpusched.h).
 //
 // It is the only place the Go scheduler touches C.  No Go pointer is retained by C after a
-// call returns (the library copies what it needs), so the cgo pointer rules hold with
-// plain slices.  NOT BUILT in the development container (no Go toolchain there); kept next
+// call returns (the library copies what it needs): flat arguments are passed as plain slices,
+// table structs are filled with C copies of the slices (cgo forbids Go pointers inside C memory).
+// unsafe.Slice needs Go 1.17+; the reference's go.mod says 1.16 — bump it or copy in a loop.  NOT BUILT in the development container (no Go toolchain there); kept next
 // to the library so that a maintainer of dimgatz98/k8s-gpu-scheduler can vendor it under
 // pkg/gpusched.
 package gpusched
@@ -86,30 +87,55 @@ func pf(s []float32) *C.float {
 	return (*C.float)(unsafe.Pointer(&s[0]))
 }
 
+// cbuf copies a Go slice into C memory: the table structs hold pointers, and cgo forbids storing
+// Go pointers in C memory (the library copies everything to the device before it returns, so the
+// C copies are freed right after the call).
+func cbuf(p unsafe.Pointer, n int) unsafe.Pointer {
+	if n == 0 {
+		return nil
+	}
+	return C.CBytes(unsafe.Slice((*byte)(p), n))
+}
+
 func (c *Ctx) UploadCluster(cl *Cluster, nodeBase int) error {
-	// the struct holds Go pointers: build it in C memory so that cgo's checks see only
-	// pointers passed as direct arguments' pointees (allowed for the duration of the call)
-	cc := (*C.gs_cluster)(C.malloc(C.size_t(unsafe.Sizeof(C.gs_cluster{}))))
-	defer C.free(unsafe.Pointer(cc))
+	var cc C.gs_cluster
 	cc.n_nodes = C.int32_t(len(cl.NodeModel))
 	cc.max_gpus = C.int32_t(cl.MaxGPUs)
-	cc.node_model, cc.node_ngpu = p8(cl.NodeModel), p8(cl.NodeNGPU)
-	cc.gpu_off, cc.res_app, cc.res_slo = p32(cl.GPUOff), p32(cl.ResApp), pf(cl.ResSLO)
+	bufs := []unsafe.Pointer{
+		cbuf(unsafe.Pointer(p8(cl.NodeModel)), len(cl.NodeModel)),
+		cbuf(unsafe.Pointer(p8(cl.NodeNGPU)), len(cl.NodeNGPU)),
+		cbuf(unsafe.Pointer(p32(cl.GPUOff)), 4*len(cl.GPUOff)),
+		cbuf(unsafe.Pointer(p32(cl.ResApp)), 4*len(cl.ResApp)),
+		cbuf(unsafe.Pointer(pf(cl.ResSLO)), 4*len(cl.ResSLO)),
+	}
+	defer func() {
+		for _, b := range bufs {
+			C.free(b)
+		}
+	}()
+	cc.node_model, cc.node_ngpu = (*C.uint8_t)(bufs[0]), (*C.uint8_t)(bufs[1])
+	cc.gpu_off, cc.res_app, cc.res_slo = (*C.uint32_t)(bufs[2]), (*C.uint32_t)(bufs[3]), (*C.float)(bufs[4])
 	if cl.RedisReachable {
 		cc.redis_reachable = 1
-	} else {
-		cc.redis_reachable = 0
 	}
-	return c.err(C.gs_upload_cluster(c.h, cc, C.int32_t(nodeBase)))
+	return c.err(C.gs_upload_cluster(c.h, &cc, C.int32_t(nodeBase)))
 }
 
 func (c *Ctx) UploadPredictions(p *Predictions) error {
-	cp := (*C.gs_predictions)(C.malloc(C.size_t(unsafe.Sizeof(C.gs_predictions{}))))
-	defer C.free(unsafe.Pointer(cp))
+	var cp C.gs_predictions
 	cp.n_apps, cp.n_cols = C.int32_t(p.NApps), C.int32_t(p.NCols)
-	cp.conf, cp.interf = pf(p.Conf), pf(p.Interf)
-	cp.col_of = (*C.int32_t)(unsafe.Pointer(&p.ColOf[0]))
-	return c.err(C.gs_upload_predictions(c.h, cp))
+	bufs := []unsafe.Pointer{
+		cbuf(unsafe.Pointer(pf(p.Conf)), 4*len(p.Conf)),
+		cbuf(unsafe.Pointer(pf(p.Interf)), 4*len(p.Interf)),
+		cbuf(unsafe.Pointer(&p.ColOf[0]), 4*len(p.ColOf)),
+	}
+	defer func() {
+		for _, b := range bufs {
+			C.free(b)
+		}
+	}()
+	cp.conf, cp.interf, cp.col_of = (*C.float)(bufs[0]), (*C.float)(bufs[1]), (*C.int32_t)(bufs[2])
+	return c.err(C.gs_upload_predictions(c.h, &cp))
 }
 
 // ScoreBatch = Score -> Logic for every (pod,node) and NormalizeScore per pod
