@@ -87,35 +87,50 @@ __global__ void __launch_bounds__(256) stage_a_kernel(DevTables T, const uint32_
   __shared__ double s_n0[kStageTile][kStageTile + 1], s_p0[kStageTile][kStageTile + 1];
   __shared__ float s_ci[kStageTile][kStageTile + 1];
   __shared__ uint32_t s_cnt[kStageTile][kStageTile + 1];
+  // per slot of the tile: resident range and model (0 = nothing to sum), worked out once by
+  // the first warp instead of by every lane of the warp that owns the slot
+  __shared__ uint32_t s_lo[kStageTile], s_hi[kStageTile];
+  __shared__ int s_model[kStageTile];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int slots = T.n_nodes * T.max_gpus;
   const int s0 = blockIdx.x * kStageTile, a0 = blockIdx.y * kStageTile;
   const int app_idx = a0 + lane;  // bucket n_apps = pods whose app is unknown
   const bool app_known = app_idx < T.n_apps;
   const bool wanted = app_idx <= T.n_apps && counts[app_idx] > 0;
-  if (!__syncthreads_or(wanted)) return;  // no pod of these 32 apps in the batch
-  const size_t A = (size_t)T.n_apps;
-  for (int j = 0; j < kStageTile / 8; ++j) {
-    const int sl = warp * (kStageTile / 8) + j;
-    const int slot = s0 + sl;
-    GpuAcc acc = {0.0, 0.0, 0, 0};
-    float ci = 0.f;
+  if (warp == 0) {
+    const int slot = s0 + lane;
+    int model = kModelNone;
+    uint32_t lo = 0, hi = 0;
     if (slot < slots && T.redis_reachable) {
       const int node = slot / T.max_gpus, g = slot - node * T.max_gpus;
-      const int model = T.node_model[node];
-      if (model != kModelNone && g < (int)T.node_ngpu[node]) {
-        const float* itab = T.interf + (size_t)(model - 1) * A * A;
-        const float* itab_t = T.interf_t + (size_t)(model - 1) * A * A;
-        const uint32_t lo = T.gpu_off[slot], hi = T.gpu_off[slot + 1];
-        for (uint32_t r = lo; r < hi; ++r) {
-          const uint32_t ar = T.res_app[r];
-          const float4 rec = T.res_rec[r];
-          if (app_known && ar < (uint32_t)T.n_apps) ci = __fadd_rn(ci, itab_t[(size_t)ar * A + app_idx]);
-          if (rec.x != 0.0f) {
-            float interf = rec.w;
-            if (app_known) interf = __fadd_rn(interf, itab[(size_t)ar * A + app_idx]);
-            add_term(acc, rec.x, rec.y, rec.z, interf);
-          }
+      if (g < (int)T.node_ngpu[node]) model = T.node_model[node];
+      lo = T.gpu_off[slot];
+      hi = T.gpu_off[slot + 1];
+    }
+    s_model[lane] = model;
+    s_lo[lane] = lo;
+    s_hi[lane] = hi;
+  }
+  if (!__syncthreads_or(wanted)) return;  // no pod of these 32 apps in the batch
+  const size_t A = (size_t)T.n_apps;
+#pragma unroll 1
+  for (int j = 0; j < kStageTile / 8; ++j) {
+    const int sl = warp * (kStageTile / 8) + j;
+    GpuAcc acc = {0.0, 0.0, 0, 0};
+    float ci = 0.f;
+    const int model = s_model[sl];
+    if (model != kModelNone) {
+      const float* itab = T.interf + (size_t)(model - 1) * A * A + app_idx;
+      const float* itab_t = T.interf_t + (size_t)(model - 1) * A * A + app_idx;
+      const uint32_t lo = s_lo[sl], hi = s_hi[sl];
+      for (uint32_t r = lo; r < hi; ++r) {
+        const uint32_t ar = T.res_app[r];
+        const float4 rec = T.res_rec[r];
+        if (app_known && ar < (uint32_t)T.n_apps) ci = __fadd_rn(ci, itab_t[(size_t)ar * A]);
+        if (rec.x != 0.0f) {
+          float interf = rec.w;
+          if (app_known) interf = __fadd_rn(interf, itab[(size_t)ar * A]);
+          add_term(acc, rec.x, rec.y, rec.z, interf);
         }
       }
     }
