@@ -214,17 +214,73 @@ __global__ void __launch_bounds__(256) gram_partial_kernel(const double* __restr
     }
 }
 
-// G[a][b] = sum over parts (fixed order: deterministic), mirrored to the lower triangle
+// G[a][b] = sum over parts (fixed order: deterministic), mirrored to the lower triangle.  With
+// `whole` (the Gram over all rows) the parts hold the rows to leave out: G = whole - sum.
 __global__ void gram_reduce_kernel(const double* __restrict__ partial, int d, int parts, int tile,
-                                   double* __restrict__ G) {
+                                   const double* __restrict__ whole, double* __restrict__ G) {
   int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= d * d) return;
   int a = idx / d, b = idx % d;
   if (b / tile < a / tile) return;  // tile not computed; filled by its mirror
   double s = 0.0;
   for (int p = 0; p < parts; ++p) s += partial[(size_t)p * d * d + idx];
+  if (whole) s = whole[idx] - s;
   G[idx] = s;
   if (a / tile != b / tile) G[(size_t)b * d + a] = s;
+}
+
+// Wide tables keep every Gram centred at one fixed vector m (the initial column means), so that
+// sums over row sets can be added and subtracted; the centring the estimator wants follows from
+//   sum_S (x-mu)(x-mu)^T = sum_S (x-m)(x-m)^T - |S| (mu-m)(mu-m)^T,  mu = mean over S.
+__global__ void recentre_kernel(double* __restrict__ G, int d, const double* __restrict__ mu,
+                                const double* __restrict__ m, const int* __restrict__ n_obs) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= d * d) return;
+  int a = idx / d, b = idx % d;
+  G[idx] -= (double)*n_obs * ((mu[a] - m[a]) * (mu[b] - m[b]));
+}
+
+// Row j of the all-rows Gram after column j changed: partial[blk][b] = sum over the block's rows of
+// (x[r][j]-m[j]) (x[r][b]-m[b]); h_row_reduce_kernel sums the blocks in order into H[j][.] and H[.][j].
+constexpr int kHRows = 128;
+__global__ void __launch_bounds__(256) h_row_partial_kernel(const double* __restrict__ Xt, int n, int d, int j,
+                                                           const double* __restrict__ m,
+                                                           double* __restrict__ partial /*[blocks][d]*/) {
+  const int r0 = blockIdx.x * kHRows;
+  const int rows = min(kHRows, n - r0);
+  double acc[kSumColsPerThread], mc[kSumColsPerThread];
+#pragma unroll
+  for (int q = 0; q < kSumColsPerThread; ++q) {
+    const int c = threadIdx.x + q * 256;
+    acc[q] = 0.0;
+    mc[q] = c < d ? m[c] : 0.0;
+  }
+  const double mj = m[j];
+#pragma unroll 4
+  for (int r = 0; r < rows; ++r) {
+    const double* row = Xt + (size_t)(r0 + r) * d;
+    const double xj = row[j] - mj;
+#pragma unroll
+    for (int q = 0; q < kSumColsPerThread; ++q) {
+      const int c = threadIdx.x + q * 256;
+      if (c < d) acc[q] = fma(xj, row[c] - mc[q], acc[q]);
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < kSumColsPerThread; ++q) {
+    const int c = threadIdx.x + q * 256;
+    if (c < d) partial[(size_t)blockIdx.x * d + c] = acc[q];
+  }
+}
+
+__global__ void h_row_reduce_kernel(const double* __restrict__ partial, int blocks, int d, int j,
+                                    double* __restrict__ H) {
+  int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= d) return;
+  double s = 0.0;
+  for (int k = 0; k < blocks; ++k) s += partial[(size_t)k * d + b];
+  H[(size_t)j * d + b] = s;
+  H[(size_t)b * d + j] = s;
 }
 
 // The same partial Gram for wide tables (d >= 128): 128x128 output tile per CTA, 8x8 outputs per
@@ -234,8 +290,12 @@ __global__ void gram_reduce_kernel(const double* __restrict__ partial, int d, in
 // 128-bit shared load of a warp is contiguous (no bank conflicts) or a broadcast.
 constexpr int kBT = 128, kBK = 16;
 
+// kList = false: rows 0..n-1, those where feature j is observed (j < 0: every row).
+// kList = true: the rows rows[0..n-1] (a list of row numbers), all of them.
+template <bool kList>
 __global__ void __launch_bounds__(256, 1) gram128_partial_kernel(const double* __restrict__ Xt,
-                                                                const uint8_t* __restrict__ mask, int n, int d,
+                                                                const uint8_t* __restrict__ mask,
+                                                                const int* __restrict__ rows, int n, int d,
                                                                 int j, const double* __restrict__ mu,
                                                                 int rows_per_part, double* __restrict__ partial) {
   if (blockIdx.x < blockIdx.y) return;
@@ -259,21 +319,33 @@ __global__ void __launch_bounds__(256, 1) gram128_partial_kernel(const double* _
   const int ca = a0 + lcol, cb = b0 + lcol;
   const double mua0 = ca < d ? mu[ca] : 0.0, mua1 = ca + 1 < d ? mu[ca + 1] : 0.0;
   const double mub0 = cb < d ? mu[cb] : 0.0, mub1 = cb + 1 < d ? mu[cb + 1] : 0.0;
+  // list mode: the row numbers of the slab after the next one are loaded with each fetch, so
+  // that a fetch never waits for its own indices
+  int nidx[4];
+  if (kList) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int r = r_begin + lrow0 + 4 * q;
+      nidx[q] = r < r_end ? rows[r] : 0;
+    }
+  }
   auto fetch = [&](int r0) {
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const int r = r0 + lrow0 + 4 * q;
       const bool in = r < r_end;
-      const double* row = Xt + (size_t)(in ? r : r_begin) * d;
+      const size_t rr = kList ? (size_t)nidx[q] : (size_t)(in ? r : r_begin);
+      const double* row = Xt + rr * d;
       // the row's values are loaded whether or not feature j is observed in it (one level of load
       // latency instead of mask -> value), and zeroed afterwards
-      const bool live = in && !mask[(size_t)(in ? r : r_begin) * d + j];
+      const bool live = kList ? in : (in && (j < 0 || !mask[rr * d + j]));
       const double xa0 = ca < d ? row[ca] : 0.0, xa1 = ca + 1 < d ? row[ca + 1] : 0.0;
       const double xb0 = cb < d ? row[cb] : 0.0, xb1 = cb + 1 < d ? row[cb + 1] : 0.0;
       pa[2 * q] = (live && ca < d) ? xa0 - mua0 : 0.0;
       pa[2 * q + 1] = (live && ca + 1 < d) ? xa1 - mua1 : 0.0;
       pb[2 * q] = (live && cb < d) ? xb0 - mub0 : 0.0;
       pb[2 * q + 1] = (live && cb + 1 < d) ? xb1 - mub1 : 0.0;
+      if (kList) nidx[q] = r + kBK < r_end ? rows[r + kBK] : 0;
     }
   };
   auto stage = [&]() {
@@ -788,6 +860,29 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
   CK(mem.alloc(&dSweeps, max_steps));
   CK(mem.alloc(&dDiff, 256));
   CK(cudaMemcpyAsync(dX, X, sizeof(double) * total, cudaMemcpyHostToDevice, s));
+  // Wide tables: the Gram over the rows where feature j is observed is taken as (Gram over all
+  // rows, kept in dH and refreshed one row per step) minus (Gram over the rows where j is missing,
+  // listed per feature in dDead), whenever fewer rows are missing than observed.
+  double *dH = nullptr, *dHPart = nullptr;
+  int* dDead = nullptr;
+  std::vector<size_t> dead_off;
+  const int h_blocks = (n + kHRows - 1) / kHRows;
+  if (big_gram) {
+    dead_off.assign((size_t)d + 1, 0);
+    for (size_t r = 0; r < (size_t)n; ++r)
+      for (int k = 0; k < d; ++k) dead_off[k + 1] += std::isnan(X[r * d + k]) ? 1 : 0;
+    for (int k = 0; k < d; ++k) dead_off[k + 1] += dead_off[k];
+    std::vector<int> dead(dead_off[d] ? dead_off[d] : 1);
+    std::vector<size_t> cur(dead_off.begin(), dead_off.end() - 1);
+    for (size_t r = 0; r < (size_t)n; ++r)
+      for (int k = 0; k < d; ++k)
+        if (std::isnan(X[r * d + k])) dead[cur[k]++] = (int)r;
+    CK(mem.alloc(&dDead, dead.size()));
+    CK(cudaMemcpyAsync(dDead, dead.data(), sizeof(int) * dead.size(), cudaMemcpyHostToDevice, s));
+    CK(cudaStreamSynchronize(s));  // `dead` goes out of scope
+    CK(mem.alloc(&dH, (size_t)d * d));
+    CK(mem.alloc(&dHPart, (size_t)h_blocks * d));
+  }
   // eigen-solver: hand-written Jacobi up to kJacobiMax, cuSOLVER's syevd beyond
   const int mm = d - 1;
   const bool use_lib = mm > kJacobiMax;
@@ -859,6 +954,11 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
   for (int k = 0; k < d; ++k) mx = std::fmax(mx, max_abs[k]);
   const double norm_tol = kRoundTol * mx;
 
+  if (big_gram) {  // Gram over all rows, centred at the initial means
+    gram128_partial_kernel<false><<<dim3(tiles, tiles, parts), 256, 0, s>>>(dXt, dMask, nullptr, n, d, -1, dMeans,
+                                                                         rows_per_part, dPartial);
+    gram_reduce_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dPartial, d, parts, gtile, nullptr, dH);
+  }
   int step = 0;
   std::vector<double> diff(256);
   CK(cudaMemcpyAsync(dPrev, dXt, sizeof(double) * total, cudaMemcpyDeviceToDevice, s));
@@ -874,14 +974,27 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
         return xrc;
       }
       finish_mu_kernel<<<(d + 255) / 256, 256, 0, s>>>(dSums, d, dMu, dNobs);
-      if (big_gram)
-        gram128_partial_kernel<<<dim3(tiles, tiles, parts), 256, 0, s>>>(dXt, dMask, n, d, j, dMu, rows_per_part, dPartial);
-      else
+      if (big_gram) {
+        const int n_dead = (int)(dead_off[j + 1] - dead_off[j]);
+        if (2 * (size_t)n_dead < (size_t)n) {
+          int rpp = (n_dead + parts - 1) / parts;
+          rpp = (rpp + kBK - 1) / kBK * kBK;
+          gram128_partial_kernel<true><<<dim3(tiles, tiles, parts), 256, 0, s>>>(
+              dXt, dMask, dDead + dead_off[j], n_dead, d, j, dMeans, rpp > 0 ? rpp : kBK, dPartial);
+          gram_reduce_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dPartial, d, parts, gtile, dH, dG);
+        } else {
+          gram128_partial_kernel<false><<<dim3(tiles, tiles, parts), 256, 0, s>>>(dXt, dMask, nullptr, n, d, j, dMeans,
+                                                                               rows_per_part, dPartial);
+          gram_reduce_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dPartial, d, parts, gtile, nullptr, dG);
+        }
+      } else {
         gram_partial_kernel<<<dim3(tiles, tiles, parts), 256, 0, s>>>(dXt, dMask, n, d, j, dMu, rows_per_part, dPartial);
-      gram_reduce_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dPartial, d, parts, gtile, dG);
+        gram_reduce_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dPartial, d, parts, gtile, nullptr, dG);
+      }
       if ((xrc = exchange(dG, (int64_t)d * d, GS_REDUCE_SUM, s))) {
         return xrc;
       }
+      if (big_gram) recentre_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dG, d, dMu, dMeans, dNobs);
       if (use_lib) {
         extract_minor_kernel<<<(mm * mm + 255) / 256, 256, 0, s>>>(dG, d, j, dA);
         if (cus.syevd(cus.h, CUSOLVER_EIG_MODE_VECTOR, CUBLAS_FILL_MODE_LOWER, mm, dA, mm, dEv, dWork, lwork,
@@ -900,6 +1013,10 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
       }
       if (missing[j] > 0)
         predict_kernel<<<(n + 7) / 8, 256, 0, s>>>(dXt, dMask, n, d, j, dCoef + (size_t)step * (d - 1), dIcpt + step);
+      if (big_gram && dead_off[j + 1] > dead_off[j]) {  // column j changed on this rank: row/column j of dH
+        h_row_partial_kernel<<<h_blocks, 256, 0, s>>>(dXt, n, d, j, dMeans, dHPart);
+        h_row_reduce_kernel<<<(d + 255) / 256, 256, 0, s>>>(dHPart, h_blocks, d, j, dH);
+      }
       m->feat.push_back(j);
     }
     max_row_diff_kernel<<<256, 256, 0, s>>>(dXt, dPrev, n, d, dDiff);
