@@ -68,17 +68,19 @@ def test_fit_errors(pkg, sched):
     m.close()
 
 
-def test_row_sharded_fit_two_contexts_one_gpu(pkg):
+@pytest.mark.parametrize("name,cut", [("synth_500x32", 230), ("synth_300x136", 140)])
+def test_row_sharded_fit_two_contexts_one_gpu(pkg, name, cut):
     """gs_complete_fit_sharded with the rows split over two contexts (two host threads standing in for
     two ranks; the all-reduce callback sums / maximises their buffers on the device): both ranks
-    return the same model, and it matches the reference's Imputer like the unsharded fit does."""
+    return the same model, and it matches the reference's Imputer like the unsharded fit does.
+    The 136-column table takes the wide path (per-rank all-rows Gram minus the missing rows)."""
     import threading
 
     import torch
 
-    g = np.load([p for p in GOLD if "synth_500x32" in p][0])
+    g = np.load([p for p in GOLD if name in p][0])
     X = g["X"]
-    halves = [X[:230], X[230:]]
+    halves = [X[:cut], X[cut:]]
     scheds = [pkg.Scheduler(0), pkg.Scheduler(0)]
     barrier = threading.Barrier(2)
     bufs = [None, None]
