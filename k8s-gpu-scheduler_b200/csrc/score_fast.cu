@@ -18,8 +18,17 @@
 //      — so the result is bit-identical;
 //   3. streams the bucket's pods through them: per pod and GPU one reciprocal, one
 //      division by a small integer and eight other float64 operations remain.
-// kk/cst live in shared memory (one conflict-free 16-byte slot per thread, GPU and branch),
-// the sums in registers, {1/c, c} in a small shared table.
+//
+// Float32 filter.  The integer score is floor(tmp) and tmp = A + B*v with per-(GPU, branch)
+// constants A = cst + 100*kk*base/c, B = 100*kk/c and v = 1/z in (0, 1].  A float32 evaluation of
+// A + B*v (one approximate reciprocal, two fused multiply-adds) lies within kFilterErr of the
+// float64 value the reference computes (bound derived at kFilterDelta below), so whenever it is
+// farther than that from an integer its floor IS the reference's int64(tmp).  Only the few
+// (pod, node, GPU) whose estimate falls within kFilterDelta of an integer — about 2.5e-4 of them
+// — are evaluated with the exact float64 sequence (for the whole warp, chosen by a vote, so
+// there is no divergence).  The float32 constants live in shared memory (one 8-byte slot per
+// thread, GPU and branch); the exact path rebuilds kk/cst from the sums (registers, or the
+// stage-A table) when it is needed.
 //
 // Pods without an SLO (SLO 0, 10 % of the synthetic batch; also denormal SLOs) have an
 // infinite 1/SLO: the candidate's term is exactly 0 (or NaN when SLO == conf - interf), so
@@ -37,7 +46,7 @@ constexpr int kLutSize = 64;  // counts the {1/c, c} table covers
 
 template <int GT>
 struct FastSmem {
-  double2 kkcst[GT][2][kTile];  // [g][0 = neg, 1 = pos][thread] = {kk, cst}
+  float2 ab[GT][2][kTile];      // [g][0 = neg, 1 = pos][thread] = float32 {A, B}: tmp ~ A + B*v
   uint16_t zinf[GT][kTile];     // int64(tmp) when the candidate's term is 0: neg | pos << 8
   double2 lut[kLutSize];        // {RN(1/c), (double)c}
   PodRec pods[kStage];
@@ -72,6 +81,45 @@ __device__ __forceinline__ double combine_lut(double neg_sum, double pos_sum, in
     tmp = __dmul_rn(100.0, div_count(pos_sum, cp, lut));
   }
   return tmp;
+}
+
+// {kk, cst} of one branch: everything of the weighted combine that does not depend on the
+// candidate's own term, with the operations and their order as in combine() (x*1.0 and 0.0+x are
+// exact, so an absent side contributes kk = 1, cst = 0).
+__device__ __forceinline__ double2 branch_const(bool neg, double neg_sum, double pos_sum, int cn0, int cp0,
+                                                const double2* lut) {
+  double kk = 1.0, cst = 0.0;
+  if (neg) {
+    if (cp0 > 0) {  // candidate lands on the negative side, positives exist
+      const double kq = div_count((double)(cn0 + 1), cn0 + 1 + cp0, lut);
+      kk = kq;
+      cst = __dmul_rn(100.0, div_count(__dmul_rn(__dsub_rn(1.0, kq), pos_sum), cp0, lut));
+    }
+  } else if (cn0 > 0) {  // candidate lands on the positive side, negatives exist
+    const double kq = div_count((double)cn0, cn0 + cp0 + 1, lut);
+    kk = __dsub_rn(1.0, kq);
+    cst = __dmul_rn(100.0, div_count(__dmul_rn(kq, neg_sum), cn0, lut));
+  }
+  return make_double2(kk, cst);
+}
+
+// Float32 filter constants.  With A, B >= 0 and A + B <= 128 the float32 estimate
+//   est = fma(B32, rcp_approx(z32), A32),  z32 = 1 + |t|  or  fma(1 + |t|, 1 + |t|, 1)
+// differs from the reference's float64 tmp by less than
+//   u*A (rounding A) + u*B (rounding B) + 5u*B (z32: at most 3u relative, the approximate
+//   reciprocal: 2u) + u*(A + B) (the final fma)  <=  8u * 128 = 6.2e-5,   u = 2^-24,
+// plus the float64 roundings of tmp itself and of A, B (below 1e-11).  kFilterDelta leaves a
+// factor of two.
+constexpr float kFilterDelta = 1.0f / 8192.0f;  // 1.22e-4
+
+// (A, B) for one branch, or (0, 0) = "always take the exact path" when they are out of the range
+// the bound assumes.  Not rounding-critical: any error here is far below the filter's margin.
+__device__ __forceinline__ float2 filter_const(double kk, double cst, double base, int c, const double2* lut) {
+  const double rc = lut[c < kLutSize ? c : 0].x;
+  const double B = 100.0 * kk * rc;
+  const double A = cst + B * base;
+  const bool ok = c < kLutSize && A >= 0.0 && B >= 0.0 && A + B <= 128.0;  // false for NaN
+  return ok ? make_float2((float)A, (float)B) : make_float2(0.f, 0.f);
 }
 
 // ------------------------------------------------------------------ stage A ----------
@@ -176,6 +224,16 @@ cudaError_t launch_transpose_interf(const float* interf, float* interf_t, int n_
 
 // ------------------------------------------------------------------ main kernel ------
 
+// a[g] for a run-time g on an array the compiler keeps in registers (a select chain instead of
+// local memory); only the rarely taken exact path uses these
+template <typename V, int GT>
+__device__ __forceinline__ V dyn_at(const V (&a)[GT], int g) {
+  V x = a[0];
+#pragma unroll
+  for (int i = 1; i < GT; ++i) x = g == i ? a[i] : x;
+  return x;
+}
+
 // GT = GPU slots the unrolled loops cover: the smallest of 2, 4, 8 that holds max_gpus, so that
 // clusters with few GPUs per node do not pay for eight.
 template <bool kTable, int GT>
@@ -216,25 +274,29 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
   // Steps 1+2.  GPUs a node does not have (and lanes without a node) keep constants that
   // evaluate to tmp = 0 + 100*((0*(0+v))/1) = 0: they can never win (a GPU needs
   // int64(tmp) >= 1), so the streamlined loop needs no guard.
-  // register-resident per-GPU state of the streamlined loop
+  // per-GPU state: the candidate's interference sum in registers; the residents' sums and counts
+  // are only needed again by the exact path — with the stage-A table it re-reads them there, so
+  // these arrays are dead after the set-up; without it they stay in registers
   double base_n[GT], base_p[GT];
   float cand_interf[GT];
-  uint32_t lut_off[GT];  // byte offsets of the neg (low half) / pos (high half) count in lut
+  uint32_t cnts[GT];  // cnt_neg | cnt_pos << 16
 #pragma unroll
   for (int g = 0; g < GT; ++g) {
     base_n[g] = 0.0;
     base_p[g] = 0.0;
     cand_interf[g] = 0.f;
-    lut_off[g] = 16u | (16u << 16);
-    sm->kkcst[g][0][tid] = make_double2(0.0, 0.0);
-    sm->kkcst[g][1][tid] = make_double2(0.0, 0.0);
+    cnts[g] = 0u;
+    // estimate 0.5: score 0, never near an integer (GPUs the node lacks, lanes without a node)
+    sm->ab[g][0][tid] = make_float2(0.5f, 0.f);
+    sm->ab[g][1][tid] = make_float2(0.5f, 0.f);
     sm->zinf[g][tid] = 0;
   }
   __syncthreads();  // lut
   int nc_score = 0;
   unsigned nc_sel = kSelNone;
+  size_t st_row = 0;  // this thread's row of the stage-A table (kTable, scored lanes)
   // fold one GPU's sums into the per-branch constants (same operations, same order as combine())
-  auto fold = [&](int g, const GpuAcc& acc, float ci, uint32_t* off_out) {
+  auto fold = [&](int g, const GpuAcc& acc, float ci) {
     const double2* lut = sm->lut;
     const int cn0 = acc.cnt_neg, cp0 = acc.cnt_pos;
     const int si = score_int(combine_lut(acc.neg_sum, acc.pos_sum, cn0, cp0, lut));
@@ -242,35 +304,22 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
       nc_score = si;
       nc_sel = (unsigned)g;
     }
-    double kk_n = 1.0, cst_n = 0.0, kk_p = 1.0, cst_p = 0.0;
-    if (cp0 > 0) {  // candidate lands on the negative side, positives exist
-      const double kq = div_count((double)(cn0 + 1), cn0 + 1 + cp0, lut);
-      kk_n = kq;
-      cst_n = __dmul_rn(100.0, div_count(__dmul_rn(__dsub_rn(1.0, kq), acc.pos_sum), cp0, lut));
-    }
-    if (cn0 > 0) {  // candidate lands on the positive side, negatives exist
-      const double kq = div_count((double)cn0, cn0 + cp0 + 1, lut);
-      kk_p = __dsub_rn(1.0, kq);
-      cst_p = __dmul_rn(100.0, div_count(__dmul_rn(kq, acc.neg_sum), cn0, lut));
-    }
-    sm->kkcst[g][0][tid] = make_double2(kk_n, cst_n);
-    sm->kkcst[g][1][tid] = make_double2(kk_p, cst_p);
+    const double2 kn = branch_const(true, acc.neg_sum, acc.pos_sum, cn0, cp0, lut);   // {kk, cst}
+    const double2 kp = branch_const(false, acc.neg_sum, acc.pos_sum, cn0, cp0, lut);
+    sm->ab[g][0][tid] = filter_const(kn.x, kn.y, acc.neg_sum, cn0 + 1, lut);
+    sm->ab[g][1][tid] = filter_const(kp.x, kp.y, acc.pos_sum, cp0 + 1, lut);
     {  // a candidate term of exactly 0 on either side
-      const double tn = __dadd_rn(cst_n, __dmul_rn(100.0, div_count(__dmul_rn(kk_n, __dadd_rn(acc.neg_sum, 0.0)),
-                                                                   cn0 + 1, lut)));
-      const double tp = __dadd_rn(cst_p, __dmul_rn(100.0, div_count(__dmul_rn(kk_p, __dadd_rn(acc.pos_sum, 0.0)),
-                                                                   cp0 + 1, lut)));
+      const double tn = __dadd_rn(kn.y, __dmul_rn(100.0, div_count(__dmul_rn(kn.x, __dadd_rn(acc.neg_sum, 0.0)),
+                                                                  cn0 + 1, lut)));
+      const double tp = __dadd_rn(kp.y, __dmul_rn(100.0, div_count(__dmul_rn(kp.x, __dadd_rn(acc.pos_sum, 0.0)),
+                                                                  cp0 + 1, lut)));
       sm->zinf[g][tid] = (uint16_t)((unsigned)score_int(tn) | ((unsigned)score_int(tp) << 8));
     }
-    *off_out = (uint32_t)((cn0 + 1) * 16) | ((uint32_t)((cp0 + 1) * 16) << 16);
     ci_max = fmaxf(ci_max, fabsf(ci));
     // streamlined domain: finite sums and candidate interference, counts inside the table
-    const bool fin = fabs(acc.neg_sum) <= 1e300 && fabs(acc.pos_sum) <= 1e300 && fabs(cst_n) <= 1e300 &&
-                     fabs(cst_p) <= 1e300 && fabsf(ci) <= 3.0e38f;
-    if (!fin || cn0 + 1 >= kLutSize || cp0 + 1 >= kLutSize) {
-      thr_general = true;
-      *off_out = 16u | (16u << 16);  // keep the table reads in range; the result is discarded
-    }
+    const bool fin = fabs(acc.neg_sum) <= 1e300 && fabs(acc.pos_sum) <= 1e300 && fabs(kn.y) <= 1e300 &&
+                     fabs(kp.y) <= 1e300 && fabsf(ci) <= 3.0e38f;
+    if (!fin || cn0 + 1 >= kLutSize || cp0 + 1 >= kLutSize) thr_general = true;
   };
   if (scored) {
     if (model == kModelA30) {
@@ -282,25 +331,23 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
     if (kTable) {
       // sums written by stage_a_kernel, slot-contiguous (coalesced across the tile): all loads
       // first, then the folds as eight independent chains
-      const size_t st_row = (size_t)(app_known ? app : (uint32_t)T.n_apps) * stage.stride + (size_t)node * T.max_gpus;
-      uint32_t cntr[GT];
+      st_row = (size_t)(app_known ? app : (uint32_t)T.n_apps) * stage.stride + (size_t)node * T.max_gpus;
 #pragma unroll
       for (int g = 0; g < GT; ++g) {
-        cntr[g] = 0;
         if (g < k) {
           // read once: streaming loads, so that the table does not push half-written output
           // sectors out of L2
           base_n[g] = __ldcs(stage.n0 + st_row + g);
           base_p[g] = __ldcs(stage.p0 + st_row + g);
           cand_interf[g] = __ldcs(stage.ci + st_row + g);
-          cntr[g] = __ldcs(stage.cnt + st_row + g);
+          cnts[g] = __ldcs(stage.cnt + st_row + g);
         }
       }
 #pragma unroll
       for (int g = 0; g < GT; ++g) {
         if (g < k) {
-          GpuAcc acc = {base_n[g], base_p[g], (int)(cntr[g] & 0xFFFFu), (int)(cntr[g] >> 16)};
-          fold(g, acc, cand_interf[g], &lut_off[g]);
+          GpuAcc acc = {base_n[g], base_p[g], (int)(cnts[g] & 0xFFFFu), (int)(cnts[g] >> 16)};
+          fold(g, acc, cand_interf[g]);
         }
       }
     } else {
@@ -308,13 +355,13 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
       const float* itab = T.interf + (size_t)(model - 1) * A * A;
       double l_bn[GT], l_bp[GT];
       float l_ci[GT];
-      uint32_t l_off[GT];
+      uint32_t l_cnt[GT];
 #pragma unroll
       for (int g = 0; g < GT; ++g) {
         l_bn[g] = 0.0;
         l_bp[g] = 0.0;
         l_ci[g] = 0.f;
-        l_off[g] = 16u | (16u << 16);
+        l_cnt[g] = 0u;
       }
       const uint32_t* offp = T.gpu_off + (size_t)node * T.max_gpus;
       uint32_t lo = offp[0];
@@ -334,17 +381,18 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
           }
         }
         lo = hi;
-        fold(g, acc, ci, &l_off[g]);
+        fold(g, acc, ci);
         l_bn[g] = acc.neg_sum;
         l_bp[g] = acc.pos_sum;
         l_ci[g] = ci;
+        l_cnt[g] = (uint32_t)acc.cnt_neg | ((uint32_t)acc.cnt_pos << 16);
       }
 #pragma unroll
       for (int g = 0; g < GT; ++g) {
         base_n[g] = l_bn[g];
         base_p[g] = l_bp[g];
         cand_interf[g] = l_ci[g];
-        lut_off[g] = l_off[g];
+        cnts[g] = l_cnt[g];
       }
     }
     nocand = (nc_score << 8) | (int)nc_sel;
@@ -396,16 +444,31 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
         if (!((pr.orig & kPodGeneral) || __any_sync(0xFFFFFFFFu, lane_general))) {
           // running maximum of key = int64(tmp) * 8 + (7 - g): the highest score wins, the
           // first GPU among equals (the reference's strict `>` in visiting order)
-          int best = 0;
           // both branch records as 32-bit shared addresses in registers: one select + one load with
           // an immediate offset per GPU
-          uint32_t kk_neg = (uint32_t)__cvta_generic_to_shared(&sm->kkcst[0][0][tid]);
-          uint32_t kk_pos = (uint32_t)__cvta_generic_to_shared(&sm->kkcst[0][1][tid]);
-          asm volatile("" : "+r"(kk_neg), "+r"(kk_pos));  // keep both materialised (else: select + add per GPU)
+          uint32_t ab_neg = (uint32_t)__cvta_generic_to_shared(&sm->ab[0][0][tid]);
+          uint32_t ab_pos = (uint32_t)__cvta_generic_to_shared(&sm->ab[0][1][tid]);
+          asm volatile("" : "+r"(ab_neg), "+r"(ab_pos));  // keep both materialised (else: select + add per GPU)
           // float32 part for two GPUs at a time with packed FADD2/FMUL2 (each half rounds like the
           // scalar instruction): -d = interf - conf (exactly -(conf - interf)), slo - d = slo + (-d)
           const float2 nconf2 = make_float2(-conf, -conf);
           const float2 slo2 = make_float2(pr.slo, pr.slo), inv2 = make_float2(pr.inv_slo, pr.inv_slo);
+          // float32 estimate of tmp: returns floor(est), *r = est - floor(est) in [0, 1)
+          auto estimate = [&](int g, bool neg, float t, float* r) -> float {
+            const float a = 1.0f + fabsf(t);
+            const float z = neg ? fmaf(a, a, 1.0f) : a;
+            float v;
+            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(v) : "f"(z));
+            float2 ab;
+            asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];"
+                         : "=f"(ab.x), "=f"(ab.y)
+                         : "r"((neg ? ab_neg : ab_pos) + (uint32_t)(g * 2 * kTile * 8)));  // folds into [R+imm]
+            const float est = fmaf(ab.y, v, ab.x);
+            const float fl = __fadd_rz(est, 8388608.0f) - 8388608.0f;  // floor for 0 <= est < 2^22, exact
+            *r = est - fl;                                             // exact
+            return fl;
+          };
+          float fbest = 0.f, rlo = 0.5f, rhi = 0.5f;
 #pragma unroll
           for (int gp = 0; gp < GT / 2; ++gp) {
             const float2 nd2 = __fadd2_rn(make_float2(cand_interf[2 * gp], cand_interf[2 * gp + 1]), nconf2);
@@ -413,25 +476,53 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
               const int g = 2 * gp + h;
-              const bool neg = pr.slo > -(h ? nd2.y : nd2.x);
-              const float t = h ? t2.y : t2.x;
-#ifdef GS_INT_CONVERT  // measured slower on B200 (4.71 vs 4.57 ms): the conversion stays on the XU pipe
-              double w = abs_f32_to_f64_finite(t);
-#else
-              double w = fabs((double)t);
-#endif
-              if (neg) w = __dadd_rn(w, 1.0);
-              if (neg) w = __dmul_rn(w, w);
-              const double v = rcp_ge1(__dadd_rn(1.0, w));
-              double2 kc;
-              asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];"
-                           : "=d"(kc.x), "=d"(kc.y)
-                           : "r"((neg ? kk_neg : kk_pos) + (uint32_t)(g * 2 * kTile * 16)));  // folds into [R+imm]
-              const uint32_t off = neg ? (lut_off[g] & 0xFFFFu) : (lut_off[g] >> 16);
-              const double2 rc = *reinterpret_cast<const double2*>(lut_bytes + off);
-              const double S = __dadd_rn(neg ? base_n[g] : base_p[g], v);
-              const double q = div_small_int(__dmul_rn(kc.x, S), rc.x, rc.y);
-              const int si = floor_nonneg(__dadd_rn(kc.y, __dmul_rn(100.0, q)));
+              float r;
+              const float fl = estimate(g, pr.slo > -(h ? nd2.y : nd2.x), h ? t2.y : t2.x, &r);
+              rlo = fminf(rlo, r);
+              rhi = fmaxf(rhi, r);
+              fbest = fmaxf(fbest, fmaf(fl, 8.0f, (float)(GT - 1 - g)));
+            }
+          }
+          int best = (int)fbest;
+          const bool unsure = has_cand && !(rlo >= kFilterDelta && rhi <= 1.0f - kFilterDelta);
+          if (__any_sync(0xFFFFFFFFu, unsure)) {
+            // Some estimate of this warp lies within kFilterDelta of an integer: redo the pod GPU by
+            // GPU, with the exact float64 sequence wherever a lane is unsure about that GPU.
+            best = 0;
+            const double2* lut = sm->lut;
+#pragma unroll 1
+            for (int g = 0; g < GT; ++g) {
+              const float nd = __fadd_rn(dyn_at(cand_interf, g), -conf);
+              const float t = __fmul_rn(pr.inv_slo, __fadd_rn(pr.slo, nd));
+              const bool neg = pr.slo > -nd;
+              float r;
+              int si = (int)estimate(g, neg, t, &r);
+              const bool near = has_cand && !(r >= kFilterDelta && r <= 1.0f - kFilterDelta);
+              if (__any_sync(0xFFFFFFFFu, near)) {
+                double bn, bp;
+                uint32_t cn;
+                if (kTable) {
+                  const bool ld = scored && g < k;
+                  bn = ld ? stage.n0[st_row + g] : 0.0;
+                  bp = ld ? stage.p0[st_row + g] : 0.0;
+                  cn = ld ? stage.cnt[st_row + g] : 0u;
+                } else {
+                  bn = dyn_at(base_n, g);
+                  bp = dyn_at(base_p, g);
+                  cn = dyn_at(cnts, g);
+                }
+                const int cn0 = (int)(cn & 0xFFFFu), cp0 = (int)(cn >> 16);
+                double w = fabs((double)t);
+                if (neg) w = __dadd_rn(w, 1.0);
+                if (neg) w = __dmul_rn(w, w);
+                const double v = rcp_ge1(__dadd_rn(1.0, w));
+                const double2 kc = branch_const(neg, bn, bp, cn0, cp0, lut);
+                const double2 rc = lut[min(neg ? cn0 + 1 : cp0 + 1, kLutSize - 1)];  // lanes outside the domain: discarded
+                const double S = __dadd_rn(neg ? bn : bp, v);
+                const double q = div_small_int(__dmul_rn(kc.x, S), rc.x, rc.y);
+                si = floor_nonneg(__dadd_rn(kc.y, __dmul_rn(100.0, q)));
+                if (!(scored && g < k)) si = 0;  // a GPU this lane's node does not have never wins
+              }
               best = max(best, si * 8 + (GT - 1 - g));
             }
           }
