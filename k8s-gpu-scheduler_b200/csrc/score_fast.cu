@@ -295,8 +295,55 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
   int nc_score = 0;
   unsigned nc_sel = kSelNone;
   size_t st_row = 0;  // this thread's row of the stage-A table (kTable, scored lanes)
-  // fold one GPU's sums into the per-branch constants (same operations, same order as combine())
-  auto fold = [&](int g, const GpuAcc& acc, float ci) {
+  // The streamlined domain of one GPU: non-negative finite sums of ordinary size (they are sums
+  // of fewer than 64 values in (0, 1]), a finite candidate interference, counts inside the table.
+  auto in_domain = [&](const GpuAcc& acc, float ci) -> bool {
+    return acc.neg_sum >= 0.0 && acc.neg_sum <= 1.0e6 && acc.pos_sum >= 0.0 && acc.pos_sum <= 1.0e6 &&
+           fabsf(ci) <= 3.0e38f && acc.cnt_neg + acc.cnt_pos + 1 < kLutSize;  // false for NaN
+  };
+  // Fold one GPU's sums into what the pod loop needs, inside the streamlined domain: the same
+  // operations in the same order as combine() / branch_const(), every division through the table
+  // and none of them guarded.  An empty side needs no special case: its k comes out as exactly
+  // 1 or 0 (c/c and 0/c are exact) and its product as exactly 0 (lut[0] = {0, 0} turns m/0 into
+  // 0), and x*1.0, 0.0+x are exact — so the values equal the guarded form's literals 1.0 and 0.0.
+  auto fold_fast = [&](int g, const GpuAcc& acc, float ci) {
+    const double2* lut = sm->lut;
+    const int n = acc.cnt_neg, p = acc.cnt_pos;
+    const double ns = acc.neg_sum, ps = acc.pos_sum;
+    const double2 Ln = lut[n], Lp = lut[p], Lnp = lut[n + p], Lnp1 = lut[n + p + 1], Ln1 = lut[n + 1], Lp1 = lut[p + 1];
+    auto dv = [](double m, const double2& L) { return div_small_int(m, L.x, L.y); };
+    // residents only (no candidate term, :667-696)
+    const double k0 = dv((double)n, Lnp);
+    const double tmp0 = __dadd_rn(__dmul_rn(100.0, dv(__dmul_rn(__dsub_rn(1.0, k0), ps), Lp)),
+                                  __dmul_rn(100.0, dv(__dmul_rn(k0, ns), Ln)));
+    const int si = score_int(tmp0);
+    if (si > nc_score) {
+      nc_score = si;
+      nc_sel = (unsigned)g;
+    }
+    // candidate on the negative side: k = (n+1)/(n+1+p)
+    const double kk_n = dv((double)(n + 1), Lnp1);
+    const double cst_n = __dmul_rn(100.0, dv(__dmul_rn(__dsub_rn(1.0, kk_n), ps), Lp));
+    // candidate on the positive side: k = n/(n+p+1)
+    const double kq_p = dv((double)n, Lnp1);
+    const double kk_p = __dsub_rn(1.0, kq_p);
+    const double cst_p = __dmul_rn(100.0, dv(__dmul_rn(kq_p, ns), Ln));
+    // a candidate term of exactly 0 on either side (pods without an SLO)
+    const double tn = __dadd_rn(cst_n, __dmul_rn(100.0, dv(__dmul_rn(kk_n, __dadd_rn(ns, 0.0)), Ln1)));
+    const double tp = __dadd_rn(cst_p, __dmul_rn(100.0, dv(__dmul_rn(kk_p, __dadd_rn(ps, 0.0)), Lp1)));
+    sm->zinf[g][tid] = (uint16_t)((unsigned)score_int(tn) | ((unsigned)score_int(tp) << 8));
+    // float32 filter: tmp = A + B*v with A = tmp at v = 0 (tn, tp) and B = 100*kk/c; (0, 0) =
+    // "always take the exact path" outside the range the error bound assumes (see kFilterDelta)
+    const double Bn = 100.0 * kk_n * Ln1.x, Bp = 100.0 * kk_p * Lp1.x;
+    const bool okn = tn >= 0.0 && Bn >= 0.0 && tn + Bn <= 128.0, okp = tp >= 0.0 && Bp >= 0.0 && tp + Bp <= 128.0;
+    sm->ab[g][0][tid] = okn ? make_float2((float)tn, (float)Bn) : make_float2(0.f, 0.f);
+    sm->ab[g][1][tid] = okp ? make_float2((float)tp, (float)Bp) : make_float2(0.f, 0.f);
+    ci_max = fmaxf(ci_max, fabsf(ci));
+  };
+  // The same outside the domain (guarded divisions, IEEE division where the table does not reach):
+  // the residents-only score and the zero-term scores stay exact, candidates of this node go
+  // through logic_eval.
+  auto fold_general = [&](int g, const GpuAcc& acc, float ci) {
     const double2* lut = sm->lut;
     const int cn0 = acc.cnt_neg, cp0 = acc.cnt_pos;
     const int si = score_int(combine_lut(acc.neg_sum, acc.pos_sum, cn0, cp0, lut));
@@ -304,22 +351,17 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
       nc_score = si;
       nc_sel = (unsigned)g;
     }
-    const double2 kn = branch_const(true, acc.neg_sum, acc.pos_sum, cn0, cp0, lut);   // {kk, cst}
+    const double2 kn = branch_const(true, acc.neg_sum, acc.pos_sum, cn0, cp0, lut);  // {kk, cst}
     const double2 kp = branch_const(false, acc.neg_sum, acc.pos_sum, cn0, cp0, lut);
-    sm->ab[g][0][tid] = filter_const(kn.x, kn.y, acc.neg_sum, cn0 + 1, lut);
-    sm->ab[g][1][tid] = filter_const(kp.x, kp.y, acc.pos_sum, cp0 + 1, lut);
-    {  // a candidate term of exactly 0 on either side
-      const double tn = __dadd_rn(kn.y, __dmul_rn(100.0, div_count(__dmul_rn(kn.x, __dadd_rn(acc.neg_sum, 0.0)),
-                                                                  cn0 + 1, lut)));
-      const double tp = __dadd_rn(kp.y, __dmul_rn(100.0, div_count(__dmul_rn(kp.x, __dadd_rn(acc.pos_sum, 0.0)),
-                                                                  cp0 + 1, lut)));
-      sm->zinf[g][tid] = (uint16_t)((unsigned)score_int(tn) | ((unsigned)score_int(tp) << 8));
-    }
+    const double tn = __dadd_rn(kn.y, __dmul_rn(100.0, div_count(__dmul_rn(kn.x, __dadd_rn(acc.neg_sum, 0.0)),
+                                                                cn0 + 1, lut)));
+    const double tp = __dadd_rn(kp.y, __dmul_rn(100.0, div_count(__dmul_rn(kp.x, __dadd_rn(acc.pos_sum, 0.0)),
+                                                                cp0 + 1, lut)));
+    sm->zinf[g][tid] = (uint16_t)((unsigned)score_int(tn) | ((unsigned)score_int(tp) << 8));
+    sm->ab[g][0][tid] = make_float2(0.f, 0.f);
+    sm->ab[g][1][tid] = make_float2(0.f, 0.f);
     ci_max = fmaxf(ci_max, fabsf(ci));
-    // streamlined domain: finite sums and candidate interference, counts inside the table
-    const bool fin = fabs(acc.neg_sum) <= 1e300 && fabs(acc.pos_sum) <= 1e300 && fabs(kn.y) <= 1e300 &&
-                     fabs(kp.y) <= 1e300 && fabsf(ci) <= 3.0e38f;
-    if (!fin || cn0 + 1 >= kLutSize || cp0 + 1 >= kLutSize) thr_general = true;
+    thr_general = true;
   };
   if (scored) {
     if (model == kModelA30) {
@@ -343,11 +385,28 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
           cnts[g] = __ldcs(stage.cnt + st_row + g);
         }
       }
+      bool dom = true;
 #pragma unroll
       for (int g = 0; g < GT; ++g) {
         if (g < k) {
-          GpuAcc acc = {base_n[g], base_p[g], (int)(cnts[g] & 0xFFFFu), (int)(cnts[g] >> 16)};
-          fold(g, acc, cand_interf[g]);
+          const GpuAcc acc = {base_n[g], base_p[g], (int)(cnts[g] & 0xFFFFu), (int)(cnts[g] >> 16)};
+          dom = dom && in_domain(acc, cand_interf[g]);
+        }
+      }
+      if (dom) {
+#pragma unroll
+        for (int g = 0; g < GT; ++g) {
+          if (g < k) {
+            const GpuAcc acc = {base_n[g], base_p[g], (int)(cnts[g] & 0xFFFFu), (int)(cnts[g] >> 16)};
+            fold_fast(g, acc, cand_interf[g]);
+          }
+        }
+      } else {
+#pragma unroll 1
+        for (int g = 0; g < k; ++g) {  // rare: one rolled copy of the guarded code
+          const uint32_t cn = stage.cnt[st_row + g];
+          const GpuAcc acc = {stage.n0[st_row + g], stage.p0[st_row + g], (int)(cn & 0xFFFFu), (int)(cn >> 16)};
+          fold_general(g, acc, stage.ci[st_row + g]);
         }
       }
     } else {
@@ -381,7 +440,10 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
           }
         }
         lo = hi;
-        fold(g, acc, ci);
+        if (in_domain(acc, ci))
+          fold_fast(g, acc, ci);
+        else
+          fold_general(g, acc, ci);
         l_bn[g] = acc.neg_sum;
         l_bp[g] = acc.pos_sum;
         l_ci[g] = ci;
