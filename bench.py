@@ -34,6 +34,9 @@ METRIC = "pod x node Filter+Score+NormalizeScore evals/sec (50k pods x 5k nodes 
 UNIT = "evals/s"
 
 
+TRAFFIC_BYTES = 2210661584  # 1 419 842 000 read + 790 819 584 written
+
+
 def workload_name(n_ranks, pods=N_PODS, nodes=N_NODES):
     return (f"batched Filter+Score+NormalizeScore, {pods} pods x {nodes} nodes x {GPUS_PER_NODE} GPUs/node per rank"
             f" ({n_ranks} rank(s), nodes sharded)")
@@ -342,17 +345,13 @@ def main():
             "wall_ms_per_step_incl_flush": t_wall * 1e3 / args.steps,
             "clocks": clocks.summary(),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the ncu capture in
-                         # profiles/r1/ncu_traffic_score_fast_grouped256.csv (default workload only): 1.05 GB of
-                         # it is the per-batch residents-sum table, the rest results + partial-sector merges
-                         "traffic": 2019169280 if (P, NL, n_apps, args.app_dist) == (N_PODS, N_NODES, N_APPS, "zipf") else None, "peak_kind": peak_kind, "kernel": "score_fast_kernel",
+                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the ncu capture
+                         # summarised in profiles/r1/ncu_score_fast_filter.txt (default workload only): 1.05 GB
+                         # of it is the per-batch residents-sum table, the rest results, partial-sector merges
+                         # and the exact path's re-reads of the table
+                         "traffic": TRAFFIC_BYTES if (P, NL, n_apps, args.app_dist) == (N_PODS, N_NODES, N_APPS, "zipf") else None, "peak_kind": peak_kind, "kernel": "score_fast_kernel",
                          "kernel_ms": kernel_ms, "algorithmic_bytes": abytes,
-                         "note": "kernel is FP64-pipe / issue bound, not HBM bound (see DESIGN.md 4.2)"},
-            # the roofline that actually binds: 16 float64 operations per (pod,node,GPU) against the
-            # measured DFMA rate of this pool's B200 (profiles/r1/ub_alu_b200.txt: 17.19 Tlane-op/s)
-            "roofline_fp64": {"bound": "fp64_pipe", "achieved": 16.0 * GPUS_PER_NODE * P * NL / (kernel_ms * 1e-3) / 1e12,
-                              "peak": 17.19, "unit": "Tlane-op/s",
-                              "frac": 16.0 * GPUS_PER_NODE * P * NL / (kernel_ms * 1e-3) / 1e12 / 17.19},
+                         "note": "kernel is instruction-issue / latency bound, not HBM bound: a float32 filter decides floor(tmp) for all but ~2.5e-4 of the (pod,node,GPU) evaluations, which take the exact float64 sequence (DESIGN.md 4.1-4.2)"},
         }
         if e2e:
             line["e2e"] = e2e
