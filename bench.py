@@ -34,7 +34,7 @@ METRIC = "pod x node Filter+Score+NormalizeScore evals/sec (50k pods x 5k nodes 
 UNIT = "evals/s"
 
 
-TRAFFIC_BYTES = 2210661584  # 1 419 842 000 read + 790 819 584 written
+TRAFFIC_BYTES = 2204962672  # 1 395 718 000 read + 809 244 672 written
 
 
 def workload_name(n_ranks, pods=N_PODS, nodes=N_NODES):
@@ -346,7 +346,7 @@ def main():
             "clocks": clocks.summary(),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the ncu capture
-                         # summarised in profiles/r1/ncu_score_fast_filter.txt (default workload only): 1.05 GB
+                         # summarised in profiles/r1/ncu_score_fast_filter_final.txt (default workload only): 1.05 GB
                          # of it is the per-batch residents-sum table, the rest results, partial-sector merges
                          # and the exact path's re-reads of the table
                          "traffic": TRAFFIC_BYTES if (P, NL, n_apps, args.app_dist) == (N_PODS, N_NODES, N_APPS, "zipf") else None, "peak_kind": peak_kind, "kernel": "score_fast_kernel",
