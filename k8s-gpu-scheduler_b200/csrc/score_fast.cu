@@ -103,24 +103,21 @@ __device__ __forceinline__ double2 branch_const(bool neg, double neg_sum, double
   return make_double2(kk, cst);
 }
 
-// Float32 filter constants.  With A, B >= 0 and A + B <= 128 the float32 estimate
+// Float32 filter constants.  With A, B >= 0 and A + B <= kFilterMaxSum (128) the float32 estimate
 //   est = fma(B32, rcp_approx(z32), A32),  z32 = 1 + |t|  or  fma(1 + |t|, 1 + |t|, 1)
 // differs from the reference's float64 tmp by less than
 //   u*A (rounding A) + u*B (rounding B) + 5u*B (z32: at most 3u relative, the approximate
-//   reciprocal: 2u) + u*(A + B) (the final fma)  <=  8u * 128 = 6.2e-5,   u = 2^-24,
+//   reciprocal: 2u) + u*(A + B) (the final fma)  <=  8u * kFilterMaxSum = 6.2e-5,   u = 2^-24,
 // plus the float64 roundings of tmp itself and of A, B (below 1e-11).  kFilterDelta leaves a
 // factor of two.
-constexpr float kFilterDelta = 1.0f / 8192.0f;  // 1.22e-4
-
-// (A, B) for one branch, or (0, 0) = "always take the exact path" when they are out of the range
-// the bound assumes.  Not rounding-critical: any error here is far below the filter's margin.
-__device__ __forceinline__ float2 filter_const(double kk, double cst, double base, int c, const double2* lut) {
-  const double rc = lut[c < kLutSize ? c : 0].x;
-  const double B = 100.0 * kk * rc;
-  const double A = cst + B * base;
-  const bool ok = c < kLutSize && A >= 0.0 && B >= 0.0 && A + B <= 128.0;  // false for NaN
-  return ok ? make_float2((float)A, (float)B) : make_float2(0.f, 0.f);
-}
+#ifndef GS_FILTER_DELTA_LOG2
+#define GS_FILTER_DELTA_LOG2 13
+#endif
+#ifndef GS_FILTER_MAX_SUM
+#define GS_FILTER_MAX_SUM 128.0
+#endif
+constexpr float kFilterDelta = 1.0f / (float)(1 << GS_FILTER_DELTA_LOG2);  // 2^-13 = 1.22e-4
+constexpr double kFilterMaxSum = GS_FILTER_MAX_SUM;                        // A + B may not exceed this
 
 // ------------------------------------------------------------------ stage A ----------
 
@@ -335,7 +332,7 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
     // float32 filter: tmp = A + B*v with A = tmp at v = 0 (tn, tp) and B = 100*kk/c; (0, 0) =
     // "always take the exact path" outside the range the error bound assumes (see kFilterDelta)
     const double Bn = 100.0 * kk_n * Ln1.x, Bp = 100.0 * kk_p * Lp1.x;
-    const bool okn = tn >= 0.0 && Bn >= 0.0 && tn + Bn <= 128.0, okp = tp >= 0.0 && Bp >= 0.0 && tp + Bp <= 128.0;
+    const bool okn = tn >= 0.0 && Bn >= 0.0 && tn + Bn <= kFilterMaxSum, okp = tp >= 0.0 && Bp >= 0.0 && tp + Bp <= kFilterMaxSum;
     sm->ab[g][0][tid] = okn ? make_float2((float)tn, (float)Bn) : make_float2(0.f, 0.f);
     sm->ab[g][1][tid] = okp ? make_float2((float)tp, (float)Bp) : make_float2(0.f, 0.f);
     ci_max = fmaxf(ci_max, fabsf(ci));
