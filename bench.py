@@ -351,7 +351,7 @@ def main():
                          # and the exact path's re-reads of the table
                          "traffic": TRAFFIC_BYTES if (P, NL, n_apps, args.app_dist) == (N_PODS, N_NODES, N_APPS, "zipf") else None, "peak_kind": peak_kind, "kernel": "score_fast_kernel",
                          "kernel_ms": kernel_ms, "algorithmic_bytes": abytes,
-                         "note": "kernel is instruction-issue / latency bound, not HBM bound: a float32 filter decides floor(tmp) for all but ~2.5e-4 of the (pod,node,GPU) evaluations, which take the exact float64 sequence (DESIGN.md 4.1-4.2)"},
+                         "note": "kernel is instruction-issue / latency bound, not HBM bound: a float32 filter decides floor(tmp) for all but ~1e-4 of the (pod,node,GPU) evaluations, which take the exact float64 sequence (DESIGN.md 4.1-4.2)"},
         }
         if e2e:
             line["e2e"] = e2e

@@ -24,7 +24,7 @@
 // A + B*v (one approximate reciprocal, two fused multiply-adds) lies within kFilterErr of the
 // float64 value the reference computes (bound derived at kFilterDelta below), so whenever it is
 // farther than that from an integer its floor IS the reference's int64(tmp).  Only the few
-// (pod, node, GPU) whose estimate falls within kFilterDelta of an integer — about 2.5e-4 of them
+// (pod, node, GPU) whose estimate falls within kFilterDelta of an integer — about 1.2e-4 of them
 // — are evaluated with the exact float64 sequence (for the whole warp, chosen by a vote, so
 // there is no divergence).  The float32 constants live in shared memory (one 8-byte slot per
 // thread, GPU and branch); the exact path rebuilds kk/cst from the sums (registers, or the
@@ -103,21 +103,24 @@ __device__ __forceinline__ double2 branch_const(bool neg, double neg_sum, double
   return make_double2(kk, cst);
 }
 
-// Float32 filter constants.  With A, B >= 0 and A + B <= kFilterMaxSum (128) the float32 estimate
+// Float32 filter constants.  With A, B >= 0 and A + B <= kFilterMaxSum the float32 estimate
 //   est = fma(B32, rcp_approx(z32), A32),  z32 = 1 + |t|  or  fma(1 + |t|, 1 + |t|, 1)
 // differs from the reference's float64 tmp by less than
-//   u*A (rounding A) + u*B (rounding B) + 5u*B (z32: at most 3u relative, the approximate
-//   reciprocal: 2u) + u*(A + B) (the final fma)  <=  8u * kFilterMaxSum = 6.2e-5,   u = 2^-24,
-// plus the float64 roundings of tmp itself and of A, B (below 1e-11).  kFilterDelta leaves a
-// factor of two.
+//   2u*A (rounding A, the final fma) + 7u*B*v (rounding B, z32: at most 3u relative, the
+//   approximate reciprocal: 1 ulp = 2u, the final fma)  <=  7u * kFilterMaxSum = 4.2e-5,  u = 2^-24,
+// plus the float64 roundings of tmp itself and of A, B (below 1e-11).  Mathematically A + B <= 100
+// (it is tmp at v = 1, a weighted mean of values in [0, 1] times 100); constants outside
+// [0, kFilterMaxSum] switch the filter off for their GPU.  kFilterDelta = 2^-14 = 6.1e-5 leaves a
+// factor of 1.45 (still 1.1 if the reciprocal were 2 ulp off).  -DGS_FILTER_DELTA_LOG2=13
+// -DGS_FILTER_MAX_SUM=128 is the wider margin the first version ran with (5 % slower).
 #ifndef GS_FILTER_DELTA_LOG2
-#define GS_FILTER_DELTA_LOG2 13
+#define GS_FILTER_DELTA_LOG2 14
 #endif
 #ifndef GS_FILTER_MAX_SUM
-#define GS_FILTER_MAX_SUM 128.0
+#define GS_FILTER_MAX_SUM 100.5
 #endif
-constexpr float kFilterDelta = 1.0f / (float)(1 << GS_FILTER_DELTA_LOG2);  // 2^-13 = 1.22e-4
-constexpr double kFilterMaxSum = GS_FILTER_MAX_SUM;                        // A + B may not exceed this
+constexpr float kFilterDelta = 1.0f / (float)(1 << GS_FILTER_DELTA_LOG2);
+constexpr double kFilterMaxSum = GS_FILTER_MAX_SUM;  // A + B may not exceed this
 
 // ------------------------------------------------------------------ stage A ----------
 
