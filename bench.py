@@ -32,9 +32,35 @@ import numpy as np  # noqa: E402
 N_PODS, N_NODES, GPUS_PER_NODE, N_APPS = 50_000, 5_000, 8, 1024
 METRIC = "pod x node Filter+Score+NormalizeScore evals/sec (50k pods x 5k nodes x 8 GPUs/node per rank)"
 UNIT = "evals/s"
+# what the library's event bracket (gs_last_score_kernel_ms) spans
+BRACKET_KERNELS = "stage_a_kernel + score_fast_kernel (one event bracket around both)"
 
 
-TRAFFIC_BYTES = 2204962672  # 1 395 718 000 read + 809 244 672 written
+def source_sha16():
+    """Hash of the CUDA sources the library is built from: ties a committed ncu capture to a build."""
+    import hashlib
+
+    h = hashlib.sha256()
+    csrc = os.path.join(ROOT, "k8s-gpu-scheduler_b200", "csrc")
+    for name in sorted(os.listdir(csrc)):
+        if name.endswith((".cu", ".cuh", ".h")):
+            with open(os.path.join(csrc, name), "rb") as f:
+                h.update(name.encode() + b"\0" + f.read())
+    return h.hexdigest()[:16]
+
+
+def measured_traffic(workload_key):
+    """dram__bytes_read.sum + dram__bytes_write.sum per step from `ncu --set full` of THIS build
+    (profiles/r2/traffic.json, written by profiles/ncu_traffic.py from the capture); None when the
+    sources changed since that capture or the workload differs."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r2", "traffic.json")) as f:
+            t = json.load(f)
+        if t.get("src_sha16") == source_sha16() and t.get("workload") == workload_key:
+            return t
+    except Exception:
+        pass
+    return None
 
 
 def workload_name(n_ranks, pods=N_PODS, nodes=N_NODES):
@@ -150,9 +176,18 @@ def cpu_reference_leg(preds, cluster, pods, budget_evals_per_thread=3_000_000, s
     ora.score_batch(one, normalize=True, threads=1)
     one_thread = n_one * cluster.n_nodes / (time.perf_counter() - t0)
     return {"value": evals * len(times) / sum(times), "unit": UNIT, "cores": threads, "kind": "port",
-            "single_thread_value": one_thread,
+            "single_thread_value": one_thread, "sampled_pods": n_sample,
             "sample": f"first {n_sample} of {pods.n_pods} pods x all {cluster.n_nodes} nodes ({evals} evals/step), "
                       f"oracle/score_oracle.c -O2, OpenMP over pods"}, sum(times) / len(times)
+
+
+def bench_config(pkg, world, P, NL, n_apps, app_dist, pods, n_res_rank0):
+    """The `config` object: identical in both arms (the driver compares them)."""
+    return {"workload": workload_name(world, P, NL), "pods": P, "nodes_per_rank": NL, "gpus_per_node": GPUS_PER_NODE,
+            "apps": n_apps, "app_distribution": app_dist, "residents_rank0": n_res_rank0,
+            "distinct_app_slo_classes": pkg.synth.distinct_classes(pods), "seed": hex(pkg.synth.SEED),
+            "l2": "flushed between timed iterations (256 MB memset, untimed); outputs 500 MB > L2",
+            "timing": "CUDA events per step on the launching stream, summed; max over ranks"}
 
 
 def run_reference(args, rank, world):
@@ -161,19 +196,45 @@ def run_reference(args, rank, world):
     import __graft_entry__ as entry
 
     pkg = entry.load_package()
-    preds, cluster, pods = pkg.synth.make_workload(N_PODS, N_NODES, GPUS_PER_NODE, N_APPS)
+    P, NL, n_apps = args.pods, args.nodes, args.apps
+    preds = pkg.synth.make_predictions(n_apps)
+    cluster_all = pkg.synth.make_cluster(NL * world, n_apps, GPUS_PER_NODE)
+    cluster = cluster_all.shard(0, NL) if world > 1 else cluster_all
+    pods = pkg.synth.make_pods(P, n_apps, app_dist=args.app_dist)
     cb, sec = cpu_reference_leg(preds, cluster, pods, steps=args.steps, warmup=min(args.warmup, 1))
     line = {
         "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32+f64", "data": "synthetic",
-        "config": {"workload": workload_name(world), "note": "CPU port of the reference's Go Logic/NormalizeScore "
-                   "(Go toolchain absent); each step is a bounded sample of the workload; the real reference also "
-                   "pays 2*G*(R+1) gRPC dials + Redis + API-server writes per Score, omitted here"},
+        "config": bench_config(pkg, world, P, NL, n_apps, args.app_dist, pods, int(cluster.res_app.size)),
+        "reference_note": "CPU port of the reference's Go Logic/NormalizeScore (Go toolchain absent); each step is a "
+                          "bounded sample of the workload (cpu_baseline.sample); the real reference also pays "
+                          "2*G*(R+1) gRPC dials + Redis + API-server writes per Score, omitted here",
+        "sampled_pods": cb["sampled_pods"],
         "cpu_baseline": cb,
         "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
+
+
+def parity_check(pkg, preds, cluster_all, pods, rank, NL, d_score, d_sel, d_best, n_check=64):
+    """Untimed: n_check pods of this rank's node shard against the CPU oracle over the WHOLE cluster
+    (global NormalizeScore extrema, global best node) — bit for bit."""
+    from oracle.score_oracle import Oracle
+
+    pick = np.random.default_rng(1234 + rank).choice(pods.n_pods, size=min(n_check, pods.n_pods), replace=False)
+    pick.sort()
+    sub = type(pods)(app=pods.app[pick], slo=pods.slo[pick])
+    w_score, w_sel, w_best = Oracle(preds, cluster_all).score_batch(sub, normalize=True)
+    cols = slice(rank * NL, (rank + 1) * NL)
+    import torch
+
+    idx = torch.from_numpy(pick).to(d_score.device)
+    g_score = d_score.index_select(0, idx).cpu().numpy()
+    g_sel = d_sel.index_select(0, idx).cpu().numpy()
+    g_best = d_best.index_select(0, idx).cpu().numpy()
+    return bool(np.array_equal(g_score, w_score[:, cols]) and np.array_equal(g_sel, w_sel[:, cols])
+                and np.array_equal(g_best, w_best))
 
 
 def main():
@@ -254,6 +315,7 @@ def main():
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     with ClockSampler(local_rank) as clocks:
         barrier()
+        launches0 = pkg.launch_count()
         t_wall0 = time.perf_counter()
         for a, b in ev:
             flush.zero_()          # evict L2 between timed iterations (not timed)
@@ -263,6 +325,7 @@ def main():
         barrier()
         t_wall = time.perf_counter() - t_wall0
     step_ms = [a.elapsed_time(b) for a, b in ev]
+    launches = pkg.launch_count() - launches0
     # dominant-kernel duration, live, from the library's own event bracket on the same stream
     kms = []
     for _ in range(3):
@@ -270,6 +333,14 @@ def main():
         step()
         torch.cuda.synchronize()
         kms.append(sch.last_score_kernel_ms())
+    # untimed: this rank's results against the CPU oracle (after a fresh step, so the buffers hold its output)
+    step()
+    torch.cuda.synchronize()
+    ok = parity_check(pkg, preds, cluster_all, pods, rank, NL, d_score, d_sel, d_best)
+    ok_t = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+    if world > 1:
+        dist.all_reduce(ok_t, op=dist.ReduceOp.MIN)
+    parity_ok = bool(int(ok_t.item()))
     total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
@@ -332,24 +403,24 @@ def main():
         kernel_ms = float(np.median(kms))
         abytes = algorithmic_bytes(P, NL, int(cluster.res_app.size), n_apps, preds.conf.shape[1], GPUS_PER_NODE)
         achieved = abytes / (kernel_ms * 1e-3) / 1e9
+        traffic = measured_traffic(f"{P}x{NL}x{GPUS_PER_NODE}:{n_apps}:{args.app_dist}")
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32+f64", "data": "synthetic",
-            "config": {"workload": workload_name(world, P, NL), "pods": P, "nodes_per_rank": NL, "gpus_per_node": GPUS_PER_NODE,
-                       "apps": n_apps, "app_distribution": args.app_dist, "residents_rank0": int(cluster.res_app.size),
-                       "distinct_app_slo_classes": pkg.synth.distinct_classes(pods), "seed": hex(pkg.synth.SEED),
-                       "l2": "flushed between timed iterations (256 MB memset, untimed); outputs 500 MB > L2",
-                       "timing": "CUDA events per step on the launching stream, summed; max over ranks"},
-            "gpu_launches": 6 * args.steps,  # hist, scan, scatter, stage_a, score_fast, normalize
+            "config": bench_config(pkg, world, P, NL, n_apps, args.app_dist, pods, int(cluster.res_app.size)),
+            "parity_ok": parity_ok,
+            "parity": "64 pods x this rank's node shard per rank vs the CPU oracle over the whole cluster, bit-exact "
+                      "(normalised score, selection byte, best node); all ranks must agree",
+            "gpu_launches": launches,  # counted by the library (gs_launch_count) over the timed region
             "wall_ms_per_step_incl_flush": t_wall * 1e3 / args.steps,
             "clocks": clocks.summary(),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the ncu capture
-                         # summarised in profiles/r1/ncu_score_fast_filter_final.txt (default workload only): 1.05 GB
-                         # of it is the per-batch residents-sum table, the rest results, partial-sector merges
-                         # and the exact path's re-reads of the table
-                         "traffic": TRAFFIC_BYTES if (P, NL, n_apps, args.app_dist) == (N_PODS, N_NODES, N_APPS, "zipf") else None, "peak_kind": peak_kind, "kernel": "score_fast_kernel",
+                         # dram__bytes_read.sum + dram__bytes_write.sum of the bracketed kernels, from an ncu
+                         # capture of THIS build (profiles/r2/traffic.json), else null
+                         "traffic": traffic["traffic_bytes"] if traffic else None,
+                         "traffic_source": traffic["source"] if traffic else None,
+                         "peak_kind": peak_kind, "kernel": BRACKET_KERNELS,
                          "kernel_ms": kernel_ms, "algorithmic_bytes": abytes,
                          "note": "kernel is instruction-issue / latency bound, not HBM bound: a float32 filter decides floor(tmp) for all but ~1e-4 of the (pod,node,GPU) evaluations, which take the exact float64 sequence (DESIGN.md 4.1-4.2)"},
         }

@@ -139,7 +139,11 @@ GS_API const char* gs_version(void);
 
 /* Upload a cluster snapshot (or the node shard [node_begin, node_begin+n_nodes) of one:
  * node_base is added to node indices in best-node results).
- * Replaces gpu_plugins.go:529-549 (Redis GET + GetSLOs) for all nodes at once. */
+ * Replaces gpu_plugins.go:529-549 (Redis GET + GetSLOs) for all nodes at once.
+ * Limits: at most 8 388 480 nodes per context (shard beyond that) and 65 535 residents per GPU.
+ * Both uploads first wait for the GPU work of every earlier scoring / normalise call on this
+ * context (whatever stream it was issued on), so a re-upload after an informer event never
+ * overwrites tables that an asynchronous gs_score_raw_dev is still reading. */
 GS_API int gs_upload_cluster(gs_ctx* ctx, const gs_cluster* cluster, int32_t node_base);
 
 /* Upload the completed prediction tables.  Replaces gpu_plugins.go:302-355 and the
@@ -249,12 +253,25 @@ GS_API int gs_select_mig(gs_ctx* ctx, const uint32_t* pod_app, const float* pod_
  * events on the launching stream; gs_last_score_kernel_ms waits for the last bracket and
  * returns its duration.  Used by bench.py for the roofline figure. */
 GS_API int gs_set_profiling(gs_ctx* ctx, int enabled);
+/* Number of CUDA kernels this library has launched in this process so far (all contexts; copies
+ * and memsets are not kernels).  bench.py reports the difference over its timed region. */
+GS_API uint64_t gs_launch_count(void);
 /* Arithmetic self-test (no counterpart in the reference): runs the streamlined reciprocal,
  * small-integer division and floor used by the restructured scoring kernel against CUDA's
  * IEEE intrinsics on `n_million` x 10^6 pseudo-random operands and returns the number of
  * results that differ in any bit (must be 0). */
 GS_API int gs_selftest(gs_ctx* ctx, uint64_t seed, int32_t n_million, uint64_t* out_mismatches);
 GS_API int gs_last_score_kernel_ms(gs_ctx* ctx, float* out_ms);
+/* Filter self-test (no counterpart in the reference): the scoring kernel decides int64(tmpScore)
+ * (gpu_plugins.go:752) from a float32 estimate wherever that estimate lies farther than
+ * *out_delta from an integer, and only otherwise runs the float64 sequence.  This runs both on
+ * about `n_million` x 10^6 drawn (residents' sums, candidate term) samples ON THE DEVICE — half of
+ * them aimed within 1e-4 of an integer score — and reports the largest |estimate - tmpScore|
+ * seen (must stay below *out_delta), how many estimates outside the band floor differently from
+ * tmpScore (must be 0), how many fell inside the band, and how many samples were evaluated. */
+GS_API int gs_selftest_filter(gs_ctx* ctx, uint64_t seed, int32_t n_million, double* out_max_dev,
+                              double* out_delta, uint64_t* out_wrong_floors, uint64_t* out_in_band,
+                              uint64_t* out_evaluated);
 
 /* ---------------------------------------------------------------- completion ------- */
 

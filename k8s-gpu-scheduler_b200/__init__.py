@@ -31,7 +31,7 @@ ERR_NAMES = {-1: "GS_ERR_INVALID", -2: "GS_ERR_CUDA", -3: "GS_ERR_STATE", -4: "G
 EXPORTS = [
     "gs_create", "gs_destroy", "gs_last_error", "gs_version", "gs_upload_cluster", "gs_upload_predictions",
     "gs_score_batch", "gs_score_raw_dev", "gs_score_raw_dev_noalloc", "gs_normalize_dev", "gs_normalize_scores", "gs_select_mig",
-    "gs_set_profiling", "gs_last_score_kernel_ms", "gs_selftest", "gs_complete_fit", "gs_complete_fit_sharded", "gs_complete_fit_transform", "gs_complete_transform", "gs_model_info", "gs_model_step", "gs_model_destroy",
+    "gs_set_profiling", "gs_last_score_kernel_ms", "gs_selftest", "gs_selftest_filter", "gs_launch_count", "gs_complete_fit", "gs_complete_fit_sharded", "gs_complete_fit_transform", "gs_complete_transform", "gs_model_info", "gs_model_step", "gs_model_destroy",
 ]
 
 
@@ -75,6 +75,7 @@ def load_library():
     L.gs_last_error.argtypes = [vp]
     L.gs_last_error.restype = C.c_char_p
     L.gs_version.restype = C.c_char_p
+    L.gs_launch_count.restype = C.c_uint64
     L.gs_upload_cluster.argtypes = [vp, C.POINTER(_GsCluster), i32]
     L.gs_upload_predictions.argtypes = [vp, C.POINTER(_GsPredictions)]
     L.gs_score_batch.argtypes = [vp, vp, vp, vp, i32, u32, vp, vp, vp]
@@ -86,6 +87,8 @@ def load_library():
     L.gs_set_profiling.argtypes = [vp, C.c_int]
     L.gs_last_score_kernel_ms.argtypes = [vp, C.POINTER(C.c_float)]
     L.gs_selftest.argtypes = [vp, C.c_uint64, i32, C.POINTER(C.c_uint64)]
+    L.gs_selftest_filter.argtypes = [vp, C.c_uint64, i32, C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                     C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.gs_complete_fit.argtypes = [vp, vp, i32, i32, C.POINTER(vp)]
     L.gs_complete_fit_sharded.argtypes = [vp, vp, i32, i32, ALLREDUCE_FN, vp, C.POINTER(vp)]
     L.gs_complete_fit_transform.argtypes = [vp, vp, i32, i32, ALLREDUCE_FN, vp, vp, C.POINTER(vp)]
@@ -96,6 +99,11 @@ def load_library():
     L.gs_model_destroy.restype = None
     _lib = L
     return L
+
+
+def launch_count() -> int:
+    """Kernels launched by the library so far in this process (gs_launch_count)."""
+    return int(load_library().gs_launch_count())
 
 
 def _ptr(a):
@@ -206,6 +214,15 @@ class Scheduler:
         bad = C.c_uint64(0)
         self._check(self._L.gs_selftest(self._h, int(seed), int(n_million), C.byref(bad)))
         return int(bad.value)
+
+    def selftest_filter(self, seed: int = 1, n_million: int = 100) -> dict:
+        """gs_selftest_filter: float32 filter estimate vs the exact float64 tmpScore, on the device."""
+        dev, delta = C.c_double(0), C.c_double(0)
+        wrong, band, n = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
+        self._check(self._L.gs_selftest_filter(self._h, int(seed), int(n_million), C.byref(dev), C.byref(delta),
+                                               C.byref(wrong), C.byref(band), C.byref(n)))
+        return {"max_dev": dev.value, "delta": delta.value, "wrong_floors": int(wrong.value),
+                "in_band": int(band.value), "evaluated": int(n.value)}
 
     # -- the other entry points -------------------------------------------------------
     def normalize_scores(self, scores) -> np.ndarray:

@@ -913,12 +913,15 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
   std::vector<long long> missing(d);
   std::vector<double> stats(3 * (size_t)d + 1);
 
+  gs::note_launch();
   column_stats_kernel<<<d, 256, 0, s>>>(dX, n, d, dStats);
   int xrc;
   if ((xrc = exchange(dStats, 2 * (int64_t)d + 1, GS_REDUCE_SUM, s)) || (xrc = exchange(dStats + 2 * d + 1, d, GS_REDUCE_MAX, s))) {
     return xrc;
   }
+  gs::note_launch();
   finish_means_kernel<<<(d + 255) / 256, 256, 0, s>>>(dStats, d, dMeans);
+  gs::note_launch();
   fill_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(dX, dMeans, total, d, dXt, dMask);
   cudaError_t e = cudaGetLastError();
   if (e == cudaSuccess) e = cudaMemcpyAsync(m->means.data(), dMeans, sizeof(double) * d, cudaMemcpyDeviceToHost, s);
@@ -955,8 +958,10 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
   const double norm_tol = kRoundTol * mx;
 
   if (big_gram) {  // Gram over all rows, centred at the initial means
+    gs::note_launch();
     gram128_partial_kernel<false><<<dim3(tiles, tiles, parts), 256, 0, s>>>(dXt, dMask, nullptr, n, d, -1, dMeans,
                                                                          rows_per_part, dPartial);
+    gs::note_launch();
     gram_reduce_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dPartial, d, parts, gtile, nullptr, dH);
   }
   int step = 0;
@@ -968,58 +973,79 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
     m->n_rounds = rnd;
     for (int oi = 0; oi < d; ++oi, ++step) {
       const int j = order[oi];
+      gs::note_launch();
       obs_sums_partial_kernel<<<sum_blocks, 256, 0, s>>>(dXt, dMask, n, d, j, dSumPart);
+      gs::note_launch();
       obs_sums_reduce_kernel<<<(d + 1 + 255) / 256, 256, 0, s>>>(dSumPart, sum_blocks, d, dSums);
       if ((xrc = exchange(dSums, (int64_t)d + 1, GS_REDUCE_SUM, s))) {
         return xrc;
       }
+      gs::note_launch();
       finish_mu_kernel<<<(d + 255) / 256, 256, 0, s>>>(dSums, d, dMu, dNobs);
       if (big_gram) {
         const int n_dead = (int)(dead_off[j + 1] - dead_off[j]);
         if (2 * (size_t)n_dead < (size_t)n) {
           int rpp = (n_dead + parts - 1) / parts;
           rpp = (rpp + kBK - 1) / kBK * kBK;
+          gs::note_launch();
           gram128_partial_kernel<true><<<dim3(tiles, tiles, parts), 256, 0, s>>>(
               dXt, dMask, dDead + dead_off[j], n_dead, d, j, dMeans, rpp > 0 ? rpp : kBK, dPartial);
+          gs::note_launch();
           gram_reduce_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dPartial, d, parts, gtile, dH, dG);
         } else {
+          gs::note_launch();
           gram128_partial_kernel<false><<<dim3(tiles, tiles, parts), 256, 0, s>>>(dXt, dMask, nullptr, n, d, j, dMeans,
                                                                                rows_per_part, dPartial);
+          gs::note_launch();
           gram_reduce_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dPartial, d, parts, gtile, nullptr, dG);
         }
       } else {
+        gs::note_launch();
         gram_partial_kernel<<<dim3(tiles, tiles, parts), 256, 0, s>>>(dXt, dMask, n, d, j, dMu, rows_per_part, dPartial);
+        gs::note_launch();
         gram_reduce_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dPartial, d, parts, gtile, nullptr, dG);
       }
       if ((xrc = exchange(dG, (int64_t)d * d, GS_REDUCE_SUM, s))) {
         return xrc;
       }
-      if (big_gram) recentre_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dG, d, dMu, dMeans, dNobs);
+      if (big_gram) {
+        gs::note_launch();
+        recentre_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dG, d, dMu, dMeans, dNobs);
+      }
       if (use_lib) {
+        gs::note_launch();
         extract_minor_kernel<<<(mm * mm + 255) / 256, 256, 0, s>>>(dG, d, j, dA);
         if (cus.syevd(cus.h, CUSOLVER_EIG_MODE_VECTOR, CUBLAS_FILL_MODE_LOWER, mm, dA, mm, dEv, dWork, lwork,
                       dInfo + step) != CUSOLVER_STATUS_SUCCESS) {
           return c->fail(GS_ERR_CUDA, "cusolverDnDsyevd failed at step %d", step);
         }
         // eigenvectors come back column-major in dA: V[i][k] = dA[i + k*mm]
+        gs::note_launch();
         bayes_ridge_kernel<<<1, 256, bayes_smem, s>>>(dG, dMu, dNobs, d, j, dA, 1, mm, dEv,
                                                       dCoef + (size_t)step * (d - 1), dIcpt + step, dIters + step);
       } else {
         int jt = 32;
         while (jt < 1024 && jt < mm * mm / 4) jt <<= 1;
+        gs::note_launch();
         jacobi_eig_kernel<<<1, jt, 0, s>>>(dG, d, j, dA, dV, dEv, dSweeps + step);
+        gs::note_launch();
         bayes_ridge_kernel<<<1, 256, bayes_smem, s>>>(dG, dMu, dNobs, d, j, dV, mm, 1, dEv,
                                                       dCoef + (size_t)step * (d - 1), dIcpt + step, dIters + step);
       }
       if (missing[j] > 0)
+        gs::note_launch();
         predict_kernel<<<(n + 7) / 8, 256, 0, s>>>(dXt, dMask, n, d, j, dCoef + (size_t)step * (d - 1), dIcpt + step);
       if (big_gram && dead_off[j + 1] > dead_off[j]) {  // column j changed on this rank: row/column j of dH
+        gs::note_launch();
         h_row_partial_kernel<<<h_blocks, 256, 0, s>>>(dXt, n, d, j, dMeans, dHPart);
+        gs::note_launch();
         h_row_reduce_kernel<<<(d + 255) / 256, 256, 0, s>>>(dHPart, h_blocks, d, j, dH);
       }
       m->feat.push_back(j);
     }
+    gs::note_launch();
     max_row_diff_kernel<<<256, 256, 0, s>>>(dXt, dPrev, n, d, dDiff);
+    gs::note_launch();
     max_small_kernel<<<1, 256, 0, s>>>(dDiff, 256);
     if ((xrc = exchange(dDiff, 1, GS_REDUCE_MAX, s))) {
       return xrc;
@@ -1090,6 +1116,7 @@ int gs_complete_transform(gs_ctx* c, const gs_model* m, const double* X, int32_t
   }
   const size_t smem = (size_t)4 * d * sizeof(double) + (size_t)4 * d + 16;
   CK(cudaFuncSetAttribute(transform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  gs::note_launch();
   transform_kernel<<<(rows + 3) / 4, 128, smem, s>>>(dX, rows, d, dMeans, dFeat, dCoef, dIcpt, m->n_steps, dOut);
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(out, dOut, sizeof(double) * total, cudaMemcpyDeviceToHost, s));

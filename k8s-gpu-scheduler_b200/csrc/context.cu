@@ -1,6 +1,7 @@
 // context.cu — the C ABI of include/gpusched.h: context, table uploads, scoring entry
 // points.  Host logic only; kernels live in score_kernels.cu.
 #include <algorithm>
+#include <atomic>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -14,6 +15,10 @@
 #include "context.h"
 
 namespace gs {
+
+static std::atomic<unsigned long long> g_launches{0};
+void note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+unsigned long long launch_count() { return g_launches.load(std::memory_order_relaxed); }
 
 int Ctx::fail(int code, const char* fmt, ...) {
   char buf[512];
@@ -59,6 +64,16 @@ int Ctx::upload(DevBuf& b, const void* src, size_t bytes, const char* what) {
     if (e != cudaSuccess) return cuda_fail(e, what);
   }
   return GS_OK;
+}
+
+int Ctx::note_use(cudaStream_t s) {
+  cudaError_t e = cudaEventRecord(ev_last_use, s);
+  return e == cudaSuccess ? GS_OK : cuda_fail(e, "cudaEventRecord(last use)");
+}
+
+int Ctx::wait_last_use() {
+  cudaError_t e = cudaEventSynchronize(ev_last_use);
+  return e == cudaSuccess ? GS_OK : cuda_fail(e, "waiting for in-flight scoring before an upload");
 }
 
 DevTables Ctx::tables() const {
@@ -152,6 +167,8 @@ using gs::Ctx;
 
 extern "C" {
 
+uint64_t gs_launch_count(void) { return gs::launch_count(); }
+
 const char* gs_version(void) { return "gpusched 0.1 sm_100a " __DATE__; }
 
 int gs_create(int device, gs_ctx** out) {
@@ -169,7 +186,9 @@ int gs_create(int device, gs_ctx** out) {
   c->device = device;
   if (const char* mb = getenv("GS_STAGE_TABLE_MB")) c->stage_budget = (size_t)strtoull(mb, nullptr, 10) << 20;
   if (cudaSetDevice(device) != cudaSuccess ||
-      cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+      cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->ev_last_use, cudaEventDisableTiming) != cudaSuccess) {
+    if (c->stream) cudaStreamDestroy(c->stream);
     cudaGetLastError();
     delete c;
     return GS_ERR_CUDA;
@@ -194,6 +213,7 @@ void gs_destroy(gs_ctx* c) {
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->ev_begin) cudaEventDestroy(c->ev_begin);
     if (c->ev_end) cudaEventDestroy(c->ev_end);
+    if (c->ev_last_use) cudaEventDestroy(c->ev_last_use);
     cudaStreamDestroy(c->stream);
   }
   delete c;
@@ -205,9 +225,9 @@ int gs_upload_cluster(gs_ctx* c, const gs_cluster* cl, int32_t node_base) {
   if (!c) return GS_ERR_INVALID;
   GS_LOCK(c);
   if (!cl) return c->fail(GS_ERR_INVALID, "gs_upload_cluster: null cluster");
-  if (cl->n_nodes > (1 << 24))
-    return c->fail(GS_ERR_INVALID, "gs_upload_cluster: %d nodes in one context; at most 2^24 (shard the cluster)",
-                   cl->n_nodes);
+  if (cl->n_nodes > gs::kMaxNodesPerCtx)
+    return c->fail(GS_ERR_INVALID, "gs_upload_cluster: %d nodes in one context; at most %d (shard the cluster)",
+                   cl->n_nodes, gs::kMaxNodesPerCtx);
   if (cl->n_nodes < 0 || cl->max_gpus < 1 || cl->max_gpus > GS_MAX_GPUS_PER_NODE)
     return c->fail(GS_ERR_INVALID, "gs_upload_cluster: n_nodes=%d max_gpus=%d out of range (max_gpus 1..%d)",
                    cl->n_nodes, cl->max_gpus, GS_MAX_GPUS_PER_NODE);
@@ -215,9 +235,13 @@ int gs_upload_cluster(gs_ctx* c, const gs_cluster* cl, int32_t node_base) {
   if (N && (!cl->node_model || !cl->node_ngpu)) return c->fail(GS_ERR_INVALID, "gs_upload_cluster: null node table");
   if (!cl->gpu_off) return c->fail(GS_ERR_INVALID, "gs_upload_cluster: null gpu_off");
   if (cl->gpu_off[0] != 0) return c->fail(GS_ERR_INVALID, "gs_upload_cluster: gpu_off[0] must be 0");
-  for (size_t s = 0; s < slots; ++s)
+  for (size_t s = 0; s < slots; ++s) {
     if (cl->gpu_off[s + 1] < cl->gpu_off[s])
       return c->fail(GS_ERR_INVALID, "gs_upload_cluster: gpu_off decreases at slot %zu", s);
+    if (cl->gpu_off[s + 1] - cl->gpu_off[s] > (uint32_t)gs::kMaxResidentsPerSlot)
+      return c->fail(GS_ERR_INVALID, "gs_upload_cluster: slot %zu holds %u residents; at most %d per GPU", s,
+                     cl->gpu_off[s + 1] - cl->gpu_off[s], gs::kMaxResidentsPerSlot);
+  }
   for (size_t n = 0; n < N; ++n) {
     if (cl->node_model[n] > GS_MODEL_V100)
       return c->fail(GS_ERR_INVALID, "gs_upload_cluster: node %zu has model %d", n, (int)cl->node_model[n]);
@@ -231,6 +255,7 @@ int gs_upload_cluster(gs_ctx* c, const gs_cluster* cl, int32_t node_base) {
   const size_t R = cl->gpu_off[slots];
   if (R && (!cl->res_app || !cl->res_slo)) return c->fail(GS_ERR_INVALID, "gs_upload_cluster: null resident table");
   GS_CUDA(c, cudaSetDevice(c->device));
+  if (int rcw = c->wait_last_use()) return rcw;  // asynchronous scoring on a caller stream may still read the tables
   // Internal node order: within every block of kGroupBlock consecutive nodes, the nodes whose
   // GPU loop runs (model and >= 1 UUID) are grouped by model, the rest last — a stable
   // partition, so that most warps hold 32 nodes of one model and can skip what none of them
@@ -302,6 +327,7 @@ int gs_upload_predictions(gs_ctx* c, const gs_predictions* pr) {
       return c->fail(GS_ERR_INVALID, "gs_upload_predictions: col_of[%d]=%d outside [-1,%d)", i, pr->col_of[i],
                      pr->n_cols);
   GS_CUDA(c, cudaSetDevice(c->device));
+  if (int rcw = c->wait_last_use()) return rcw;
   const size_t A = (size_t)pr->n_apps, K = (size_t)pr->n_cols;
   int rc;
   if ((rc = c->upload(c->conf, pr->conf, sizeof(float) * A * K, "conf"))) return rc;
@@ -353,7 +379,7 @@ static int score_raw_locked(gs_ctx* c, const uint32_t* d_app, const float* d_slo
     GS_CUDA(c, cudaEventRecord(c->ev_end, s));
     c->ev_valid = true;
   }
-  return GS_OK;
+  return c->note_use(s);
 }
 
 int gs_score_raw_dev(gs_ctx* c, const uint32_t* d_pod_app, const float* d_pod_slo, const int32_t* d_pod_self,
@@ -382,7 +408,7 @@ int gs_normalize_dev(gs_ctx* c, int32_t n_pods, uint8_t* d_score, const uint64_t
                                        (const unsigned long long*)d_neg_lo, d_best,
                                        stream ? (cudaStream_t)stream : c->stream);
   if (e != cudaSuccess) return c->cuda_fail(e, "normalize");
-  return GS_OK;
+  return c->note_use(stream ? (cudaStream_t)stream : c->stream);
 }
 
 int gs_score_batch(gs_ctx* c, const uint32_t* pod_app, const float* pod_slo, const int32_t* pod_self, int32_t P,
@@ -542,6 +568,29 @@ int gs_selftest(gs_ctx* c, uint64_t seed, int32_t n_million, uint64_t* out_misma
   if (e != cudaSuccess) return c->cuda_fail(e, "selftest");
   GS_CUDA(c, cudaMemcpyAsync(out_mismatches, c->b_misc.p, sizeof(uint64_t), cudaMemcpyDeviceToHost, c->stream));
   GS_CUDA(c, cudaStreamSynchronize(c->stream));
+  return GS_OK;
+}
+
+int gs_selftest_filter(gs_ctx* c, uint64_t seed, int32_t n_million, double* out_max_dev, double* out_delta,
+                       uint64_t* out_wrong_floors, uint64_t* out_in_band, uint64_t* out_evaluated) {
+  if (!c) return GS_ERR_INVALID;
+  GS_LOCK(c);
+  if (n_million < 1 || !out_max_dev || !out_delta || !out_wrong_floors || !out_in_band || !out_evaluated)
+    return c->fail(GS_ERR_INVALID, "gs_selftest_filter: bad argument");
+  GS_CUDA(c, cudaSetDevice(c->device));
+  int rc;
+  if ((rc = c->reserve(c->b_misc, 256, "selftest counters"))) return rc;
+  GS_CUDA(c, cudaMemsetAsync(c->b_misc.p, 0, 4 * sizeof(unsigned long long), c->stream));
+  cudaError_t e = gs::launch_selftest_filter(seed, 3907, n_million, (unsigned long long*)c->b_misc.p, c->stream);
+  if (e != cudaSuccess) return c->cuda_fail(e, "selftest_filter");
+  unsigned long long h[4];
+  GS_CUDA(c, cudaMemcpyAsync(h, c->b_misc.p, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+  GS_CUDA(c, cudaStreamSynchronize(c->stream));
+  memcpy(out_max_dev, &h[0], sizeof(double));
+  *out_delta = gs::filter_delta();
+  *out_wrong_floors = h[1];
+  *out_in_band = h[2];
+  *out_evaluated = h[3];
   return GS_OK;
 }
 

@@ -45,6 +45,11 @@ struct Ctx {
   bool profiling = false;
   bool ev_valid = false;
   cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+  // recorded after the last launch of every device-pointer scoring call (on the caller's stream);
+  // table uploads wait for it, so that a re-upload never overwrites tables a kernel still reads
+  cudaEvent_t ev_last_use = nullptr;
+  int note_use(cudaStream_t s);
+  int wait_last_use();
 
   int fail(int code, const char* fmt, ...) __attribute__((format(printf, 3, 4)));
   int cuda_fail(cudaError_t e, const char* what);

@@ -63,29 +63,69 @@ bool parse_json_string_array(const char* s, std::vector<std::string>* out) {
     }
     ++p;
     std::string cur;
-    while (*p && *p != '"') {
-      if (*p == '\\' && p[1]) {
+    // encoding/json's scanner rejects the whole document on a malformed string: an escape other
+    // than \" \\ \/ \b \f \n \r \t \uXXXX, a \u without four hex digits, a raw control character
+    auto hex4 = [](const char* q, unsigned* v) {  // q -> the four digits after "\u"
+      *v = 0;
+      for (int i = 0; i < 4; ++i) {
+        const unsigned char ch = (unsigned char)q[i];  // a NUL ends the scan here: never read past it
+        if (!isxdigit(ch)) return false;
+        *v = *v * 16 + (unsigned)(isdigit(ch) ? ch - '0' : tolower(ch) - 'a' + 10);
+      }
+      return true;
+    };
+    auto utf8 = [&cur](unsigned cp) {
+      if (cp < 0x80) {
+        cur += (char)cp;
+      } else if (cp < 0x800) {
+        cur += (char)(0xC0 | (cp >> 6));
+        cur += (char)(0x80 | (cp & 0x3F));
+      } else if (cp < 0x10000) {
+        cur += (char)(0xE0 | (cp >> 12));
+        cur += (char)(0x80 | ((cp >> 6) & 0x3F));
+        cur += (char)(0x80 | (cp & 0x3F));
+      } else {
+        cur += (char)(0xF0 | (cp >> 18));
+        cur += (char)(0x80 | ((cp >> 12) & 0x3F));
+        cur += (char)(0x80 | ((cp >> 6) & 0x3F));
+        cur += (char)(0x80 | (cp & 0x3F));
+      }
+    };
+    bool bad = false;
+    while (*p && *p != '"' && !bad) {
+      if ((unsigned char)*p < 0x20) {
+        bad = true;
+      } else if (*p == '\\') {
         ++p;
         switch (*p) {
-          case 'n': cur += '\n'; break;
-          case 't': cur += '\t'; break;
-          case 'r': cur += '\r'; break;
-          case 'b': cur += '\b'; break;
-          case 'f': cur += '\f'; break;
-          case 'u': {  // \uXXXX: UUIDs are ASCII; keep the low byte
-            unsigned v = 0;
-            for (int i = 1; i <= 4 && p[i]; ++i) v = v * 16 + (unsigned)(isdigit(p[i]) ? p[i] - '0' : (tolower(p[i]) - 'a' + 10));
-            cur += (char)(v & 0x7F);
-            p += 4;
+          case '"': cur += '"'; ++p; break;
+          case '\\': cur += '\\'; ++p; break;
+          case '/': cur += '/'; ++p; break;
+          case 'n': cur += '\n'; ++p; break;
+          case 't': cur += '\t'; ++p; break;
+          case 'r': cur += '\r'; ++p; break;
+          case 'b': cur += '\b'; ++p; break;
+          case 'f': cur += '\f'; ++p; break;
+          case 'u': {  // \uXXXX -> UTF-8, surrogate pairs combined, lone surrogates U+FFFD (as Go's unquote)
+            unsigned v = 0, lo = 0;
+            if (!hex4(p + 1, &v)) { bad = true; break; }
+            p += 5;
+            if (v >= 0xD800 && v < 0xDC00 && p[0] == '\\' && p[1] == 'u' && hex4(p + 2, &lo) && lo >= 0xDC00 && lo < 0xE000) {
+              v = 0x10000 + ((v - 0xD800) << 10) + (lo - 0xDC00);
+              p += 6;
+            } else if (v >= 0xD800 && v < 0xE000) {
+              v = 0xFFFD;
+            }
+            utf8(v);
             break;
           }
-          default: cur += *p;
+          default: bad = true;  // includes the NUL of a document that ends inside an escape
         }
-        ++p;
       } else {
         cur += *p++;
       }
     }
+    if (bad) { out->clear(); return false; }
     if (*p != '"') { out->clear(); return false; }
     ++p;
     out->push_back(cur);

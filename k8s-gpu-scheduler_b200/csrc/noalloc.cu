@@ -93,17 +93,20 @@ extern "C" int gs_score_raw_dev_noalloc(gs_ctx* ctx, const uint32_t* d_pod_app, 
   if (c->max_gpus > kFastMaxGpus)
     return c->fail(GS_ERR_INVALID, "gs_score_raw_dev_noalloc: %d GPU slots per node exceed the %d it covers", c->max_gpus,
                    kFastMaxGpus);
-  if (n_pods == 0 || c->n_nodes == 0) return GS_OK;
+  if (n_pods == 0) return GS_OK;
   cudaError_t e = cudaSetDevice(c->device);
   if (e != cudaSuccess) return c->cuda_fail(e, "cudaSetDevice");
-  unsigned char* base = nullptr;
-  if ((e = scratch_for_device(c->device, &base)) != cudaSuccess) return c->cuda_fail(e, "cudaGetSymbolAddress(scratch)");
   cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
 
-  // the caller's per-pod extrema are max-accumulated: they must start at zero
+  // the caller's per-pod extrema are max-accumulated: they must start at zero — also when this
+  // context holds no node at all (an empty shard is legal: its zero extrema must not disturb the
+  // other ranks' values in the all-reduce), exactly as gs_score_raw_dev leaves them
   if ((e = cudaMemsetAsync(d_hi_arg, 0, sizeof(uint64_t) * (size_t)n_pods, s)) != cudaSuccess ||
       (e = cudaMemsetAsync(d_neg_lo, 0, sizeof(uint64_t) * (size_t)n_pods, s)) != cudaSuccess)
     return c->cuda_fail(e, "cudaMemsetAsync(extrema)");
+  if (c->n_nodes == 0) return GS_OK;
+  unsigned char* base = nullptr;
+  if ((e = scratch_for_device(c->device, &base)) != cudaSuccess) return c->cuda_fail(e, "cudaGetSymbolAddress(scratch)");
 
   gs::DevTables T = c->tables();
   float4* res_rec = reinterpret_cast<float4*>(base + kOffResRec);
@@ -122,5 +125,5 @@ extern "C" int gs_score_raw_dev_noalloc(gs_ctx* ctx, const uint32_t* d_pod_app, 
   e = gs::launch_score_fast(T, d_pod_app, d_pod_slo, n_pods, sc, d_score, d_sel, (unsigned long long*)d_hi_arg,
                             (unsigned long long*)d_neg_lo, s);
   if (e != cudaSuccess) return c->cuda_fail(e, "score_fast (no-alloc)");
-  return GS_OK;
+  return c->note_use(s);  // an event created with the context: nothing is allocated here
 }

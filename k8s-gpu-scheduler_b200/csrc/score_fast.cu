@@ -218,6 +218,7 @@ __global__ void __launch_bounds__(256) transpose_interf_kernel(const float* __re
 
 cudaError_t launch_transpose_interf(const float* interf, float* interf_t, int n_apps, cudaStream_t s) {
   dim3 grid((n_apps + 31) / 32, (n_apps + 31) / 32, 2);
+  note_launch();
   transpose_interf_kernel<<<grid, 256, 0, s>>>(interf, interf_t, n_apps);
   return cudaGetLastError();
 }
@@ -517,16 +518,13 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
           const float2 slo2 = make_float2(pr.slo, pr.slo), inv2 = make_float2(pr.inv_slo, pr.inv_slo);
           // float32 estimate of tmp: returns floor(est), *r = est - floor(est) in [0, 1)
           auto estimate = [&](int g, bool neg, float t, float* r) -> float {
-            const float a = 1.0f + fabsf(t);
-            const float z = neg ? fmaf(a, a, 1.0f) : a;
-            float v;
-            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(v) : "f"(z));
+            const float z = filter_z(t, neg);
             float2 ab;
             asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];"
                          : "=f"(ab.x), "=f"(ab.y)
                          : "r"((neg ? ab_neg : ab_pos) + (uint32_t)(g * 2 * kTile * 8)));  // folds into [R+imm]
-            const float est = fmaf(ab.y, v, ab.x);
-            const float fl = __fadd_rz(est, 8388608.0f) - 8388608.0f;  // floor for 0 <= est < 2^22, exact
+            const float est = filter_est(ab.x, ab.y, z);
+            const float fl = filter_floor(est);                        // floor for 0 <= est < 2^22, exact
             *r = est - fl;                                             // exact
             return fl;
           };
@@ -631,6 +629,7 @@ cudaError_t launch_stage_a(const DevTables& T, const uint32_t* counts, const Sta
   const int slots = T.n_nodes * T.max_gpus;
   if (slots == 0 || !stage.n0) return cudaSuccess;
   dim3 ga((unsigned)((slots + kStageTile - 1) / kStageTile), (unsigned)((T.n_apps + 1 + kStageTile - 1) / kStageTile));
+  note_launch();
   stage_a_kernel<<<ga, 256, 0, s>>>(T, counts, stage);
   return cudaGetLastError();
 }
@@ -643,6 +642,7 @@ cudaError_t launch_score_main(const DevTables& T, const PodScratch& sc, uint8_t*
   score_fast_kernel<TABLE, GT><<<grid, kTile, 0, s>>>(T, sc.stage, sc.sorted, sc.chunks, sc.n_chunks, score, sel, \
                                                       hi_arg, neg_lo)
   const bool table = sc.stage.n0 != nullptr;
+  note_launch();
   if (T.max_gpus <= 2) {
     if (table) GS_LAUNCH_FAST(true, 2); else GS_LAUNCH_FAST(false, 2);
   } else if (T.max_gpus <= 4) {
@@ -695,8 +695,108 @@ __global__ void selftest_kernel(unsigned long long seed, int iters, unsigned lon
   if (bad) atomicAdd(mismatches, bad);
 }
 
+// The float32 filter against the exact float64 sequence, on the device (the hardware's own
+// rcp.approx, not an emulation).  Per sample: residents' counts and sums of one GPU are drawn,
+// folded into {A, B, kk, cst} exactly as fold_fast does, and one candidate term t is evaluated
+// both ways.  Even iterations draw |t| log-uniformly over 2^-20 .. 2^10; odd iterations aim tmp
+// at an integer +- 1e-4 (solving for t), which is where a wrong floor could hide.
+//   out[0] = max |est - tmp| (bits of a non-negative double), out[1] = samples whose estimate is
+//   outside the +-kFilterDelta band yet floors differently from tmp (must be 0), out[2] = samples
+//   inside the band (these take the exact path in the kernel), out[3] = samples evaluated.
+__global__ void selftest_filter_kernel(unsigned long long seed, int iters, unsigned long long* out) {
+  unsigned long long x = seed + 0x9E3779B97F4A7C15ull * (blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x + 1);
+  unsigned long long wrong = 0, band = 0, done = 0;
+  double maxdev = 0.0;
+  auto next = [&]() {
+    x ^= x << 13;
+    x ^= x >> 7;
+    x ^= x << 17;
+    return x;
+  };
+  auto unit = [&]() { return (double)(next() >> 11) * (1.0 / 9007199254740992.0); };  // [0, 1)
+  auto dv = [](double m, int c) {
+    if (c == 0) return 0.0;  // lut[0] = {0, 0}
+    const double cd = (double)c;
+    return div_small_int(m, __ddiv_rn(1.0, cd), cd);
+  };
+  for (int it = 0; it < iters; ++it) {
+    const unsigned long long r0 = next();
+    const bool small = (r0 & 15) < 11;
+    const int n = small ? (int)((r0 >> 8) % 5) : (int)((r0 >> 8) % 31);
+    const int p = small ? (int)((r0 >> 16) % 5) : (int)((r0 >> 16) % 31);
+    const bool neg = (r0 >> 32) & 1;
+    const double ns = (double)n * (1.0 - unit()), ps = (double)p * (1.0 - unit());
+    // fold_fast's constants
+    const double kk_n = dv((double)(n + 1), n + p + 1);
+    const double cst_n = __dmul_rn(100.0, dv(__dmul_rn(__dsub_rn(1.0, kk_n), ps), p));
+    const double kq_p = dv((double)n, n + p + 1);
+    const double kk_p = __dsub_rn(1.0, kq_p);
+    const double cst_p = __dmul_rn(100.0, dv(__dmul_rn(kq_p, ns), n));
+    const double tn = __dadd_rn(cst_n, __dmul_rn(100.0, dv(__dmul_rn(kk_n, __dadd_rn(ns, 0.0)), n + 1)));
+    const double tp = __dadd_rn(cst_p, __dmul_rn(100.0, dv(__dmul_rn(kk_p, __dadd_rn(ps, 0.0)), p + 1)));
+    const double Bn = 100.0 * kk_n * __ddiv_rn(1.0, (double)(n + 1)), Bp = 100.0 * kk_p * __ddiv_rn(1.0, (double)(p + 1));
+    const double A = neg ? tn : tp, B = neg ? Bn : Bp;
+    if (!(A >= 0.0 && B >= 0.0 && A + B <= kFilterMaxSum)) continue;  // the kernel switches the filter off here
+    double at;  // |t|
+    if ((it & 1) == 0) {
+      at = exp2(-20.0 + 30.0 * unit()) * (1.0 + unit());
+    } else {
+      const double vmax = neg ? 0.5 : 1.0;
+      const double lo = ceil(A), hi = floor(A + B * vmax);
+      if (!(hi >= lo) || B <= 0.0) continue;
+      const double k = lo + floor(unit() * (hi - lo + 1.0));
+      const unsigned sel = (unsigned)(next() & 7);
+      const double eps = sel == 0 ? 0.0 : (sel == 1 ? 1e-7 : (sel == 2 ? -1e-7 : (unit() - 0.5) * 2e-4));
+      double v = (k + eps - A) / B;
+      if (!(v > 1e-6)) v = 1e-6;
+      if (v > vmax) v = vmax;
+      const double z = 1.0 / v;
+      at = neg ? sqrt(z - 1.0) - 1.0 : z - 1.0;
+      if (!(at >= 0.0)) at = 0.0;
+    }
+    const float t = (next() & 1) ? (float)at : -(float)at;
+    if (!(fabsf(t) < 1.0e18f)) continue;
+    // exact float64 sequence (the kernel's exact path)
+    double w = fabs((double)t);
+    if (neg) w = __dadd_rn(w, 1.0);
+    if (neg) w = __dmul_rn(w, w);
+    const double v = rcp_ge1(__dadd_rn(1.0, w));
+    const int c = neg ? n + 1 : p + 1;
+    const double S = __dadd_rn(neg ? ns : ps, v);
+    const double q = dv(__dmul_rn(neg ? kk_n : kk_p, S), c);
+    const double tmp = __dadd_rn(neg ? cst_n : cst_p, __dmul_rn(100.0, q));
+    const int si = floor_nonneg(tmp);
+    // float32 estimate
+    const float est = filter_est((float)A, (float)B, filter_z(t, neg));
+    const float fl = filter_floor(est);
+    const float r = est - fl;
+    const double dev = fabs((double)est - tmp);
+    maxdev = dev > maxdev ? dev : maxdev;
+    ++done;
+    if (r >= kFilterDelta && r <= 1.0f - kFilterDelta) {
+      if ((int)fl != si) ++wrong;
+    } else {
+      ++band;
+    }
+  }
+  atomicMax(&out[0], (unsigned long long)__double_as_longlong(maxdev));
+  if (wrong) atomicAdd(&out[1], wrong);
+  atomicAdd(&out[2], band);
+  atomicAdd(&out[3], done);
+}
+
+cudaError_t launch_selftest_filter(unsigned long long seed, int blocks, int iters, unsigned long long* d_out,
+                                   cudaStream_t s) {
+  note_launch();
+  selftest_filter_kernel<<<blocks, 256, 0, s>>>(seed, iters, d_out);
+  return cudaGetLastError();
+}
+
+double filter_delta() { return (double)kFilterDelta; }
+
 cudaError_t launch_selftest(unsigned long long seed, int blocks, int iters, unsigned long long* d_mismatches,
                             cudaStream_t s) {
+  note_launch();
   selftest_kernel<<<blocks, 256, 0, s>>>(seed, iters, d_mismatches);
   return cudaGetLastError();
 }

@@ -56,6 +56,7 @@ __global__ void resident_prep_kernel(DevTables T, float4* __restrict__ res_rec) 
 cudaError_t launch_resident_prep(const DevTables& T, float4* res_rec, cudaStream_t s) {
   int slots = T.n_nodes * T.max_gpus;
   if (slots == 0) return cudaSuccess;
+  note_launch();
   resident_prep_kernel<<<(slots + 127) / 128, 128, 0, s>>>(T, res_rec);
   return cudaGetLastError();
 }
@@ -109,6 +110,7 @@ cudaError_t launch_score_direct(const DevTables& T, const uint32_t* pod_app, con
                                 unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s) {
   if (n_pods == 0 || T.n_nodes == 0) return cudaSuccess;
   dim3 grid((unsigned)n_pods, (unsigned)((T.n_nodes + kTile - 1) / kTile));
+  note_launch();
   score_direct_kernel<<<grid, kTile, 0, s>>>(T, pod_app, pod_slo, pod_self, score, sel, hi_arg, neg_lo);
   return cudaGetLastError();
 }
@@ -219,6 +221,7 @@ __global__ void pod_scatter_kernel(DevTables T, const uint32_t* __restrict__ pod
 cudaError_t launch_pod_histogram(const uint32_t* pod_app, int n_pods, int n_apps, uint32_t* counts, cudaStream_t s) {
   cudaError_t e = cudaMemsetAsync(counts, 0, sizeof(uint32_t) * (size_t)(n_apps + 2), s);
   if (e != cudaSuccess) return e;
+  note_launch();
   pod_hist_kernel<<<(n_pods + 255) / 256, 256, 0, s>>>(pod_app, n_pods, n_apps, counts);
   return cudaGetLastError();
 }
@@ -229,8 +232,11 @@ cudaError_t launch_pod_bucketing(const DevTables& T, const uint32_t* pod_app, co
   cudaError_t e = cudaMemsetAsync(sc.counts, 0, sizeof(uint32_t) * (size_t)(T.n_apps + 2), s);
   if (e != cudaSuccess) return e;
   int pb = (n_pods + 255) / 256;
+  note_launch();
   pod_hist_kernel<<<pb, 256, 0, s>>>(pod_app, n_pods, T.n_apps, sc.counts);
+  note_launch();
   pod_scan_kernel<<<1, 1024, 0, s>>>(T.n_apps, sc.counts, sc.cursor, sc.chunks, sc.n_chunks, sc.max_chunks);
+  note_launch();
   pod_scatter_kernel<<<pb, 256, 0, s>>>(T, pod_app, pod_slo, n_pods, sc.cursor, sc.sorted);
   return cudaGetLastError();
 }
@@ -288,6 +294,7 @@ cudaError_t launch_normalize(int n_pods, int n_nodes, int rescale, uint8_t* scor
                              const unsigned long long* hi_arg, const unsigned long long* neg_lo, int32_t* best,
                              cudaStream_t s) {
   if (n_pods == 0) return cudaSuccess;
+  note_launch();
   normalize_kernel<<<(n_pods + 3) / 4, 128, 0, s>>>(n_pods, n_nodes, rescale, score, hi_arg, neg_lo, best);
   return cudaGetLastError();
 }
@@ -325,6 +332,7 @@ __global__ void __launch_bounds__(1024) normalize_i64_kernel(long long* __restri
 
 cudaError_t launch_normalize_i64(long long* scores, int n, cudaStream_t s) {
   if (n == 0) return cudaSuccess;
+  note_launch();
   normalize_i64_kernel<<<1, 1024, 0, s>>>(scores, n);
   return cudaGetLastError();
 }
@@ -363,6 +371,7 @@ __global__ void select_mig_kernel(DevTables T, const uint32_t* __restrict__ pod_
 cudaError_t launch_select_mig(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
                               uint8_t* out, cudaStream_t s) {
   if (n_pods == 0) return cudaSuccess;
+  note_launch();
   select_mig_kernel<<<(n_pods + 255) / 256, 256, 0, s>>>(T, pod_app, pod_slo, n_pods, out);
   return cudaGetLastError();
 }

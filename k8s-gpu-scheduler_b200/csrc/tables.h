@@ -44,6 +44,9 @@ constexpr uint32_t kPodGeneral = 0x40000000u;  // SLO is NaN or infinite: genera
 constexpr uint32_t kPodInfInv = 0x20000000u;   // 1/SLO is infinite (SLO is 0 or denormal): every term is 0 or NaN
 constexpr uint32_t kPodIndexMask = 0x1FFFFFFFu;
 constexpr int kMaxPods = 1 << 29;
+// node tiles ride on grid.y (<= 65535 tiles of kTile nodes); per-GPU counts are packed into 16 bits
+constexpr int kMaxNodesPerCtx = 65535 * 128;
+constexpr int kMaxResidentsPerSlot = 65535;
 
 // A work item of the restructured kernel: up to kChunk pods of one app.
 struct ChunkDesc {
@@ -93,6 +96,11 @@ inline uint32_t max_chunks_for(int n_pods, int n_apps) {
 }
 constexpr int kStageTableMinPods = 256;  // smaller batches walk the resident lists in the scoring kernel
 
+// every kernel launch of the library is counted (gs_launch_count): bench.py reports the launches of
+// its timed region from this counter instead of assuming them
+void note_launch();
+unsigned long long launch_count();
+
 cudaError_t launch_resident_prep(const DevTables& T, float4* res_rec, cudaStream_t s);
 cudaError_t launch_score_direct(const DevTables& T, const uint32_t* pod_app, const float* pod_slo,
                                 const int32_t* pod_self, int n_pods, uint8_t* score, uint8_t* sel,
@@ -106,6 +114,9 @@ cudaError_t launch_score_fast(const DevTables& T, const uint32_t* pod_app, const
 cudaError_t launch_transpose_interf(const float* interf, float* interf_t, int n_apps, cudaStream_t s);
 cudaError_t launch_selftest(unsigned long long seed, int blocks, int iters, unsigned long long* d_mismatches,
                             cudaStream_t s);
+cudaError_t launch_selftest_filter(unsigned long long seed, int blocks, int iters, unsigned long long* d_out,
+                                   cudaStream_t s);
+double filter_delta();
 cudaError_t launch_pod_histogram(const uint32_t* pod_app, int n_pods, int n_apps, uint32_t* counts, cudaStream_t s);
 cudaError_t launch_stage_a(const DevTables& T, const uint32_t* counts, const StageA& stage, cudaStream_t s);
 cudaError_t launch_score_main(const DevTables& T, const PodScratch& sc, uint8_t* score, uint8_t* sel,

@@ -139,6 +139,10 @@ def test_redis_value_parsing_edge_cases(host):
         ('["GPU-1", 7]', 2),            # UnmarshalTypeError: the element keeps its zero value "", decoding goes on
         ('["GPU-\\u0031","MIG-\\"x\\""]', 2), ('["unterminated', 0),
         ('["a"] trailing', 0),          # invalid JSON: checkValid fails before anything is decoded
+        # malformed escapes make the document invalid (and must never be read past the terminator)
+        ('["\\u1', 0), ('["\\u12"]', 0), ('["\\uZZZZ"]', 0), ('["\\', 0), ('["\\u', 0), ('["\\x41"]', 0),
+        ('["a\tb"]', 0),                # raw control character inside a string
+        ('["\\u00e9\\ud83d\\ude00\\/"]', 1),   # UTF-8, a surrogate pair, the escaped solidus
     ]
     for i, (value, _) in enumerate(cases):
         b.add_node(f"gpu-node-{i}", value)

@@ -70,6 +70,62 @@ def test_noalloc_entry_point_matches_regular_entry_point(pkg, synth):
         sch.close()
 
 
+def test_noalloc_entry_point_matches_the_oracle(pkg, synth, oracle_mod):
+    """Not only the same bytes as the regular entry point: the same bytes as the CPU restatement of
+    the reference (raw scores, selection bytes, and — after the normalise phase — normalised
+    scores and best node)."""
+    import torch
+
+    dev = torch.device("cuda", 0)
+    sch = pkg.Scheduler(0)
+    try:
+        preds, cluster, pods = synth.make_workload(500, 260, gpus_per_node=8, n_apps=90, ragged_gpus=True,
+                                                   p_unknown_app=0.02)
+        sch.upload_predictions(preds)
+        sch.upload_cluster(cluster, node_base=7)
+        ora = oracle_mod.Oracle(preds, cluster)
+        want_raw = ora.score_batch(pods, normalize=False, node_base=7)
+        want_nrm = ora.score_batch(pods, normalize=True, node_base=7)
+        b = _device_batch(torch, pods, 260, dev)
+        best = torch.empty(pods.n_pods, dtype=torch.int32, device=dev)
+        stream = torch.cuda.Stream(device=dev)
+        with torch.cuda.stream(stream):
+            sch.score_raw_dev_noalloc(b["app"], b["slo"], pods.n_pods, b["score"], b["sel"], b["hi"], b["neg"],
+                                      stream=stream.cuda_stream)
+            stream.synchronize()
+            assert np.array_equal(b["score"].cpu().numpy(), want_raw[0])
+            assert np.array_equal(b["sel"].cpu().numpy(), want_raw[1])
+            sch.normalize_dev(pods.n_pods, b["score"], b["hi"], b["neg"], best, stream=stream.cuda_stream)
+            stream.synchronize()
+        assert np.array_equal(b["score"].cpu().numpy(), want_nrm[0])
+        assert np.array_equal(best.cpu().numpy(), want_nrm[2])
+    finally:
+        sch.close()
+
+
+def test_noalloc_entry_point_on_an_empty_node_shard(pkg, synth):
+    """A context that holds no node (a rank whose shard is empty) must still leave both per-pod
+    extrema at zero, as the regular entry point does: they go into the all-reduce(MAX) over ranks,
+    where stale values would corrupt every rank's minimum, maximum and best node."""
+    import torch
+
+    dev = torch.device("cuda", 0)
+    sch = pkg.Scheduler(0)
+    try:
+        preds, _, pods = synth.make_workload(64, 4, gpus_per_node=8, n_apps=16)
+        sch.upload_predictions(preds)
+        sch.upload_cluster(synth.make_cluster(0, 16, 8))
+        ref = _device_batch(torch, pods, 0, dev)
+        got = _device_batch(torch, pods, 0, dev)   # extrema start as garbage (-1)
+        sch.score_raw_dev(ref["app"], ref["slo"], pods.n_pods, ref["score"], ref["sel"], ref["hi"], ref["neg"])
+        sch.score_raw_dev_noalloc(got["app"], got["slo"], pods.n_pods, got["score"], got["sel"], got["hi"], got["neg"])
+        torch.cuda.synchronize()
+        assert int(got["hi"].abs().max()) == 0 and int(got["neg"].abs().max()) == 0
+        assert torch.equal(ref["hi"], got["hi"]) and torch.equal(ref["neg"], got["neg"])
+    finally:
+        sch.close()
+
+
 def test_noalloc_entry_point_refuses_oversize_batches(pkg, synth):
     import torch
 
