@@ -115,8 +115,8 @@ def test_noalloc_entry_point_on_an_empty_node_shard(pkg, synth):
         preds, _, pods = synth.make_workload(64, 4, gpus_per_node=8, n_apps=16)
         sch.upload_predictions(preds)
         sch.upload_cluster(synth.make_cluster(0, 16, 8))
-        ref = _device_batch(torch, pods, 0, dev)
-        got = _device_batch(torch, pods, 0, dev)   # extrema start as garbage (-1)
+        ref = _device_batch(torch, pods, 1, dev)   # (an empty [P, 0] tensor would be a null pointer)
+        got = _device_batch(torch, pods, 1, dev)   # extrema start as garbage (-1)
         sch.score_raw_dev(ref["app"], ref["slo"], pods.n_pods, ref["score"], ref["sel"], ref["hi"], ref["neg"])
         sch.score_raw_dev_noalloc(got["app"], got["slo"], pods.n_pods, got["score"], got["sel"], got["hi"], got["neg"])
         torch.cuda.synchronize()
