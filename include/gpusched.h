@@ -82,6 +82,8 @@ extern "C" {
 #define GS_SCORE_RAW 0u        /* out_score = what Score() returns (gpu_plugins.go:779-810) */
 #define GS_SCORE_NORMALIZE 1u  /* out_score = after NormalizeScore() (gpu_plugins.go:816-841) */
 #define GS_SCORE_DIRECT 2u     /* force the un-restructured one-thread-per-(pod,node) kernel */
+#define GS_SCORE_NO_DEDUPE 4u  /* score every pod itself, even pods with equal (app, SLO) (measurement) */
+#define GS_SCORE_LANES_NODES 8u /* restructured path: the one-thread-per-node kernel only (measurement) */
 
 /* ---------------------------------------------------------------- tables ----------- */
 
@@ -248,10 +250,12 @@ GS_API int gs_select_mig(gs_ctx* ctx, const uint32_t* pod_app, const float* pod_
 
 /* ---------------------------------------------------------------- measurement ------ */
 
-/* Instrumentation (no counterpart in the reference): when enabled, the scoring entry
- * points bracket their dominant kernel (the per-(pod,node) scoring kernel) with CUDA
- * events on the launching stream; gs_last_score_kernel_ms waits for the last bracket and
- * returns its duration.  Used by bench.py for the roofline figure. */
+/* Instrumentation (no counterpart in the reference): when enabled, gs_score_raw_dev records CUDA
+ * events on the launching stream before the residents-sum kernel (stage_a_kernel), between it and
+ * the scoring kernels, and after the scoring kernels.  gs_last_score_kernel_ms waits for the last
+ * bracket and returns the duration of the scoring kernels alone (score_pods_kernel and, for the work
+ * items it leaves, score_fast_kernel; score_direct_kernel with GS_SCORE_DIRECT); gs_last_stage_a_ms
+ * returns stage_a_kernel's.  Used by bench.py for the roofline figure. */
 GS_API int gs_set_profiling(gs_ctx* ctx, int enabled);
 /* Number of CUDA kernels this library has launched in this process so far (all contexts; copies
  * and memsets are not kernels).  bench.py reports the difference over its timed region. */
@@ -262,6 +266,7 @@ GS_API uint64_t gs_launch_count(void);
  * results that differ in any bit (must be 0). */
 GS_API int gs_selftest(gs_ctx* ctx, uint64_t seed, int32_t n_million, uint64_t* out_mismatches);
 GS_API int gs_last_score_kernel_ms(gs_ctx* ctx, float* out_ms);
+GS_API int gs_last_stage_a_ms(gs_ctx* ctx, float* out_ms);
 /* Filter self-test (no counterpart in the reference): the scoring kernel decides int64(tmpScore)
  * (gpu_plugins.go:752) from a float32 estimate wherever that estimate lies farther than
  * *out_delta from an integer, and only otherwise runs the float64 sequence.  This runs both on

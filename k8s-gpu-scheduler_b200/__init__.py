@@ -21,7 +21,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("GS_LIB_PATH") or os.path.join(_HERE, "libgpusched.so")
 
 GS_OK = 0
-SCORE_RAW, SCORE_NORMALIZE, SCORE_DIRECT = 0, 1, 2
+SCORE_RAW, SCORE_NORMALIZE, SCORE_DIRECT, SCORE_NO_DEDUPE, SCORE_LANES_NODES = 0, 1, 2, 4, 8
 SEL_NONE = 31
 NOALLOC_MAX_PODS, NOALLOC_MAX_APPS, NOALLOC_MAX_RESIDENTS = 65536, 4096, 131072
 ERR_NAMES = {-1: "GS_ERR_INVALID", -2: "GS_ERR_CUDA", -3: "GS_ERR_STATE", -4: "GS_ERR_NOMEM",
@@ -31,7 +31,7 @@ ERR_NAMES = {-1: "GS_ERR_INVALID", -2: "GS_ERR_CUDA", -3: "GS_ERR_STATE", -4: "G
 EXPORTS = [
     "gs_create", "gs_destroy", "gs_last_error", "gs_version", "gs_upload_cluster", "gs_upload_predictions",
     "gs_score_batch", "gs_score_raw_dev", "gs_score_raw_dev_noalloc", "gs_normalize_dev", "gs_normalize_scores", "gs_select_mig",
-    "gs_set_profiling", "gs_last_score_kernel_ms", "gs_selftest", "gs_selftest_filter", "gs_launch_count", "gs_complete_fit", "gs_complete_fit_sharded", "gs_complete_fit_transform", "gs_complete_transform", "gs_model_info", "gs_model_step", "gs_model_destroy",
+    "gs_set_profiling", "gs_last_score_kernel_ms", "gs_last_stage_a_ms", "gs_selftest", "gs_selftest_filter", "gs_launch_count", "gs_complete_fit", "gs_complete_fit_sharded", "gs_complete_fit_transform", "gs_complete_transform", "gs_model_info", "gs_model_step", "gs_model_destroy",
 ]
 
 
@@ -86,6 +86,7 @@ def load_library():
     L.gs_select_mig.argtypes = [vp, vp, vp, i32, vp]
     L.gs_set_profiling.argtypes = [vp, C.c_int]
     L.gs_last_score_kernel_ms.argtypes = [vp, C.POINTER(C.c_float)]
+    L.gs_last_stage_a_ms.argtypes = [vp, C.POINTER(C.c_float)]
     L.gs_selftest.argtypes = [vp, C.c_uint64, i32, C.POINTER(C.c_uint64)]
     L.gs_selftest_filter.argtypes = [vp, C.c_uint64, i32, C.POINTER(C.c_double), C.POINTER(C.c_double),
                                      C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
@@ -165,7 +166,8 @@ class Scheduler:
         self._check(self._L.gs_upload_predictions(self._h, C.byref(s)))
 
     # -- scoring, host buffers --------------------------------------------------------
-    def score_batch(self, pods: Pods, normalize: bool = True, direct: bool = False, out=None, want_matrices=True):
+    def score_batch(self, pods: Pods, normalize: bool = True, direct: bool = False, out=None, want_matrices=True,
+                    flags: int = 0):
         """Score + (optionally) NormalizeScore for every (pod,node): returns (score, sel, best)."""
         app = np.ascontiguousarray(pods.app, dtype=np.uint32)
         slo = np.ascontiguousarray(pods.slo, dtype=np.float32)
@@ -180,16 +182,16 @@ class Scheduler:
         else:
             score = sel = None
             best = np.empty(P, dtype=np.int32)
-        flags = (SCORE_NORMALIZE if normalize else 0) | (SCORE_DIRECT if direct else 0)
+        flags = int(flags) | (SCORE_NORMALIZE if normalize else 0) | (SCORE_DIRECT if direct else 0)
         self._check(self._L.gs_score_batch(self._h, _ptr(app), _ptr(slo), _ptr(self_slot), P, flags, _ptr(score),
                                            _ptr(sel), _ptr(best)))
         return score, sel, best
 
     # -- scoring, device pointers (torch tensors or raw addresses) ----------------------
     def score_raw_dev(self, d_app, d_slo, n_pods, d_score, d_sel, d_hi_arg, d_neg_lo, d_self=None, direct=False,
-                      stream=None):
+                      stream=None, flags: int = 0):
         self._check(self._L.gs_score_raw_dev(self._h, _ptr(d_app), _ptr(d_slo), _ptr(d_self), int(n_pods),
-                                             SCORE_DIRECT if direct else 0, _ptr(d_score), _ptr(d_sel),
+                                             int(flags) | (SCORE_DIRECT if direct else 0), _ptr(d_score), _ptr(d_sel),
                                              _ptr(d_hi_arg), _ptr(d_neg_lo), _ptr(stream)))
 
     def score_raw_dev_noalloc(self, d_app, d_slo, n_pods, d_score, d_sel, d_hi_arg, d_neg_lo, stream=None):
@@ -208,6 +210,11 @@ class Scheduler:
     def last_score_kernel_ms(self) -> float:
         ms = C.c_float(0)
         self._check(self._L.gs_last_score_kernel_ms(self._h, C.byref(ms)))
+        return float(ms.value)
+
+    def last_stage_a_ms(self) -> float:
+        ms = C.c_float(0)
+        self._check(self._L.gs_last_stage_a_ms(self._h, C.byref(ms)))
         return float(ms.value)
 
     def selftest(self, seed: int = 1, n_million: int = 100) -> int:

@@ -118,12 +118,21 @@ int Ctx::ensure_prepared() {
 
 int Ctx::ensure_scratch(int n_pods) {
   uint32_t mc = max_chunks_for(n_pods, n_apps);
+  const size_t nb = (size_t)n_buckets_for(n_apps) + 4;
+  const size_t np = (size_t)(n_pods ? n_pods : 1);
   int rc;
-  if ((rc = reserve(sc_counts, sizeof(uint32_t) * (size_t)(n_apps + 2), "pod bucket counts"))) return rc;
-  if ((rc = reserve(sc_cursor, sizeof(uint32_t) * (size_t)(n_apps + 2), "pod bucket cursors"))) return rc;
+  if ((rc = reserve(sc_counts, sizeof(uint32_t) * nb, "pod bucket counts"))) return rc;
+  if ((rc = reserve(sc_cursor, sizeof(uint32_t) * nb, "pod bucket cursors"))) return rc;
   if ((rc = reserve(sc_nchunks, 256, "chunk counter"))) return rc;
   if ((rc = reserve(sc_chunks, sizeof(ChunkDesc) * (size_t)mc, "chunk descriptors"))) return rc;
-  if ((rc = reserve(sc_sorted, sizeof(PodRec) * (size_t)(n_pods ? n_pods : 1), "sorted pods"))) return rc;
+  if ((rc = reserve(sc_sorted, sizeof(PodRec) * np, "sorted pods"))) return rc;
+  if ((rc = reserve(sc_bucket, sizeof(uint32_t) * np, "pod buckets"))) return rc;
+  if (dedupe) {
+    const size_t hs = hash_size_for(n_pods);
+    if ((rc = reserve(sc_rep, sizeof(uint32_t) * np, "class representatives"))) return rc;
+    if ((rc = reserve(sc_hkeys, sizeof(unsigned long long) * hs, "class table keys"))) return rc;
+    if ((rc = reserve(sc_hvals, sizeof(uint32_t) * hs, "class table values"))) return rc;
+  }
   // residents-sum table: 24 bytes per (app bucket, GPU slot), if it fits the budget
   const size_t entries = (size_t)(n_apps + 1) * (size_t)n_nodes * (size_t)max_gpus;
   if (n_pods >= kStageTableMinPods && entries * 24 <= stage_budget) {
@@ -132,14 +141,25 @@ int Ctx::ensure_scratch(int n_pods) {
   return GS_OK;
 }
 
-PodScratch Ctx::scratch_view(int n_pods) const {
+PodScratch Ctx::scratch_view(int n_pods, bool use_dedupe) const {
   PodScratch sc;
   sc.counts = (uint32_t*)sc_counts.p;
   sc.cursor = (uint32_t*)sc_cursor.p;
   sc.n_chunks = (uint32_t*)sc_nchunks.p;
   sc.chunks = (ChunkDesc*)sc_chunks.p;
   sc.sorted = (PodRec*)sc_sorted.p;
+  sc.bucket = (uint32_t*)sc_bucket.p;
   sc.max_chunks = max_chunks_for(n_pods, n_apps);
+  sc.rep = nullptr;
+  sc.hkeys = nullptr;
+  sc.hvals = nullptr;
+  sc.hash_size = 0;
+  if (use_dedupe && dedupe && sc_rep.p) {
+    sc.rep = (uint32_t*)sc_rep.p;
+    sc.hkeys = (unsigned long long*)sc_hkeys.p;
+    sc.hvals = (uint32_t*)sc_hvals.p;
+    sc.hash_size = hash_size_for(n_pods);
+  }
   sc.stage = StageA{nullptr, nullptr, nullptr, nullptr, 0};
   const size_t entries = (size_t)(n_apps + 1) * (size_t)n_nodes * (size_t)max_gpus;
   const size_t e8 = (entries + 31) / 32 * 32;  // keep every array 256-byte aligned
@@ -185,6 +205,8 @@ int gs_create(int device, gs_ctx** out) {
   if (!c) return GS_ERR_NOMEM;
   c->device = device;
   if (const char* mb = getenv("GS_STAGE_TABLE_MB")) c->stage_budget = (size_t)strtoull(mb, nullptr, 10) << 20;
+  if (const char* v = getenv("GS_NO_DEDUPE")) c->dedupe = atoi(v) == 0;
+  if (const char* v = getenv("GS_LANES_NODES")) c->lanes_nodes = atoi(v) != 0;
   if (cudaSetDevice(device) != cudaSuccess ||
       cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreateWithFlags(&c->ev_last_use, cudaEventDisableTiming) != cudaSuccess) {
@@ -205,14 +227,14 @@ void gs_destroy(gs_ctx* c) {
     cudaStreamSynchronize(c->stream);
     gs::DevBuf* bufs[] = {&c->node_orig, &c->res_new, &c->node_model, &c->node_ngpu, &c->gpu_off,   &c->res_app,   &c->res_slo, &c->conf,
                           &c->interf,     &c->interf_t,  &c->sc_stage,  &c->col_of,    &c->res_rec,   &c->sc_counts, &c->sc_cursor,
-                          &c->sc_nchunks, &c->sc_chunks, &c->sc_sorted, &c->sc_counts_all, &c->b_pod_app, &c->b_pod_slo,
+                          &c->sc_nchunks, &c->sc_chunks, &c->sc_sorted, &c->sc_counts_all, &c->sc_bucket, &c->sc_rep, &c->sc_hkeys, &c->sc_hvals, &c->b_pod_app, &c->b_pod_slo,
                           &c->b_pod_self, &c->b_score,   &c->b_sel,     &c->b_extrema, &c->b_best,  &c->b_misc};
     for (gs::DevBuf* b : bufs) c->release(*b);
     for (auto& ev : c->ev_chunk)
       if (ev) cudaEventDestroy(ev);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
-    if (c->ev_begin) cudaEventDestroy(c->ev_begin);
-    if (c->ev_end) cudaEventDestroy(c->ev_end);
+    for (auto& ev : c->ev_prof)
+      if (ev) cudaEventDestroy(ev);
     if (c->ev_last_use) cudaEventDestroy(c->ev_last_use);
     cudaStreamDestroy(c->stream);
   }
@@ -256,27 +278,13 @@ int gs_upload_cluster(gs_ctx* c, const gs_cluster* cl, int32_t node_base) {
   if (R && (!cl->res_app || !cl->res_slo)) return c->fail(GS_ERR_INVALID, "gs_upload_cluster: null resident table");
   GS_CUDA(c, cudaSetDevice(c->device));
   if (int rcw = c->wait_last_use()) return rcw;  // asynchronous scoring on a caller stream may still read the tables
-  // Internal node order: within every block of kGroupBlock consecutive nodes, the nodes whose
-  // GPU loop runs (model and >= 1 UUID) are grouped by model, the rest last — a stable
-  // partition, so that most warps hold 32 nodes of one model and can skip what none of them
-  // needs.  Results are written in the CALLER's node order (node_orig maps back); grouping
-  // inside blocks rather than globally keeps the writers of one 32-byte output sector close in
-  // time, so L2 merges them (a global grouping measured 2.2 GB of extra DRAM read-modify-write).
-  // Residents move with their nodes, order within a GPU unchanged.
-  constexpr size_t kGroupBlock = 256;
+  // Internal node order.  Round 1 grouped the nodes of every 256-block by model so that the warps of
+  // the one-thread-per-node kernel were homogeneous; the lanes-are-pods kernel evaluates nodes from
+  // per-slice lists instead and wants consecutive internal nodes to be consecutive bytes of a result
+  // row, so the order is now the caller's.  (node_orig / res_new stay, as identities, for the kernels
+  // that were written against them.)
   std::vector<uint32_t> order(N), res_new(R ? R : 1);
-  {
-    size_t w = 0;
-    for (size_t b0 = 0; b0 < N; b0 += kGroupBlock) {
-      const size_t b1 = std::min(N, b0 + kGroupBlock);
-      for (int pass = 0; pass < 3; ++pass)
-        for (size_t n = b0; n < b1; ++n) {
-          const bool scored = cl->node_model[n] != GS_MODEL_NONE && cl->node_ngpu[n] > 0;
-          const int cls = !scored ? 2 : (cl->node_model[n] == GS_MODEL_A30 ? 0 : 1);
-          if (cls == pass) order[w++] = (uint32_t)n;
-        }
-    }
-  }
+  for (size_t n = 0; n < N; ++n) order[n] = (uint32_t)n;
   std::vector<uint8_t> p_model(N ? N : 1), p_ngpu(N ? N : 1);
   std::vector<uint32_t> p_off(slots + 1), p_app(R ? R : 1);
   std::vector<float> p_slo(R ? R : 1);
@@ -359,26 +367,26 @@ static int score_raw_locked(gs_ctx* c, const uint32_t* d_app, const float* d_slo
   cudaError_t e;
   if (fast && (rc = c->ensure_scratch(P))) return rc;
   if (c->profiling) {
-    if (!c->ev_begin) {
-      GS_CUDA(c, cudaEventCreate(&c->ev_begin));
-      GS_CUDA(c, cudaEventCreate(&c->ev_end));
-    }
+    for (auto& ev : c->ev_prof)
+      if (!ev) GS_CUDA(c, cudaEventCreate(&ev));
     c->ev_valid = false;
   }
+  const bool lanes_nodes = c->lanes_nodes || (flags & GS_SCORE_LANES_NODES);
   if (fast) {
-    gs::PodScratch sc = c->scratch_view(P);
+    gs::PodScratch sc = c->scratch_view(P, !(flags & GS_SCORE_NO_DEDUPE));
     e = gs::launch_score_fast(T, d_app, d_slo, P, sc, d_score, d_sel, (unsigned long long*)d_hi,
-                              (unsigned long long*)d_neg, s, c->profiling ? c->ev_begin : nullptr);
+                              (unsigned long long*)d_neg, s, c->profiling ? c->ev_prof : nullptr, lanes_nodes);
   } else {
-    if (c->profiling) GS_CUDA(c, cudaEventRecord(c->ev_begin, s));
+    if (c->profiling) {
+      GS_CUDA(c, cudaEventRecord(c->ev_prof[0], s));
+      GS_CUDA(c, cudaEventRecord(c->ev_prof[1], s));
+    }
     e = gs::launch_score_direct(T, d_app, d_slo, d_self, P, d_score, d_sel, (unsigned long long*)d_hi,
                                 (unsigned long long*)d_neg, s);
+    if (c->profiling) GS_CUDA(c, cudaEventRecord(c->ev_prof[2], s));
   }
   if (e != cudaSuccess) return c->cuda_fail(e, fast ? "score_fast" : "score_direct");
-  if (c->profiling) {
-    GS_CUDA(c, cudaEventRecord(c->ev_end, s));
-    c->ev_valid = true;
-  }
+  if (c->profiling) c->ev_valid = true;
   return c->note_use(s);
 }
 
@@ -456,7 +464,7 @@ int gs_score_batch(gs_ctx* c, const uint32_t* pod_app, const float* pod_slo, con
   if (n_slices > 1) {
     if ((rc = c->ensure_prepared())) return rc;
     if ((rc = c->ensure_scratch(P))) return rc;
-    if ((rc = c->reserve(c->sc_counts_all, sizeof(uint32_t) * (size_t)(c->n_apps + 2), "bucket counts (batch)"))) return rc;
+    if ((rc = c->reserve(c->sc_counts_all, sizeof(uint32_t) * (size_t)(gs::n_buckets_for(c->n_apps) + 4), "bucket counts (batch)"))) return rc;
     if (!c->copy_stream) {
       GS_CUDA(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
       for (auto& ev : c->ev_chunk) GS_CUDA(c, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
@@ -477,12 +485,16 @@ int gs_score_batch(gs_ctx* c, const uint32_t* pod_app, const float* pod_slo, con
     for (int k = 0; k < n_slices; ++k) {
       const int p0 = k * per, np = std::min(per, P - p0);
       if (np <= 0) break;
-      gs::PodScratch sc = c->scratch_view(np);
+      gs::PodScratch sc = c->scratch_view(np, !(flags & GS_SCORE_NO_DEDUPE));
+      sc.stage = whole.stage;  // the table covers the batch's apps (built above), whatever the slice size
       const size_t row0 = (size_t)p0 * N;
       e = gs::launch_pod_bucketing(T, d_app + p0, d_slo + p0, np, sc, s);
       if (e == cudaSuccess)
-        e = gs::launch_score_main(T, sc, d_score + row0, d_sel + row0, (unsigned long long*)(d_hi + p0),
-                                  (unsigned long long*)(d_neg + p0), s);
+        e = gs::launch_score_any(T, sc, d_score + row0, d_sel + row0, (unsigned long long*)(d_hi + p0),
+                                 (unsigned long long*)(d_neg + p0), s, c->lanes_nodes || (flags & GS_SCORE_LANES_NODES));
+      if (e == cudaSuccess)
+        e = gs::launch_expand_classes(T, sc.rep, np, d_score + row0, d_sel + row0, (unsigned long long*)(d_hi + p0),
+                                      (unsigned long long*)(d_neg + p0), s);
       if (e == cudaSuccess)
         e = gs::launch_normalize(np, c->n_nodes, rescale, d_score + row0, (const unsigned long long*)(d_hi + p0),
                                  (const unsigned long long*)(d_neg + p0), d_best + p0, s);
@@ -550,8 +562,19 @@ int gs_last_score_kernel_ms(gs_ctx* c, float* out_ms) {
   if (!out_ms) return c->fail(GS_ERR_INVALID, "gs_last_score_kernel_ms: null output");
   if (!c->profiling || !c->ev_valid) return c->fail(GS_ERR_STATE, "no profiled scoring call to report");
   GS_CUDA(c, cudaSetDevice(c->device));
-  GS_CUDA(c, cudaEventSynchronize(c->ev_end));
-  GS_CUDA(c, cudaEventElapsedTime(out_ms, c->ev_begin, c->ev_end));
+  GS_CUDA(c, cudaEventSynchronize(c->ev_prof[2]));
+  GS_CUDA(c, cudaEventElapsedTime(out_ms, c->ev_prof[1], c->ev_prof[2]));
+  return GS_OK;
+}
+
+int gs_last_stage_a_ms(gs_ctx* c, float* out_ms) {
+  if (!c) return GS_ERR_INVALID;
+  GS_LOCK(c);
+  if (!out_ms) return c->fail(GS_ERR_INVALID, "gs_last_stage_a_ms: null output");
+  if (!c->profiling || !c->ev_valid) return c->fail(GS_ERR_STATE, "no profiled scoring call to report");
+  GS_CUDA(c, cudaSetDevice(c->device));
+  GS_CUDA(c, cudaEventSynchronize(c->ev_prof[1]));
+  GS_CUDA(c, cudaEventElapsedTime(out_ms, c->ev_prof[0], c->ev_prof[1]));
   return GS_OK;
 }
 

@@ -33,6 +33,9 @@ struct Ctx {
   DevBuf res_rec;
   // scratch of the restructured scoring path
   DevBuf sc_counts, sc_cursor, sc_nchunks, sc_chunks, sc_sorted, sc_stage, sc_counts_all;
+  DevBuf sc_bucket, sc_rep, sc_hkeys, sc_hvals;
+  bool dedupe = true;       // class dedupe on (GS_NO_DEDUPE=1 in the environment, or GS_SCORE_NO_DEDUPE per call, turns it off)
+  bool lanes_nodes = false; // GS_LANES_NODES=1: always the one-thread-per-node kernel
   // host-buffer entry point: second stream + events to overlap the device->host copies with compute
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_chunk[8] = {};
@@ -45,6 +48,8 @@ struct Ctx {
   bool profiling = false;
   bool ev_valid = false;
   cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+  cudaEvent_t ev_prof[3] = {};  // before stage A, after it, after the scoring kernel
+  bool ev_prof_valid = false;
   // recorded after the last launch of every device-pointer scoring call (on the caller's stream);
   // table uploads wait for it, so that a re-upload never overwrites tables a kernel still reads
   cudaEvent_t ev_last_use = nullptr;
@@ -59,7 +64,7 @@ struct Ctx {
   DevTables tables() const;
   int ensure_prepared();
   int ensure_scratch(int n_pods);
-  PodScratch scratch_view(int n_pods) const;
+  PodScratch scratch_view(int n_pods, bool use_dedupe = true) const;
 };
 
 cudaError_t launch_normalize_i64(long long* scores, int n, cudaStream_t s);

@@ -33,17 +33,19 @@ using namespace gs;
 constexpr int kNaMaxPods = GS_NOALLOC_MAX_PODS;
 constexpr int kNaMaxApps = GS_NOALLOC_MAX_APPS;
 constexpr int kNaMaxResidents = GS_NOALLOC_MAX_RESIDENTS;
-constexpr size_t kNaMaxChunks = (size_t)kNaMaxPods / kChunk + kNaMaxApps + 2;
+constexpr size_t kNaBuckets = (size_t)(kNaMaxApps + 1) * kKinds + 4;
+constexpr size_t kNaMaxChunks = (size_t)kNaMaxPods / kChunk + kNaBuckets + 1;
 
 constexpr size_t align256(size_t x) { return (x + 255) / 256 * 256; }
 // carve-up of the array
 constexpr size_t kOffResRec = 0;
 constexpr size_t kOffCounts = kOffResRec + align256(sizeof(float4) * (size_t)kNaMaxResidents);
-constexpr size_t kOffCursor = kOffCounts + align256(sizeof(uint32_t) * (size_t)(kNaMaxApps + 2));
-constexpr size_t kOffNChunks = kOffCursor + align256(sizeof(uint32_t) * (size_t)(kNaMaxApps + 2));
+constexpr size_t kOffCursor = kOffCounts + align256(sizeof(uint32_t) * kNaBuckets);
+constexpr size_t kOffNChunks = kOffCursor + align256(sizeof(uint32_t) * kNaBuckets);
 constexpr size_t kOffChunks = kOffNChunks + 256;
 constexpr size_t kOffSorted = kOffChunks + align256(sizeof(ChunkDesc) * kNaMaxChunks);
-constexpr size_t kScratchBytes = kOffSorted + align256(sizeof(PodRec) * (size_t)kNaMaxPods);
+constexpr size_t kOffBucket = kOffSorted + align256(sizeof(PodRec) * (size_t)kNaMaxPods);
+constexpr size_t kScratchBytes = kOffBucket + align256(sizeof(uint32_t) * (size_t)kNaMaxPods);
 static_assert(kScratchBytes <= (size_t)4 << 20, "keep the resident scratch modest");
 
 // The scratch itself.  In host code this NAME is only a host-side stand-in for the symbol,
@@ -120,6 +122,11 @@ extern "C" int gs_score_raw_dev_noalloc(gs_ctx* ctx, const uint32_t* d_pod_app, 
   sc.n_chunks = reinterpret_cast<uint32_t*>(base + kOffNChunks);
   sc.chunks = reinterpret_cast<gs::ChunkDesc*>(base + kOffChunks);
   sc.sorted = reinterpret_cast<gs::PodRec*>(base + kOffSorted);
+  sc.bucket = reinterpret_cast<uint32_t*>(base + kOffBucket);
+  sc.rep = nullptr;  // no class dedupe here: its hash table would double the resident array
+  sc.hkeys = nullptr;
+  sc.hvals = nullptr;
+  sc.hash_size = 0;
   sc.max_chunks = gs::max_chunks_for(n_pods, c->n_apps);
   sc.stage = gs::StageA{nullptr, nullptr, nullptr, nullptr, 0};  // no residents-sum table: too large to hold statically
   e = gs::launch_score_fast(T, d_pod_app, d_pod_slo, n_pods, sc, d_score, d_sel, (unsigned long long*)d_hi_arg,

@@ -38,11 +38,9 @@
 // Pods whose SLO is NaN/Inf, lanes whose float32 term could overflow, and nodes whose
 // sums are not finite take the general path (score_common.cuh's op-for-op logic_eval) —
 // chosen per warp, so the streamlined loop is divergence-free.
-#include "score_common.cuh"
+#include "score_fold.cuh"
 
 namespace gs {
-
-constexpr int kLutSize = 64;  // counts the {1/c, c} table covers
 
 template <int GT>
 struct FastSmem {
@@ -54,73 +52,8 @@ struct FastSmem {
   uint32_t neg[kTile / 32][kStage];
 };
 static_assert(sizeof(FastSmem<kFastMaxGpus>) <= 48 * 1024, "static shared memory");
+static_assert(kKinds == 4, "stage_a_kernel reads the four kind counts of an app as one uint4");
 static_assert(kStage == kTile, "a CTA stages its pods with one thread each");
-
-// m / c for a count c: the table form where its preconditions hold, IEEE division otherwise
-// (both correctly rounded, hence identical).
-__device__ __forceinline__ double div_count(double m, int c, const double2* lut) {
-  const double am = fabs(m);
-  if (c < kLutSize && (am == 0.0 || (am > 1e-250 && am < 1e300))) {
-    const double2 e = lut[c];
-    return div_small_int(m, e.x, e.y);
-  }
-  return __ddiv_rn(m, (double)c);
-}
-
-// combine() of score_math.cuh with the divisions by counts done through the table
-__device__ __forceinline__ double combine_lut(double neg_sum, double pos_sum, int cn, int cp, const double2* lut) {
-  double tmp = 0.0;
-  if (cn > 0 && cp > 0) {
-    const double k = div_count((double)cn, cn + cp, lut);
-    const double a = __dmul_rn(100.0, div_count(__dmul_rn(__dsub_rn(1.0, k), pos_sum), cp, lut));
-    const double b = __dmul_rn(100.0, div_count(__dmul_rn(k, neg_sum), cn, lut));
-    tmp = __dadd_rn(a, b);
-  } else if (cn > 0) {
-    tmp = __dmul_rn(100.0, div_count(neg_sum, cn, lut));
-  } else if (cp > 0) {
-    tmp = __dmul_rn(100.0, div_count(pos_sum, cp, lut));
-  }
-  return tmp;
-}
-
-// {kk, cst} of one branch: everything of the weighted combine that does not depend on the
-// candidate's own term, with the operations and their order as in combine() (x*1.0 and 0.0+x are
-// exact, so an absent side contributes kk = 1, cst = 0).
-__device__ __forceinline__ double2 branch_const(bool neg, double neg_sum, double pos_sum, int cn0, int cp0,
-                                                const double2* lut) {
-  double kk = 1.0, cst = 0.0;
-  if (neg) {
-    if (cp0 > 0) {  // candidate lands on the negative side, positives exist
-      const double kq = div_count((double)(cn0 + 1), cn0 + 1 + cp0, lut);
-      kk = kq;
-      cst = __dmul_rn(100.0, div_count(__dmul_rn(__dsub_rn(1.0, kq), pos_sum), cp0, lut));
-    }
-  } else if (cn0 > 0) {  // candidate lands on the positive side, negatives exist
-    const double kq = div_count((double)cn0, cn0 + cp0 + 1, lut);
-    kk = __dsub_rn(1.0, kq);
-    cst = __dmul_rn(100.0, div_count(__dmul_rn(kq, neg_sum), cn0, lut));
-  }
-  return make_double2(kk, cst);
-}
-
-// Float32 filter constants.  With A, B >= 0 and A + B <= kFilterMaxSum the float32 estimate
-//   est = fma(B32, rcp_approx(z32), A32),  z32 = 1 + |t|  or  fma(1 + |t|, 1 + |t|, 1)
-// differs from the reference's float64 tmp by less than
-//   2u*A (rounding A, the final fma) + 7u*B*v (rounding B, z32: at most 3u relative, the
-//   approximate reciprocal: 1 ulp = 2u, the final fma)  <=  7u * kFilterMaxSum = 4.2e-5,  u = 2^-24,
-// plus the float64 roundings of tmp itself and of A, B (below 1e-11).  Mathematically A + B <= 100
-// (it is tmp at v = 1, a weighted mean of values in [0, 1] times 100); constants outside
-// [0, kFilterMaxSum] switch the filter off for their GPU.  kFilterDelta = 2^-14 = 6.1e-5 leaves a
-// factor of 1.45 (still 1.1 if the reciprocal were 2 ulp off).  -DGS_FILTER_DELTA_LOG2=13
-// -DGS_FILTER_MAX_SUM=128 is the wider margin the first version ran with (5 % slower).
-#ifndef GS_FILTER_DELTA_LOG2
-#define GS_FILTER_DELTA_LOG2 14
-#endif
-#ifndef GS_FILTER_MAX_SUM
-#define GS_FILTER_MAX_SUM 100.5
-#endif
-constexpr float kFilterDelta = 1.0f / (float)(1 << GS_FILTER_DELTA_LOG2);
-constexpr double kFilterMaxSum = GS_FILTER_MAX_SUM;  // A + B may not exceed this
 
 // ------------------------------------------------------------------ stage A ----------
 
@@ -144,7 +77,11 @@ __global__ void __launch_bounds__(256) stage_a_kernel(DevTables T, const uint32_
   const int s0 = blockIdx.x * kStageTile, a0 = blockIdx.y * kStageTile;
   const int app_idx = a0 + lane;  // bucket n_apps = pods whose app is unknown
   const bool app_known = app_idx < T.n_apps;
-  const bool wanted = app_idx <= T.n_apps && counts[app_idx] > 0;
+  bool wanted = false;  // does any (app, kind) bucket of this app hold pods?
+  if (app_idx <= T.n_apps) {
+    const uint4 c4 = *reinterpret_cast<const uint4*>(counts + (size_t)app_idx * kKinds);
+    wanted = (c4.x | c4.y | c4.z | c4.w) != 0u;
+  }
   if (warp == 0) {
     const int slot = s0 + lane;
     int model = kModelNone;
@@ -244,12 +181,13 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
                                                              uint8_t* __restrict__ out_score,
                                                              uint8_t* __restrict__ out_sel,
                                                              unsigned long long* hi_arg,
-                                                             unsigned long long* neg_lo) {
+                                                             unsigned long long* neg_lo, int skip_plain) {
   __shared__ FastSmem<GT> sm_storage;
   FastSmem<GT>* sm = &sm_storage;
   if (blockIdx.x >= *n_chunks) return;
   const int tid = threadIdx.x;
   const ChunkDesc cd = chunks[blockIdx.x];
+  if (skip_plain && (cd.kind & 0xFFu) == (uint32_t)kKindPlain) return;  // served by score_pods_kernel
   if (tid < kLutSize) sm->lut[tid] = make_double2(tid ? __ddiv_rn(1.0, (double)tid) : 0.0, (double)tid);
 
   const uint32_t tile_node0 = blockIdx.y * kTile;
@@ -636,11 +574,11 @@ cudaError_t launch_stage_a(const DevTables& T, const uint32_t* counts, const Sta
 
 // the scoring kernel over the work items that launch_pod_bucketing left in `sc`
 cudaError_t launch_score_main(const DevTables& T, const PodScratch& sc, uint8_t* score, uint8_t* sel,
-                              unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s) {
+                              unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s, bool skip_plain) {
   dim3 grid(sc.max_chunks, (unsigned)((T.n_nodes + kTile - 1) / kTile));
 #define GS_LAUNCH_FAST(TABLE, GT)                                                                                  \
   score_fast_kernel<TABLE, GT><<<grid, kTile, 0, s>>>(T, sc.stage, sc.sorted, sc.chunks, sc.n_chunks, score, sel, \
-                                                      hi_arg, neg_lo)
+                                                      hi_arg, neg_lo, skip_plain ? 1 : 0)
   const bool table = sc.stage.n0 != nullptr;
   note_launch();
   if (T.max_gpus <= 2) {
@@ -654,15 +592,29 @@ cudaError_t launch_score_main(const DevTables& T, const PodScratch& sc, uint8_t*
   return cudaGetLastError();
 }
 
+// the lanes-are-pods kernel needs the stage-A table and at most 8 GPU slots; everything else (small
+// batches, tables beyond the budget, the no-allocation entry point) runs the one-thread-per-node kernel
+cudaError_t launch_score_any(const DevTables& T, const PodScratch& sc, uint8_t* score, uint8_t* sel,
+                             unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s, bool lanes_nodes) {
+  if (!lanes_nodes && sc.stage.n0 != nullptr && T.max_gpus == kFastMaxGpus)
+    return launch_score_pods(T, sc, score, sel, hi_arg, neg_lo, s);
+  return launch_score_main(T, sc, score, sel, hi_arg, neg_lo, s, false);
+}
+
+// prof (optional) = three events: before stage A, between stage A and the scoring kernel, after the
+// scoring kernel (the class expansion that follows is outside the bracket)
 cudaError_t launch_score_fast(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
                               const PodScratch& sc, uint8_t* score, uint8_t* sel, unsigned long long* hi_arg,
-                              unsigned long long* neg_lo, cudaStream_t s, cudaEvent_t before_main) {
+                              unsigned long long* neg_lo, cudaStream_t s, const cudaEvent_t* prof, bool lanes_nodes) {
   if (n_pods == 0 || T.n_nodes == 0) return cudaSuccess;
   cudaError_t e = launch_pod_bucketing(T, pod_app, pod_slo, n_pods, sc, s);
   if (e != cudaSuccess) return e;
-  if (before_main && (e = cudaEventRecord(before_main, s)) != cudaSuccess) return e;
+  if (prof && (e = cudaEventRecord(prof[0], s)) != cudaSuccess) return e;
   if ((e = launch_stage_a(T, sc.counts, sc.stage, s)) != cudaSuccess) return e;
-  return launch_score_main(T, sc, score, sel, hi_arg, neg_lo, s);
+  if (prof && (e = cudaEventRecord(prof[1], s)) != cudaSuccess) return e;
+  if ((e = launch_score_any(T, sc, score, sel, hi_arg, neg_lo, s, lanes_nodes)) != cudaSuccess) return e;
+  if (prof && (e = cudaEventRecord(prof[2], s)) != cudaSuccess) return e;
+  return launch_expand_classes(T, sc.rep, n_pods, score, sel, hi_arg, neg_lo, s);
 }
 
 // ------------------------------------------------------------------ self test --------

@@ -115,13 +115,147 @@ cudaError_t launch_score_direct(const DevTables& T, const uint32_t* pod_app, con
   return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------ class dedupe -----
+
+// Scores depend on a pending pod only through (app, SLO) (gpu_plugins.go:626-651 candidate
+// configuration, :698-723 candidate term, :607-612 interference column) — pods of one Deployment
+// share both (deploy/busybox/busybox.yaml:26-28).  Pods with the same app and the same SLO BITS form
+// a class; only the lowest-index pod of a class is scored, the others receive copies of its rows.
+// Open addressing with linear probing; the table is at least twice the batch, so probes are short.
+constexpr unsigned long long kEmptyKey = ~0ull;
+
+__device__ __forceinline__ uint32_t hash_key(unsigned long long k) {
+  k ^= k >> 33;
+  k *= 0xFF51AFD7ED558CCDull;
+  k ^= k >> 33;
+  k *= 0xC4CEB9FE1A85EC53ull;
+  k ^= k >> 33;
+  return (uint32_t)k;
+}
+
+// pass 1: rep[p] = slot of the pod's class in the table; hvals[slot] = lowest pod index of the class
+__global__ void class_insert_kernel(const uint32_t* __restrict__ pod_app, const float* __restrict__ pod_slo, int n_pods,
+                                    unsigned long long* hkeys, uint32_t* hvals, uint32_t mask, uint32_t* rep) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_pods) return;
+  const unsigned long long key = ((unsigned long long)pod_app[p] << 32) | (unsigned long long)__float_as_uint(pod_slo[p]);
+  if (key == kEmptyKey) {  // the one key that collides with the empty marker stays its own class
+    rep[p] = kNoBucket;
+    return;
+  }
+  uint32_t h = hash_key(key) & mask;
+  for (;;) {
+    const unsigned long long prev = atomicCAS(&hkeys[h], kEmptyKey, key);
+    if (prev == kEmptyKey || prev == key) break;
+    h = (h + 1) & mask;
+  }
+  atomicMin(&hvals[h], (uint32_t)p);
+  rep[p] = h;
+}
+
+// pass 2: rep[p] = representative pod of p's class
+__global__ void class_lookup_kernel(int n_pods, const uint32_t* __restrict__ hvals, uint32_t* rep) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_pods) return;
+  const uint32_t slot = rep[p];
+  rep[p] = slot == kNoBucket ? (uint32_t)p : hvals[slot];
+}
+
+// Copy a representative's finished rows (raw score, selection byte) and extrema to every other pod
+// of its class: one warp per pod, widest vector the two rows' alignment allows.
+__device__ __forceinline__ void copy_row(uint8_t* __restrict__ dst, const uint8_t* __restrict__ src, int n, int lane) {
+  const uintptr_t a = (uintptr_t)dst, b = (uintptr_t)src;
+  const int rel = (int)((a ^ b) & 15);
+  if ((rel & 3) != 0) {
+    for (int i = lane; i < n; i += 32) dst[i] = src[i];
+    return;
+  }
+  const int w = rel == 0 ? 16 : (rel == 8 ? 8 : 4);  // bytes per vector both pointers can be aligned to together
+  int head = (int)((w - (a & (w - 1))) & (w - 1));
+  if (head > n) head = n;
+  for (int i = lane; i < head; i += 32) dst[i] = src[i];
+  const int nvec = (n - head) / w;
+  if (w == 16) {
+    const uint4* s4 = (const uint4*)(src + head);
+    uint4* d4 = (uint4*)(dst + head);
+    for (int i = lane; i < nvec; i += 32) d4[i] = s4[i];
+  } else if (w == 8) {
+    const uint2* s2 = (const uint2*)(src + head);
+    uint2* d2 = (uint2*)(dst + head);
+    for (int i = lane; i < nvec; i += 32) d2[i] = s2[i];
+  } else {
+    const uint32_t* s1 = (const uint32_t*)(src + head);
+    uint32_t* d1 = (uint32_t*)(dst + head);
+    for (int i = lane; i < nvec; i += 32) d1[i] = s1[i];
+  }
+  for (int i = head + nvec * w + lane; i < n; i += 32) dst[i] = src[i];
+}
+
+__global__ void __launch_bounds__(128) expand_classes_kernel(int n_pods, int n_nodes, const uint32_t* __restrict__ rep,
+                                                            uint8_t* score, uint8_t* sel, unsigned long long* hi_arg,
+                                                            unsigned long long* neg_lo) {
+  const int lane = threadIdx.x & 31;
+  const int p = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (p >= n_pods) return;
+  const uint32_t r = rep[p];
+  if (r == (uint32_t)p) return;
+  copy_row(score + (size_t)p * n_nodes, score + (size_t)r * n_nodes, n_nodes, lane);
+  copy_row(sel + (size_t)p * n_nodes, sel + (size_t)r * n_nodes, n_nodes, lane);
+  if (lane == 0) {
+    hi_arg[p] = hi_arg[r];
+    neg_lo[p] = neg_lo[r];
+  }
+}
+
+cudaError_t launch_expand_classes(const DevTables& T, const uint32_t* rep, int n_pods, uint8_t* score, uint8_t* sel,
+                                  unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s) {
+  if (!rep || n_pods == 0) return cudaSuccess;
+  note_launch();
+  expand_classes_kernel<<<(n_pods + 3) / 4, 128, 0, s>>>(n_pods, T.n_nodes, rep, score, sel, hi_arg, neg_lo);
+  return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------ pod bucketing ----
 
-__global__ void pod_hist_kernel(const uint32_t* __restrict__ pod_app, int n_pods, int n_apps, uint32_t* counts) {
+// the fields of a pod that the scoring kernels need, and its kind
+__device__ __forceinline__ PodRec make_pod_rec(const DevTables& T, uint32_t app, float slo, uint32_t p, int* kind) {
+  bool f6;
+  PodRec rec;
+  rec.slo = slo;
+  rec.inv_slo = __fdiv_rn(1.0f, slo);
+  rec.conf_v100 = conf_v100_for(T, app, slo, &f6);
+  // plain (finite SLO with a finite non-zero reciprocal), infinite reciprocal (SLO missing = 0, or
+  // denormal), or general
+  const bool inf_inv = fabsf(rec.inv_slo) > 3.4e38f;                            // +-Inf; false for NaN
+  const bool plain = fabsf(slo) <= 3.4e38f && rec.inv_slo != 0.0f && !inf_inv;  // false for NaN, +-Inf
+  rec.orig = p | (f6 ? kPodF6 : 0u) | (inf_inv ? kPodInfInv : (plain ? 0u : kPodGeneral));
+  *kind = inf_inv ? kKindInfInv : (!plain ? kKindGeneral : (rec.conf_v100 == -1.0f ? kKindNoV100 : kKindPlain));
+  return rec;
+}
+
+// bucket of every pod that is scored itself (class representatives, or all pods without dedupe)
+__global__ void pod_hist_kernel(DevTables T, const uint32_t* __restrict__ pod_app, const float* __restrict__ pod_slo,
+                                int n_pods, const uint32_t* __restrict__ rep, uint32_t* counts,
+                                uint32_t* __restrict__ bucket) {
   int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= n_pods) return;
-  uint32_t a = pod_app[p];
-  atomicAdd(&counts[a < (uint32_t)n_apps ? a : (uint32_t)n_apps], 1u);
+  if (rep && rep[p] != (uint32_t)p) {
+    bucket[p] = kNoBucket;
+    return;
+  }
+  int kind;
+  const uint32_t a = pod_app[p];
+  (void)make_pod_rec(T, a, pod_slo[p], (uint32_t)p, &kind);
+  const int b = bucket_of(a, T.n_apps, kind);
+  bucket[p] = (uint32_t)b;
+  atomicAdd(&counts[b], 1u);
+}
+
+// which apps occur in a batch at all (bucket kind 0 of each app): stage A's input when a batch is scored in slices
+__global__ void app_presence_kernel(const uint32_t* __restrict__ pod_app, int n_pods, int n_apps, uint32_t* counts) {
+  int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_pods) return;
+  atomicAdd(&counts[bucket_of(pod_app[p], n_apps, 0)], 1u);
 }
 
 // Single CTA: exclusive scan of the bucket sizes -> scatter cursors and chunk descriptors.
@@ -136,12 +270,17 @@ __global__ void __launch_bounds__(1024) pod_scan_kernel(int n_apps, const uint32
     s_carry_n = 0;
   }
   __syncthreads();
-  const int n_buckets = n_apps + 1;
+  const int n_buckets = (n_apps + 1) * kKinds;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int base = 0; base < n_buckets; base += 1024) {
     int b = base + threadIdx.x;
     uint32_t c = b < n_buckets ? counts[b] : 0u;
-    uint32_t n = (c + kChunk - 1) / kChunk;
+    // work items: the kKindPlain and kKindNoV100 pods of an app are neighbours in the sorted order and
+    // share work items (the first bucket emits them for both); the other kinds get their own
+    const int kind_b = b % kKinds;
+    const uint32_t c_items = kind_b == kKindPlain ? c + (b + 1 < n_buckets ? counts[b + 1] : 0u)
+                                                  : (kind_b == kKindNoV100 ? 0u : c);
+    uint32_t n = (c_items + kChunk - 1) / kChunk;
     uint32_t ic = c, in = n;  // inclusive warp scans
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -177,11 +316,18 @@ __global__ void __launch_bounds__(1024) pod_scan_kernel(int n_apps, const uint32
     uint32_t off_n = s_carry_n + s_warp_n[warp] + in - n;
     if (b < n_buckets) {
       cursor[b] = off_c;
-      uint32_t app = b < n_apps ? (uint32_t)b : kAppUnknown;
+      const int ai = b / kKinds;
+      uint32_t app = ai < n_apps ? (uint32_t)ai : kAppUnknown;
       for (uint32_t j = 0; j < n; ++j) {
         if (off_n + j < max_chunks) {
-          uint32_t len = c - j * kChunk;
-          chunks[off_n + j] = ChunkDesc{app, off_c + j * kChunk, len < (uint32_t)kChunk ? len : (uint32_t)kChunk, 0u};
+          uint32_t len = c_items - j * kChunk;
+          len = len < (uint32_t)kChunk ? len : (uint32_t)kChunk;
+          // kind field: bits 0..7 the kind; for kKindPlain items bits 8.. = how many of the item's pods are
+          // kKindPlain (they come first; the rest are kKindNoV100)
+          uint32_t n_plain = c > j * kChunk ? c - j * kChunk : 0u;
+          n_plain = n_plain < len ? n_plain : len;
+          chunks[off_n + j] = ChunkDesc{app, off_c + j * kChunk, len,
+                                        kind_b == kKindPlain ? ((uint32_t)kKindPlain | (n_plain << 8)) : (uint32_t)kind_b};
         }
       }
     }
@@ -196,48 +342,48 @@ __global__ void __launch_bounds__(1024) pod_scan_kernel(int n_apps, const uint32
 }
 
 __global__ void pod_scatter_kernel(DevTables T, const uint32_t* __restrict__ pod_app,
-                                   const float* __restrict__ pod_slo, int n_pods, uint32_t* cursor,
+                                   const float* __restrict__ pod_slo, int n_pods,
+                                   const uint32_t* __restrict__ bucket, uint32_t* cursor,
                                    PodRec* __restrict__ sorted) {
   int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= n_pods) return;
-  uint32_t a = pod_app[p];
-  float slo = pod_slo[p];
-  uint32_t pos = atomicAdd(&cursor[a < (uint32_t)T.n_apps ? a : (uint32_t)T.n_apps], 1u);
-  bool f6;
-  float c = conf_v100_for(T, a, slo, &f6);
-  PodRec rec;
-  rec.slo = slo;
-  rec.inv_slo = __fdiv_rn(1.0f, slo);
-  rec.conf_v100 = c;
-  // class of the pod for score_fast_kernel: plain (finite SLO with a finite non-zero
-  // reciprocal), infinite reciprocal (SLO missing = 0, or denormal), or general
-  const bool inf_inv = fabsf(rec.inv_slo) > 3.4e38f;                       // +-Inf; false for NaN
-  const bool plain = fabsf(slo) <= 3.4e38f && rec.inv_slo != 0.0f && !inf_inv;  // false for NaN, +-Inf
-  rec.orig = (uint32_t)p | (f6 ? kPodF6 : 0u) | (inf_inv ? kPodInfInv : (plain ? 0u : kPodGeneral));
-  sorted[pos] = rec;
+  const uint32_t b = bucket[p];
+  if (b == kNoBucket) return;
+  int kind;
+  const PodRec rec = make_pod_rec(T, pod_app[p], pod_slo[p], (uint32_t)p, &kind);
+  sorted[atomicAdd(&cursor[b], 1u)] = rec;
 }
 
-// pods per app bucket (counts must hold n_apps + 2 words; zeroed here)
+// apps present in a batch (counts must hold n_buckets + 1 words; zeroed here)
 cudaError_t launch_pod_histogram(const uint32_t* pod_app, int n_pods, int n_apps, uint32_t* counts, cudaStream_t s) {
-  cudaError_t e = cudaMemsetAsync(counts, 0, sizeof(uint32_t) * (size_t)(n_apps + 2), s);
+  cudaError_t e = cudaMemsetAsync(counts, 0, sizeof(uint32_t) * (size_t)(n_buckets_for(n_apps) + 1), s);
   if (e != cudaSuccess) return e;
   note_launch();
-  pod_hist_kernel<<<(n_pods + 255) / 256, 256, 0, s>>>(pod_app, n_pods, n_apps, counts);
+  app_presence_kernel<<<(n_pods + 255) / 256, 256, 0, s>>>(pod_app, n_pods, n_apps, counts);
   return cudaGetLastError();
 }
 
-// Bucket the pods by app: histogram -> scan (cursors + work items) -> scatter.
+// Class dedupe (if the scratch carries a table), then bucket the scored pods by (app, kind):
+// histogram -> scan (cursors + work items) -> scatter.
 cudaError_t launch_pod_bucketing(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
                                  const PodScratch& sc, cudaStream_t s) {
-  cudaError_t e = cudaMemsetAsync(sc.counts, 0, sizeof(uint32_t) * (size_t)(T.n_apps + 2), s);
+  cudaError_t e = cudaMemsetAsync(sc.counts, 0, sizeof(uint32_t) * (size_t)(n_buckets_for(T.n_apps) + 1), s);
   if (e != cudaSuccess) return e;
-  int pb = (n_pods + 255) / 256;
+  const int pb = (n_pods + 255) / 256;
+  if (sc.rep) {
+    if ((e = cudaMemsetAsync(sc.hkeys, 0xFF, sizeof(unsigned long long) * (size_t)sc.hash_size, s)) != cudaSuccess) return e;
+    if ((e = cudaMemsetAsync(sc.hvals, 0xFF, sizeof(uint32_t) * (size_t)sc.hash_size, s)) != cudaSuccess) return e;
+    note_launch();
+    class_insert_kernel<<<pb, 256, 0, s>>>(pod_app, pod_slo, n_pods, sc.hkeys, sc.hvals, sc.hash_size - 1, sc.rep);
+    note_launch();
+    class_lookup_kernel<<<pb, 256, 0, s>>>(n_pods, sc.hvals, sc.rep);
+  }
   note_launch();
-  pod_hist_kernel<<<pb, 256, 0, s>>>(pod_app, n_pods, T.n_apps, sc.counts);
+  pod_hist_kernel<<<pb, 256, 0, s>>>(T, pod_app, pod_slo, n_pods, sc.rep, sc.counts, sc.bucket);
   note_launch();
   pod_scan_kernel<<<1, 1024, 0, s>>>(T.n_apps, sc.counts, sc.cursor, sc.chunks, sc.n_chunks, sc.max_chunks);
   note_launch();
-  pod_scatter_kernel<<<pb, 256, 0, s>>>(T, pod_app, pod_slo, n_pods, sc.cursor, sc.sorted);
+  pod_scatter_kernel<<<pb, 256, 0, s>>>(T, pod_app, pod_slo, n_pods, sc.bucket, sc.cursor, sc.sorted);
   return cudaGetLastError();
 }
 

@@ -1,0 +1,421 @@
+// score_pods.cu — the lanes-are-pods Score kernel (sm_100a).
+//
+// Reference: pkg/plugins/gpu_plugin/gpu_plugins.go:562-757 (the per-GPU loop of Logic).
+//
+// Same restructuring and the same float32 filter as score_fast.cu (read its header first); what
+// changes is who owns what.  A CTA is ONE warp and takes one work item (up to kChunk pods of one
+// app) x one slice of kSlice = 32 consecutive nodes:
+//
+//   phase 1  lane = node.  Each lane folds its node's eight GPUs (sums from the stage-A table) into
+//            the float32 filter constants {A, B} per (GPU, branch), exactly as score_fast_kernel
+//            does, and leaves them in shared memory — once per (work item, node).
+//   phase 2  lane = (pod, node): the warp takes kPW = 8 pods x kNW = 4 nodes per pass, so that small
+//            app buckets (most buckets hold fewer than 32 pods) waste few lanes.  A node's
+//            constants are read as shared-memory broadcasts (four distinct records per load); the
+//            per-pod values — SLO, |1/SLO|, the V100 configuration — stay in registers.
+//
+// Why this is cheaper than one thread per node:
+//   * the evaluation loop runs over a LIST of the slice's nodes that need one — nodes without a
+//     model or UUIDs (score 0, :558) and, for pods that no V100 configuration satisfies (:667), all
+//     V100 nodes are answered from a per-slice template row instead;
+//   * per-pod extrema stay in registers over the slice (no REDUX per pod, one pair of atomics per
+//     (pod, slice)), and results go through an 8 x 32-byte staging tile and leave as full 32-byte
+//     sectors instead of byte stores;
+//   * two GPUs are evaluated per step with packed float32 instructions (FADD2/FMUL2/FFMA2), and the
+//     branch is resolved by evaluating tmp = A + B*v for both branches in one FFMA2 and selecting.
+//
+// Work items hold pods of kind kKindPlain followed by pods of kind kKindNoV100 (ChunkDesc::kind
+// carries the number of the former); pods without an SLO and pods with a non-finite SLO are
+// separate work items that the one-thread-per-node kernel serves (they are few: after class
+// dedupe at most one pod without an SLO per app).
+#include "score_fold.cuh"
+
+namespace gs {
+
+constexpr int kPW = 8;         // pods per pass
+constexpr int kNW = 32 / kPW;  // nodes per pass
+
+struct NodeHdr {
+  uint32_t nocand;  // score << 8 | selected GPU of the residents alone (:667-696)
+  uint32_t flags;   // bits 0..7 selection-byte flags of the node; kHdrV100; bits 16.. = GPUs of the node
+  float bound;      // |conf| (A30) + max_g |ci_g|: the node's part of the bound on |t|
+  uint32_t pad;
+};
+constexpr uint32_t kHdrV100 = 1u << 8;
+
+template <int GT>
+struct PodsSmem {
+  float4 abn[kSlice][GT / 2];  // per GPU pair {An[g], An[g+1], Bn[g], Bn[g+1]}
+  float4 abp[kSlice][GT / 2];  // the same for the positive branch
+  float st[kSlice][GT];        // A30: ci - conf (= -(conf - ci), :716);  V100: ci (the pod's conf is subtracted per lane)
+  NodeHdr hdr[kSlice];
+  double2 lut[kLutSize];
+  uint8_t list[2][kSlice];     // [kind] nodes of the slice to evaluate (streamlined domain)
+  uint8_t glist[2][kSlice];    // [kind] nodes to evaluate op for op (sums outside the domain)
+  uint8_t tmpl_score[2][kSlice], tmpl_sel[2][kSlice];  // [kind] results of the nodes that are not evaluated
+  uint8_t stage_score[kPW][kSlice], stage_sel[kPW][kSlice];
+  uint32_t n_list[2], n_glist[2], key_c[2], neg_c[2];  // extrema of the template nodes
+};
+
+// One (pod, node, GPU) step of the exact float64 sequence, for the lanes whose float32 estimate is
+// within kFilterDelta of an integer (same code as score_fast_kernel's exact path).
+template <int GT>
+__device__ __forceinline__ int exact_gpu(const StageA& stage, size_t st_row, int g, int k, float t, bool neg,
+                                         const double2* lut) {
+  const bool ld = g < k;
+  const double bn = ld ? stage.n0[st_row + g] : 0.0;
+  const double bp = ld ? stage.p0[st_row + g] : 0.0;
+  const uint32_t cn = ld ? stage.cnt[st_row + g] : 0u;
+  const int cn0 = (int)(cn & 0xFFFFu), cp0 = (int)(cn >> 16);
+  double w = fabs((double)t);
+  if (neg) w = __dadd_rn(w, 1.0);
+  if (neg) w = __dmul_rn(w, w);
+  const double v = rcp_ge1(__dadd_rn(1.0, w));
+  const double2 kc = branch_const(neg, bn, bp, cn0, cp0, lut);
+  const double2 rc = lut[min(neg ? cn0 + 1 : cp0 + 1, kLutSize - 1)];
+  const double S = __dadd_rn(neg ? bn : bp, v);
+  const double q = div_small_int(__dmul_rn(kc.x, S), rc.x, rc.y);
+  const int si = floor_nonneg(__dadd_rn(kc.y, __dmul_rn(100.0, q)));
+  return ld ? si : 0;  // a GPU the node does not have never wins
+}
+
+// Redo one pass GPU by GPU: float32 estimate first, the exact sequence wherever a lane's estimate
+// is near an integer.  Warp-collective.  Returns max over g of int64(tmp) * 8 + (GT - 1 - g).
+template <int GT>
+static __device__ __noinline__ int redo_pass(const PodsSmem<GT>* sm, const StageA stage, size_t st_row, int n, int k,
+                                             float s, float arinv, float negconf, bool has_cand) {
+  int best = 0;
+#pragma unroll 1
+  for (int g = 0; g < GT; ++g) {
+    const float nd = __fadd_rn(sm->st[n][g], negconf);
+    const float e = __fadd_rn(s, nd);
+    const float t = __fmul_rn(arinv, e);
+    const bool neg = e > 0.0f;
+    const float4 ab = neg ? sm->abn[n][g >> 1] : sm->abp[n][g >> 1];
+    const float A = (g & 1) ? ab.y : ab.x, B = (g & 1) ? ab.w : ab.z;
+    const float est = filter_est(A, B, filter_z(t, neg));
+    const float fl = filter_floor(est);
+    const float r = est - fl;
+    int si = (int)fl;
+    const bool near = has_cand && !(r >= kFilterDelta && r <= 1.0f - kFilterDelta);
+    if (__any_sync(0xFFFFFFFFu, near)) si = exact_gpu<GT>(stage, st_row, g, k, t, neg, sm->lut);
+    best = max(best, si * 8 + (GT - 1 - g));
+  }
+  return best;
+}
+
+template <int GT>
+__global__ void __launch_bounds__(32, 16) score_pods_kernel(DevTables T, StageA stage, const PodRec* __restrict__ pods,
+                                                             const ChunkDesc* __restrict__ chunks,
+                                                             const uint32_t* __restrict__ n_chunks,
+                                                             uint8_t* __restrict__ out_score,
+                                                             uint8_t* __restrict__ out_sel, unsigned long long* hi_arg,
+                                                             unsigned long long* neg_lo) {
+  __shared__ __align__(16) PodsSmem<GT> sm_storage;
+  PodsSmem<GT>* sm = &sm_storage;
+  if (blockIdx.x >= *n_chunks) return;
+  const ChunkDesc cd = chunks[blockIdx.x];
+  if ((cd.kind & 0xFFu) != (uint32_t)kKindPlain) return;  // pods without / with a non-finite SLO: the other kernel
+  const int lane = threadIdx.x;
+  const uint32_t n_plain = cd.kind >> 8;                  // the first n_plain pods are kKindPlain, the rest kKindNoV100
+  for (int i = lane; i < kLutSize; i += 32) sm->lut[i] = make_double2(i ? __ddiv_rn(1.0, (double)i) : 0.0, (double)i);
+
+  // ---------------------------------------------------------------- phase 1: lane = node
+  const int node0 = blockIdx.y * kSlice;
+  const int n_in = min(kSlice, T.n_nodes - node0);
+  const uint32_t app = cd.app;
+  const bool app_known = app < (uint32_t)T.n_apps;
+  {
+    const int node = node0 + lane;
+    const bool in_range = lane < n_in;
+    int model = kModelNone, k = 0;
+    if (in_range && T.redis_reachable) {
+      model = T.node_model[node];
+      k = T.node_ngpu[node];
+    }
+    const bool scored = model != kModelNone && k > 0;
+    unsigned node_flags = scored ? kFlagEligible : 0u;
+    float conf_a30 = 0.0f, ci_max = 0.0f;
+    bool general = false;
+    int nc_score = 0;
+    unsigned nc_sel = kSelNone;
+    float An[GT], Bn[GT], Ap[GT], Bp[GT], stv[GT];
+#pragma unroll
+    for (int g = 0; g < GT; ++g) {
+      // estimate 0.5: score 0, never near an integer (GPUs the node lacks)
+      An[g] = Ap[g] = 0.5f;
+      Bn[g] = Bp[g] = 0.f;
+      stv[g] = 0.f;
+    }
+    __syncwarp();  // lut
+    if (scored) {
+      if (model == kModelA30) {
+        float v;
+        const bool ok = conf_lookup(T, app, model, k, &v);
+        conf_a30 = ok ? v : 0.0f;  // missing key -> Go zero value, gpu_plugins.go:637
+        if (ok) node_flags |= kFlagF6;
+      }
+      const size_t st_row = (size_t)(app_known ? app : (uint32_t)T.n_apps) * stage.stride + (size_t)node * T.max_gpus;
+      double bn[GT], bp[GT];
+      float ci[GT];
+      uint32_t cnts[GT];
+      bool dom = true;
+#pragma unroll
+      for (int g = 0; g < GT; ++g) {
+        bn[g] = bp[g] = 0.0;
+        ci[g] = 0.f;
+        cnts[g] = 0u;
+        if (g < k) {
+          bn[g] = __ldcs(stage.n0 + st_row + g);
+          bp[g] = __ldcs(stage.p0 + st_row + g);
+          ci[g] = __ldcs(stage.ci + st_row + g);
+          cnts[g] = __ldcs(stage.cnt + st_row + g);
+          const GpuAcc acc = {bn[g], bp[g], (int)(cnts[g] & 0xFFFFu), (int)(cnts[g] >> 16)};
+          dom = dom && fold_in_domain(acc, ci[g]);
+        }
+      }
+      if (dom) {
+#pragma unroll
+        for (int g = 0; g < GT; ++g) {
+          if (g < k) {
+            const GpuAcc acc = {bn[g], bp[g], (int)(cnts[g] & 0xFFFFu), (int)(cnts[g] >> 16)};
+            const FoldOut o = fold_fast_fn(acc, sm->lut);
+            if (o.si > nc_score) {
+              nc_score = o.si;
+              nc_sel = (unsigned)g;
+            }
+            An[g] = o.An, Bn[g] = o.Bn, Ap[g] = o.Ap, Bp[g] = o.Bp;
+            ci_max = fmaxf(ci_max, fabsf(ci[g]));
+          }
+        }
+      } else {
+        general = true;  // candidates of this node go through logic_eval; only the residents-only score is needed
+#pragma unroll 1
+        for (int g = 0; g < k; ++g) {
+          const uint32_t cn = stage.cnt[st_row + g];
+          const GpuAcc acc = {stage.n0[st_row + g], stage.p0[st_row + g], (int)(cn & 0xFFFFu), (int)(cn >> 16)};
+          const FoldOut o = fold_general_fn(acc, sm->lut);
+          if (o.si > nc_score) {
+            nc_score = o.si;
+            nc_sel = (unsigned)g;
+          }
+        }
+      }
+      const float negconf = model == kModelA30 ? -conf_a30 : -0.0f;
+#pragma unroll
+      for (int g = 0; g < GT; ++g) stv[g] = __fadd_rn(ci[g], negconf);  // x + (-0) = x: V100 rows keep ci
+    }
+#pragma unroll
+    for (int gp = 0; gp < GT / 2; ++gp) {
+      sm->abn[lane][gp] = make_float4(An[2 * gp], An[2 * gp + 1], Bn[2 * gp], Bn[2 * gp + 1]);
+      sm->abp[lane][gp] = make_float4(Ap[2 * gp], Ap[2 * gp + 1], Bp[2 * gp], Bp[2 * gp + 1]);
+    }
+#pragma unroll
+    for (int g = 0; g < GT; ++g) sm->st[lane][g] = stv[g];
+    NodeHdr h;
+    h.nocand = ((uint32_t)nc_score << 8) | nc_sel;
+    h.flags = node_flags | (model == kModelV100 ? kHdrV100 : 0u) | ((uint32_t)k << 16);
+    h.bound = (model == kModelA30 ? fabsf(conf_a30) : 0.0f) + ci_max;
+    h.pad = 0u;
+    sm->hdr[lane] = h;
+    // evaluation lists and template rows per kind (0: a V100 configuration exists, 1: none does)
+    // F6 on V100 nodes = some 1P/2P/4P_V100 column exists for this app (gpu_plugins.go:639-651)
+    bool f6_app = false;
+    {
+      float tmp;
+      for (int i = 0; i < 3; ++i) f6_app |= conf_lookup(T, app, kModelV100, 1 << i, &tmp);
+    }
+    const bool is_v = model == kModelV100;
+#pragma unroll
+    for (int kind = 0; kind < 2; ++kind) {
+      const bool cand = scored && !(kind == 1 && is_v);  // a candidate term enters this node's score
+      const unsigned m_fast = __ballot_sync(0xFFFFFFFFu, cand && !general);
+      const unsigned m_gen = __ballot_sync(0xFFFFFFFFu, cand && general);
+      const unsigned lt = (1u << lane) - 1u;
+      if (cand && !general) sm->list[kind][__popc(m_fast & lt)] = (uint8_t)lane;
+      if (cand && general) sm->glist[kind][__popc(m_gen & lt)] = (uint8_t)lane;
+      const bool tmpl = in_range && !cand;
+      sm->tmpl_score[kind][lane] = (uint8_t)nc_score;
+      sm->tmpl_sel[kind][lane] = (uint8_t)(nc_sel | node_flags | ((is_v && scored && f6_app) ? kFlagF6 : 0u));
+      uint32_t key = tmpl ? lane_key(nc_score, (uint32_t)node) : 0u;
+      uint32_t ng = tmpl ? (uint32_t)(100 - nc_score) : 0u;
+      key = __reduce_max_sync(0xFFFFFFFFu, key);
+      ng = __reduce_max_sync(0xFFFFFFFFu, ng);
+      if (lane == 0) {
+        sm->n_list[kind] = __popc(m_fast);
+        sm->n_glist[kind] = __popc(m_gen);
+        sm->key_c[kind] = key;
+        sm->neg_c[kind] = ng;
+      }
+    }
+  }
+  // the slice's largest node bound: lets whole passes skip the per-lane overflow check
+  float slice_bound = sm->hdr[lane].bound;  // own write, visible without a barrier
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) slice_bound = fmaxf(slice_bound, __shfl_xor_sync(0xFFFFFFFFu, slice_bound, d));
+  if (!(slice_bound <= 3.0e38f)) slice_bound = __int_as_float(0x7F800000);  // NaN anywhere -> +Inf: always check
+  __syncwarp();
+
+  // ---------------------------------------------------------------- phase 2: lane = (pod, node)
+  const int pi = lane & (kPW - 1), q = lane >> 3;
+  const size_t N = (size_t)T.n_nodes;
+  const bool vec8 = (N % 8 == 0) && ((((uintptr_t)out_score) | ((uintptr_t)out_sel)) % 8 == 0);
+  const float2 one2 = make_float2(1.0f, 1.0f), mone2 = make_float2(-1.0f, -1.0f);
+  const float2 magic2 = make_float2(8388608.0f, 8388608.0f), nmagic2 = make_float2(-8388608.0f, -8388608.0f);
+  const float2 eight2 = make_float2(8.0f, 8.0f);
+  // a pass never mixes kinds: the plain pods are padded to a multiple of kPW
+  const uint32_t plain_padded = (n_plain + kPW - 1) / kPW * kPW;
+  const uint32_t p_end = plain_padded + (cd.len - n_plain);
+#pragma unroll 1
+  for (uint32_t p0 = 0; p0 < p_end; p0 += kPW) {
+    uint32_t base = p0;
+    int kind = 0;
+    uint32_t seg_end = n_plain;
+    if (p0 >= plain_padded) {
+      kind = 1;
+      base = n_plain + (p0 - plain_padded);
+      seg_end = cd.len;
+    }
+    const bool valid = base + pi < seg_end;
+    const PodRec pr = pods[cd.start + (valid ? base + pi : base)];
+    const uint32_t orig = pr.orig & kPodIndexMask;
+    const float s = pr.slo, arinv = fabsf(pr.inv_slo);
+    const float ncv = kind == 0 ? -pr.conf_v100 : -0.0f;  // kind 1 never evaluates a V100 node
+    // may any lane's float32 term leave the finite range on some node of the slice?
+    const bool slow = __any_sync(0xFFFFFFFFu, !(arinv * (fabsf(s) + fabsf(pr.conf_v100) + slice_bound) < 1.0e38f));
+    // template rows into the staging tile: lane -> pod row lane >> 2, 8 nodes each
+    {
+      const int row = lane >> 2, c8 = (lane & 3) * 8;
+      *reinterpret_cast<uint2*>(&sm->stage_score[row][c8]) = *reinterpret_cast<const uint2*>(&sm->tmpl_score[kind][c8]);
+      *reinterpret_cast<uint2*>(&sm->stage_sel[row][c8]) = *reinterpret_cast<const uint2*>(&sm->tmpl_sel[kind][c8]);
+    }
+    __syncwarp();
+    uint32_t hi = 0u, ng = 0u;
+    const int nL = (int)sm->n_list[kind];
+#pragma unroll 1
+    for (int it = 0; it < nL; it += kNW) {
+      const bool active = it + q < nL;
+      const int n = sm->list[kind][active ? it + q : it];
+      const NodeHdr h = sm->hdr[n];
+      const bool is_v = (h.flags & kHdrV100) != 0u;
+      const bool has_cand = active && valid;
+      const float negconf = is_v ? ncv : -0.0f;
+      const float2 negconf2 = make_float2(negconf, negconf), s2 = make_float2(s, s), ar2 = make_float2(arinv, arinv);
+      int best;
+      bool lane_general = false;
+      if (slow) lane_general = has_cand && !(arinv * (fabsf(s) + (is_v ? fabsf(pr.conf_v100) : 0.0f) + h.bound) < 1.0e38f);
+      if (slow && __any_sync(0xFFFFFFFFu, lane_general)) {
+        // rare: some lane's term may overflow — every candidate lane of this pass goes op for op
+        best = 0;
+        if (has_cand) {
+          unsigned selbyte;
+          const int sc = logic_eval(T, app, s, -1, node0 + n, &selbyte);
+          const unsigned g = selbyte & 31u;
+          best = sc > 0 ? sc * 8 + (GT - 1 - (int)g) : 0;
+        }
+      } else {
+        float fbest = 0.f, rlo = 0.5f, rhi = 0.5f;
+#pragma unroll
+        for (int gp = 0; gp < GT / 2; ++gp) {
+          const float2 st2 = *reinterpret_cast<const float2*>(&sm->st[n][2 * gp]);
+          const float4 abn = sm->abn[n][gp], abp = sm->abp[n][gp];
+          const float2 e2 = __fadd2_rn(s2, __fadd2_rn(st2, negconf2));  // slo - (conf - interf), :716
+          const float2 t2 = __fmul2_rn(ar2, e2);                        // |1/slo| * (slo - d): |t| with the sign of e
+          const float a0 = 1.0f + fabsf(t2.x), a1 = 1.0f + fabsf(t2.y);
+          const float2 zn2 = __ffma2_rn(make_float2(a0, a1), make_float2(a0, a1), one2);
+          const bool neg0 = e2.x > 0.0f, neg1 = e2.y > 0.0f;           // SLO > conf - interf
+          float v0, v1;
+          asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(v0) : "f"(neg0 ? zn2.x : a0));
+          asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(v1) : "f"(neg1 ? zn2.y : a1));
+          const float2 v2 = make_float2(v0, v1);
+          const float2 estn = __ffma2_rn(make_float2(abn.z, abn.w), v2, make_float2(abn.x, abn.y));
+          const float2 estp = __ffma2_rn(make_float2(abp.z, abp.w), v2, make_float2(abp.x, abp.y));
+          const float2 est = make_float2(neg0 ? estn.x : estp.x, neg1 ? estn.y : estp.y);
+          const float2 fl = __fadd2_rn(__fadd2_rz(est, magic2), nmagic2);  // floor for 0 <= est < 2^22, exact
+          const float2 r = __ffma2_rn(fl, mone2, est);                     // est - floor(est), exact
+          const float2 key = __ffma2_rn(fl, eight2, make_float2((float)(GT - 1 - 2 * gp), (float)(GT - 2 - 2 * gp)));
+          rlo = fminf(fminf(rlo, r.x), r.y);
+          rhi = fmaxf(fmaxf(rhi, r.x), r.y);
+          fbest = fmaxf(fmaxf(fbest, key.x), key.y);
+        }
+        best = (int)fbest;
+        const bool unsure = has_cand && !(rlo >= kFilterDelta && rhi <= 1.0f - kFilterDelta);
+        if (__any_sync(0xFFFFFFFFu, unsure)) {
+          const size_t st_row = (size_t)(app_known ? app : (uint32_t)T.n_apps) * stage.stride +
+                                (size_t)(node0 + n) * T.max_gpus;
+          best = redo_pass<GT>(sm, stage, st_row, n, (int)(h.flags >> 16), s, arinv, negconf, has_cand);
+        }
+      }
+      const int score = best >> 3;
+      const unsigned sel = score > 0 ? (unsigned)(GT - 1 - (best & 7)) : kSelNone;
+      if (has_cand) {
+        sm->stage_score[pi][n] = (uint8_t)score;
+        sm->stage_sel[pi][n] = (uint8_t)(sel | (h.flags & 0xFFu) | (is_v ? kFlagF6 : 0u) | kFlagF7);
+        hi = max(hi, lane_key(score, (uint32_t)(node0 + n)));
+        ng = max(ng, (uint32_t)(100 - score));
+      }
+    }
+    // nodes whose sums fall outside the streamlined domain: op for op
+    const int nG = (int)sm->n_glist[kind];
+#pragma unroll 1
+    for (int it = 0; it < nG; it += kNW) {
+      if (it + q < nG && valid) {
+        const int n = sm->glist[kind][it + q];
+        unsigned selbyte;
+        const int sc = logic_eval(T, app, s, -1, node0 + n, &selbyte);
+        sm->stage_score[pi][n] = (uint8_t)sc;
+        sm->stage_sel[pi][n] = (uint8_t)selbyte;
+        hi = max(hi, lane_key(sc, (uint32_t)(node0 + n)));
+        ng = max(ng, (uint32_t)(100 - sc));
+      }
+    }
+    // per-pod extrema: the four node lanes of a pod, plus the template nodes
+    hi = max(hi, __shfl_xor_sync(0xFFFFFFFFu, hi, 8));
+    ng = max(ng, __shfl_xor_sync(0xFFFFFFFFu, ng, 8));
+    hi = max(hi, __shfl_xor_sync(0xFFFFFFFFu, hi, 16));
+    ng = max(ng, __shfl_xor_sync(0xFFFFFFFFu, ng, 16));
+    hi = max(hi, sm->key_c[kind]);
+    ng = max(ng, sm->neg_c[kind]);
+    if (q == 0 && valid) publish_extrema(hi, ng, T.node_base, orig, hi_arg, neg_lo);
+    __syncwarp();
+    // write the tile out: lane -> pod row lane >> 2, nodes [8 * (lane & 3), +8)
+    {
+      const int row = lane >> 2, c8 = (lane & 3) * 8;
+      const uint32_t orow = __shfl_sync(0xFFFFFFFFu, orig, row);       // lanes 0..7 hold the eight pods
+      const bool rvalid = __shfl_sync(0xFFFFFFFFu, (int)valid, row) != 0;
+      if (rvalid && c8 < n_in) {
+        const size_t o = (size_t)orow * N + (size_t)(node0 + c8);
+        if (vec8) {
+          *reinterpret_cast<uint2*>(out_score + o) = *reinterpret_cast<const uint2*>(&sm->stage_score[row][c8]);
+          *reinterpret_cast<uint2*>(out_sel + o) = *reinterpret_cast<const uint2*>(&sm->stage_sel[row][c8]);
+        } else {
+          const int m = min(8, n_in - c8);
+          for (int j = 0; j < m; ++j) {
+            out_score[o + j] = sm->stage_score[row][c8 + j];
+            out_sel[o + j] = sm->stage_sel[row][c8 + j];
+          }
+        }
+      }
+    }
+    __syncwarp();
+  }
+}
+
+// the lanes-are-pods kernel over the work items of kind kKindPlain, then the one-thread-per-node
+// kernel for the rest (it skips the work items this one has served)
+cudaError_t launch_score_pods(const DevTables& T, const PodScratch& sc, uint8_t* score, uint8_t* sel,
+                              unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s) {
+  dim3 grid(sc.max_chunks, (unsigned)((T.n_nodes + kSlice - 1) / kSlice));
+  note_launch();
+  if (T.max_gpus <= 2)
+    score_pods_kernel<2><<<grid, 32, 0, s>>>(T, sc.stage, sc.sorted, sc.chunks, sc.n_chunks, score, sel, hi_arg, neg_lo);
+  else if (T.max_gpus <= 4)
+    score_pods_kernel<4><<<grid, 32, 0, s>>>(T, sc.stage, sc.sorted, sc.chunks, sc.n_chunks, score, sel, hi_arg, neg_lo);
+  else
+    score_pods_kernel<8><<<grid, 32, 0, s>>>(T, sc.stage, sc.sorted, sc.chunks, sc.n_chunks, score, sel, hi_arg, neg_lo);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  return launch_score_main(T, sc, score, sel, hi_arg, neg_lo, s, /*skip_plain=*/true);
+}
+
+}  // namespace gs

@@ -48,12 +48,25 @@ constexpr int kMaxPods = 1 << 29;
 constexpr int kMaxNodesPerCtx = 65535 * 128;
 constexpr int kMaxResidentsPerSlot = 65535;
 
-// A work item of the restructured kernel: up to kChunk pods of one app.
+// Pending pods are bucketed by (app, kind); a work item never mixes kinds, so every warp of the
+// scoring kernels runs one code path.
+constexpr int kKindPlain = 0;    // finite SLO with a finite non-zero reciprocal; some V100 configuration exceeds it
+constexpr int kKindNoV100 = 1;   // the same, but no 1P/2P/4P_V100 prediction exceeds the SLO: no candidate term on V100 nodes (:667)
+constexpr int kKindInfInv = 2;   // 1/SLO is infinite (SLO missing = 0, or denormal)
+constexpr int kKindGeneral = 3;  // SLO is NaN or infinite, or its reciprocal is 0: op-for-op path
+constexpr int kKinds = 4;
+// bucket of a pod: app-major, so that the work items of one app are neighbours (n_apps = unknown app)
+__host__ __device__ inline int bucket_of(uint32_t app, int n_apps, int kind) {
+  return (int)(app < (uint32_t)n_apps ? app : (uint32_t)n_apps) * kKinds + kind;
+}
+inline int n_buckets_for(int n_apps) { return (n_apps + 1) * kKinds; }
+
+// A work item of the restructured kernels: up to kChunk pods of one (app, kind) bucket.
 struct ChunkDesc {
   uint32_t app;
   uint32_t start;
   uint32_t len;
-  uint32_t pad;
+  uint32_t kind;
 };
 
 #ifndef GS_KCHUNK
@@ -66,6 +79,7 @@ constexpr int kChunk = GS_KCHUNK; // pods per work item (one app); staged kStage
 constexpr int kStage = 128;      // pods staged in shared memory at once (= kTile)
 constexpr int kFastMaxGpus = 8;  // GPUs per node the register-resident kernel covers
 constexpr int kTile = 128;       // nodes per CTA
+constexpr int kSlice = 32;       // nodes per CTA of the lanes-are-pods kernel (one warp)
 
 // Per-batch table of the residents' sums for every (app bucket, GPU slot), written by
 // stage_a_kernel and read back coalesced by score_fast_kernel: [n_apps + 1][slots].
@@ -79,20 +93,33 @@ struct StageA {
 
 // Scratch of the restructured path (owned by the context).
 struct PodScratch {
-  uint32_t* counts;   // [A+2] pods per app bucket (bucket A = unknown app)
-  uint32_t* cursor;   // [A+2] scatter cursors
+  uint32_t* counts;   // [(A+1)*kKinds + 1] pods per (app, kind) bucket (app A = unknown app)
+  uint32_t* cursor;   // [(A+1)*kKinds + 1] scatter cursors
   uint32_t* n_chunks; // [1]
   ChunkDesc* chunks;  // [max_chunks]
   PodRec* sorted;     // [P]
+  uint32_t* bucket;   // [P] bucket of each pod, kNoBucket for pods that are not scored themselves (duplicates)
   uint32_t max_chunks;
   StageA stage;       // n0 == nullptr: score_fast_kernel walks the resident lists itself
+  // class dedupe: pods with equal (app, SLO bits) get equal rows, so only one representative per class
+  // (the lowest pod index) is scored and its rows are copied to the others.  rep == nullptr: off.
+  uint32_t* rep;              // [P] representative of each pod's class
+  unsigned long long* hkeys;  // [hash_size] open-addressing table: app << 32 | SLO bits
+  uint32_t* hvals;            // [hash_size] lowest pod index of the class
+  uint32_t hash_size;         // power of two >= 2 * P
 };
+constexpr uint32_t kNoBucket = 0xFFFFFFFFu;
 
-// upper bound on the work items a batch can produce: one per started kChunk per app bucket, and
+// upper bound on the work items a batch can produce: one per started kChunk per bucket, and
 // never more than there are pods
 inline uint32_t max_chunks_for(int n_pods, int n_apps) {
-  const uint32_t by_buckets = (uint32_t)(n_pods / kChunk + n_apps + 2);
+  const uint32_t by_buckets = (uint32_t)(n_pods / kChunk + n_buckets_for(n_apps) + 1);
   return by_buckets < (uint32_t)n_pods ? by_buckets : (uint32_t)(n_pods > 0 ? n_pods : 1);
+}
+inline uint32_t hash_size_for(int n_pods) {
+  uint32_t h = 64;
+  while (h < 2u * (uint32_t)(n_pods > 0 ? n_pods : 1)) h <<= 1;
+  return h;
 }
 constexpr int kStageTableMinPods = 256;  // smaller batches walk the resident lists in the scoring kernel
 
@@ -107,10 +134,19 @@ cudaError_t launch_score_direct(const DevTables& T, const uint32_t* pod_app, con
                                 unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s);
 cudaError_t launch_pod_bucketing(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
                                  const PodScratch& scratch, cudaStream_t s);
+// bucketing -> stage A -> scoring kernel -> class expansion.  lanes_nodes: use the one-thread-per-node
+// kernel (score_fast_kernel) even where the lanes-are-pods kernel (score_pods_kernel) could run.
+// prof: nullptr, or three events recorded before stage A, after it, and after the scoring kernel.
 cudaError_t launch_score_fast(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
                               const PodScratch& scratch, uint8_t* score, uint8_t* sel,
                               unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s,
-                              cudaEvent_t before_main = nullptr);
+                              const cudaEvent_t* prof = nullptr, bool lanes_nodes = false);
+cudaError_t launch_score_any(const DevTables& T, const PodScratch& sc, uint8_t* score, uint8_t* sel,
+                             unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s, bool lanes_nodes);
+cudaError_t launch_score_pods(const DevTables& T, const PodScratch& sc, uint8_t* score, uint8_t* sel,
+                              unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s);
+cudaError_t launch_expand_classes(const DevTables& T, const uint32_t* rep, int n_pods, uint8_t* score, uint8_t* sel,
+                                  unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s);
 cudaError_t launch_transpose_interf(const float* interf, float* interf_t, int n_apps, cudaStream_t s);
 cudaError_t launch_selftest(unsigned long long seed, int blocks, int iters, unsigned long long* d_mismatches,
                             cudaStream_t s);
@@ -120,7 +156,8 @@ double filter_delta();
 cudaError_t launch_pod_histogram(const uint32_t* pod_app, int n_pods, int n_apps, uint32_t* counts, cudaStream_t s);
 cudaError_t launch_stage_a(const DevTables& T, const uint32_t* counts, const StageA& stage, cudaStream_t s);
 cudaError_t launch_score_main(const DevTables& T, const PodScratch& sc, uint8_t* score, uint8_t* sel,
-                              unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s);
+                              unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s,
+                              bool skip_plain = false);
 cudaError_t launch_normalize(int n_pods, int n_nodes, int rescale, uint8_t* score,
                              const unsigned long long* hi_arg, const unsigned long long* neg_lo,
                              int32_t* best, cudaStream_t s);

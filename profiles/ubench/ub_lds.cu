@@ -8,7 +8,7 @@
 //      3 LDS.128 per-lane distinct        4 LDS.64 per-lane distinct                   5 LDS.32 one address
 //      6 LDS.64 two addresses inside one 16 B record (lane parity)                    7 LDS.32 4 addresses 160 B apart
 //      8 LDS.128 2 addresses (lane/16) 160 B apart
-template <int PAT>
+template <int PAT, bool USE = true>
 __global__ void lds_k(float* out) {
   __shared__ __align__(16) float sm[8192];
   for (int i = threadIdx.x; i < 8192; i += blockDim.x) sm[i] = (float)i * 1e-3f;
@@ -33,15 +33,15 @@ __global__ void lds_k(float* out) {
       if (PAT == 0 || PAT == 1 || PAT == 2 || PAT == 3 || PAT == 8) {
         float x, y, z, w;
         asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(x), "=f"(y), "=f"(z), "=f"(w) : "r"(addr));
-        acc0 += x; acc1 += y; acc2 += z; acc3 += w;
+        if (USE) { acc0 += x; acc1 += y; acc2 += z; acc3 += w; }
       } else if (PAT == 4 || PAT == 6) {
         float x, y;
         asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(x), "=f"(y) : "r"(addr));
-        acc0 += x; acc1 += y;
+        if (USE) { acc0 += x; acc1 += y; }
       } else {
         float x;
         asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(addr));
-        acc0 += x;
+        if (USE) acc0 += x;
       }
     }
     a = base + ((a - base + 5120u) & 16383u) ;
@@ -130,6 +130,16 @@ int main() {
   L(6, "LDS.64 2 addresses in one 16 B record");
   L(5, "LDS.32 one address (broadcast)");
   L(7, "LDS.32 4 addresses, 160 B apart");
+  // the loads alone (results unused, 32 warps per SM): the shared-memory pipe's own rate
+  threads = 256;
+#define LN(P, NAME) timeit(NAME, [&] { lds_k<P, false><<<blocks, threads>>>(out); }, (double)ITERS * 8, blocks, threads)
+  LN(0, "[loads only] LDS.128 one address");
+  LN(2, "[loads only] LDS.128 4 addresses, 160 B apart");
+  LN(3, "[loads only] LDS.128 32 addresses");
+  LN(4, "[loads only] LDS.64 32 addresses");
+  LN(6, "[loads only] LDS.64 2 addresses in 16 B");
+  LN(5, "[loads only] LDS.32 one address");
+  LN(7, "[loads only] LDS.32 4 addresses");
   threads = 512;
 #define A(O, NAME, N) timeit(NAME, [&] { alu_k<O><<<blocks, threads>>>(out, 1.0f); }, (double)ITERS * N, blocks, threads)
   A(0, "FFMA", 8);

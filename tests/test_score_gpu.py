@@ -9,17 +9,23 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-def _check(sched, oracle_mod, preds, cluster, pods, node_base=0):
+# every way the library can produce the bytes: the lanes-are-pods kernel (default where the batch is
+# large enough for the residents-sum table), the one-thread-per-node kernel, without class dedupe,
+# and the op-for-op kernel
+VARIANTS = (dict(), dict(flags=8), dict(flags=4), dict(flags=4 | 8), dict(direct=True))
+
+
+def _check(sched, oracle_mod, preds, cluster, pods, node_base=0, variants=VARIANTS):
     sched.upload_predictions(preds)
     sched.upload_cluster(cluster, node_base=node_base)
     ora = oracle_mod.Oracle(preds, cluster)
     for normalize in (False, True):
         want = ora.score_batch(pods, normalize=normalize, node_base=node_base)
-        for direct in (False, True):
-            got = sched.score_batch(pods, normalize=normalize, direct=direct)
+        for kw in variants:
+            got = sched.score_batch(pods, normalize=normalize, **kw)
             for w, g, name in zip(want, got, ("score", "sel", "best")):
                 bad = np.argwhere(w != g)
-                assert bad.size == 0, (f"{name} differs at {bad[:5].tolist()} (normalize={normalize}, direct={direct}): "
+                assert bad.size == 0, (f"{name} differs at {bad[:5].tolist()} (normalize={normalize}, {kw}): "
                                        f"want {w[tuple(bad[0])]}, got {g[tuple(bad[0])]}")
 
 
@@ -45,6 +51,41 @@ def test_ragged_gpus_and_unknown_apps(sched, oracle_mod, synth):
 def test_odd_shapes(sched, oracle_mod, synth, n_pods, n_nodes, gpn):
     preds, cluster, pods = synth.make_workload(n_pods, n_nodes, gpus_per_node=gpn, n_apps=33, seed=1234 + n_pods)
     _check(sched, oracle_mod, preds, cluster, pods, node_base=1000)
+
+
+@pytest.mark.parametrize("n_pods,n_nodes,gpn,n_apps", [(300, 33, 8, 7), (777, 250, 8, 40), (1024, 97, 4, 20),
+                                                       (513, 64, 2, 5), (2000, 1001, 8, 300), (260, 31, 8, 1)])
+def test_lanes_are_pods_kernel_shapes(sched, oracle_mod, synth, n_pods, n_nodes, gpn, n_apps):
+    """Batches large enough for the residents-sum table (>= 256 pods) take the lanes-are-pods kernel:
+    node counts that are no multiple of 8 or 32 (byte-wise row stores, short last slice), 2/4/8 GPU
+    slots, ragged GPU counts, unknown apps, tiny and huge app buckets."""
+    preds, cluster, pods = synth.make_workload(n_pods, n_nodes, gpus_per_node=gpn, n_apps=n_apps, seed=77 + n_pods,
+                                               ragged_gpus=True, p_unknown_app=0.03)
+    if gpn < 8:
+        preds.col_of[:, gpn] = preds.col_of[:, 8]       # give the tables a column for this GPU count
+        preds.col_of[:, 1] = preds.col_of[:, 8]
+    _check(sched, oracle_mod, preds, cluster, pods, node_base=5)
+
+
+def test_class_dedupe(sched, oracle_mod, synth):
+    """Pods with equal (app, SLO bits) are scored once and copied: many duplicates, duplicates of the
+    special values (0, -0, NaN, Inf, denormal, negative), the unknown app, and the one key that
+    collides with the hash table's empty marker (unknown app + all-ones NaN)."""
+    preds, cluster, _ = synth.make_workload(10, 180, gpus_per_node=8, n_apps=12)
+    rng = np.random.default_rng(9)
+    P = 3000
+    slo_values = np.array([10.0, 35.5, 120.25, 300.0, 599.0, 0.0, -0.0, np.nan, np.inf, 1e-40, -77.0, 0.01],
+                          dtype=np.float32)
+    app = rng.integers(0, 14, size=P).astype(np.uint32)
+    app[app >= 12] = synth.APP_UNKNOWN
+    slo = slo_values[rng.integers(0, slo_values.size, size=P)].copy()
+    bits = slo.view(np.uint32)
+    bits[::97] = 0xFFFFFFFF                               # a NaN whose bits are all ones
+    pods = synth.Pods(app=app, slo=bits.view(np.float32))
+    assert synth.distinct_classes(pods) < 200
+    _check(sched, oracle_mod, preds, cluster, pods)
+    uniq = synth.Pods(app=app, slo=rng.uniform(10, 600, size=P).astype(np.float32))   # no duplicates at all
+    _check(sched, oracle_mod, preds, cluster, uniq, variants=(dict(), dict(flags=4)))
 
 
 def test_more_than_8_gpus_per_node_uses_direct_kernel(sched, oracle_mod, synth):
