@@ -176,6 +176,26 @@ GS_API int gs_score_batch(gs_ctx* ctx, const uint32_t* pod_app, const float* pod
                    const int32_t* pod_self, int32_t n_pods, uint32_t flags,
                    uint8_t* out_score, uint8_t* out_sel, int32_t* out_best);
 
+/* Decisions only: what the framework and PostBind need of a cycle, 8 bytes per pod instead of two
+ * n_nodes-byte rows.  For every pod: the node the framework's selectHost picks when this is the only
+ * score plugin (highest score, lowest index on ties; -1 without nodes), the selection byte AT that
+ * node — the {nodeName: selectedUUID} record Logic leaves in the pod's ConfigMap
+ * (gpu_plugins.go:759-768) and PostBind reads back (:894-895) —, the raw score extrema over the
+ * nodes (NormalizeScore's highest/lowest, :818-827: the chosen node's normalised score is 100 if
+ * raw_hi > raw_lo, else 0), and the V100 configuration Logic records under MPS_<node> (:640-665):
+ * 0 = the chosen node is not a V100 node with UUIDs, else 1, 2 or 4 for "1P_V100" / "2P_V100" /
+ * "4P_V100" (PostBind derives CUDA_MPS_PINNED_DEVICE_MEM_LIMIT / ..._ACTIVE_THREAD_PERCENTAGE from
+ * it, :896-903).  Same arguments as gs_score_batch otherwise. */
+typedef struct gs_decision {
+  int32_t node;
+  uint8_t sel;    /* GS_SEL_* of the chosen node */
+  uint8_t raw_hi; /* highest raw score over the nodes */
+  uint8_t raw_lo; /* lowest raw score over the nodes */
+  uint8_t mps;    /* 0, 1, 2 or 4 */
+} gs_decision;
+GS_API int gs_score_decisions(gs_ctx* ctx, const uint32_t* pod_app, const float* pod_slo,
+                              const int32_t* pod_self, int32_t n_pods, uint32_t flags, gs_decision* out);
+
 /* Same computation on DEVICE pointers (all arguments are device memory on the context's
  * device), asynchronous on `stream` (a cudaStream_t passed as void*; NULL = the
  * context's own stream).  Split in two phases so that a node-sharded multi-GPU caller

@@ -84,6 +84,15 @@ GS_API int gsp_plugin_prescore(gsp_plugin* p, const char* pod_name, const char* 
  * node, :798-801; GetSLOs failure, :544-548). */
 GS_API int gsp_plugin_score(gsp_plugin* p, const char* node_name, int64_t* out_score, char* out_uuid,
                             int uuid_cap);
+/* PostBind's data path (gpu_plugins.go:843-926) for the last PreScore'd pod bound to nodeName: the
+ * three values the reference appends to the pod's ConfigMap — CUDA_VISIBLE_DEVICES = the UUID Logic
+ * selected on that node (its {nodeName: selectedUUID} record, :759-768, :894-895), and the MPS limits
+ * derived from the V100 configuration Logic recorded as MPS_<nodeName> (:640-665, :896-903).
+ * Returns 1 when the reference would write them (UUID not empty, :907), 0 when it would not, a
+ * negative value on error (unknown node, no PreScore, Redis not found :852).  The ConfigMap write
+ * itself stays with the caller. */
+GS_API int gsp_plugin_postbind(gsp_plugin* p, const char* node_name, char* out_uuid, int uuid_cap,
+                               char* out_mps_mem, int mem_cap, char* out_mps_threads, int threads_cap);
 /* Score for every node of the builder, in node order: what the framework's 16 workers collect
  * by calling Score once per node (nodes whose Score fails get -1).  For replay drivers. */
 GS_API int gsp_plugin_score_all(gsp_plugin* p, int64_t* out_scores, int n);

@@ -30,7 +30,7 @@ ERR_NAMES = {-1: "GS_ERR_INVALID", -2: "GS_ERR_CUDA", -3: "GS_ERR_STATE", -4: "G
 # every symbol include/gpusched.h declares
 EXPORTS = [
     "gs_create", "gs_destroy", "gs_last_error", "gs_version", "gs_upload_cluster", "gs_upload_predictions",
-    "gs_score_batch", "gs_score_raw_dev", "gs_score_raw_dev_noalloc", "gs_normalize_dev", "gs_normalize_scores", "gs_select_mig",
+    "gs_score_batch", "gs_score_decisions", "gs_score_raw_dev", "gs_score_raw_dev_noalloc", "gs_normalize_dev", "gs_normalize_scores", "gs_select_mig",
     "gs_set_profiling", "gs_last_score_kernel_ms", "gs_last_stage_a_ms", "gs_selftest", "gs_selftest_filter", "gs_launch_count", "gs_complete_fit", "gs_complete_fit_sharded", "gs_complete_fit_transform", "gs_complete_transform", "gs_model_info", "gs_model_step", "gs_model_destroy",
 ]
 
@@ -79,6 +79,7 @@ def load_library():
     L.gs_upload_cluster.argtypes = [vp, C.POINTER(_GsCluster), i32]
     L.gs_upload_predictions.argtypes = [vp, C.POINTER(_GsPredictions)]
     L.gs_score_batch.argtypes = [vp, vp, vp, vp, i32, u32, vp, vp, vp]
+    L.gs_score_decisions.argtypes = [vp, vp, vp, vp, i32, u32, vp]
     L.gs_score_raw_dev.argtypes = [vp, vp, vp, vp, i32, u32, vp, vp, vp, vp, vp]
     L.gs_score_raw_dev_noalloc.argtypes = [vp, vp, vp, i32, vp, vp, vp, vp, vp]
     L.gs_normalize_dev.argtypes = [vp, i32, vp, vp, vp, vp, vp]
@@ -186,6 +187,20 @@ class Scheduler:
         self._check(self._L.gs_score_batch(self._h, _ptr(app), _ptr(slo), _ptr(self_slot), P, flags, _ptr(score),
                                            _ptr(sel), _ptr(best)))
         return score, sel, best
+
+    DECISION_DTYPE = np.dtype([("node", "<i4"), ("sel", "u1"), ("raw_hi", "u1"), ("raw_lo", "u1"), ("mps", "u1")])
+
+    def score_decisions(self, pods: Pods, flags: int = 0, out=None) -> np.ndarray:
+        """gs_score_decisions: per pod the chosen node, the selection byte there, the raw score extrema
+        and the V100 MPS configuration — 8 bytes per pod."""
+        app = np.ascontiguousarray(pods.app, dtype=np.uint32)
+        slo = np.ascontiguousarray(pods.slo, dtype=np.float32)
+        self_slot = None if pods.self_slot is None else np.ascontiguousarray(pods.self_slot, dtype=np.int32)
+        if out is None:
+            out = np.empty(app.shape[0], dtype=self.DECISION_DTYPE)
+        self._check(self._L.gs_score_decisions(self._h, _ptr(app), _ptr(slo), _ptr(self_slot), int(app.shape[0]),
+                                               int(flags), _ptr(out)))
+        return out
 
     # -- scoring, device pointers (torch tensors or raw addresses) ----------------------
     def score_raw_dev(self, d_app, d_slo, n_pods, d_score, d_sel, d_hi_arg, d_neg_lo, d_self=None, direct=False,

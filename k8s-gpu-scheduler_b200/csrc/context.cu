@@ -533,6 +533,51 @@ int gs_score_batch(gs_ctx* c, const uint32_t* pod_app, const float* pod_slo, con
   return GS_OK;
 }
 
+int gs_score_decisions(gs_ctx* c, const uint32_t* pod_app, const float* pod_slo, const int32_t* pod_self, int32_t P,
+                       uint32_t flags, gs_decision* out) {
+  static_assert(sizeof(gs_decision) == sizeof(gs::Decision) && sizeof(gs_decision) == 8, "decision layout");
+  if (!c) return GS_ERR_INVALID;
+  GS_LOCK(c);
+  if (P < 0 || P > gs::kMaxPods || (P && (!pod_app || !pod_slo || !out)))
+    return c->fail(GS_ERR_INVALID, "gs_score_decisions: null pointer or n_pods outside [0, 2^29]");
+  if (!c->have_cluster || !c->have_preds)
+    return c->fail(GS_ERR_STATE, "scoring needs gs_upload_cluster and gs_upload_predictions first");
+  if (P == 0) return GS_OK;
+  GS_CUDA(c, cudaSetDevice(c->device));
+  const size_t N = (size_t)c->n_nodes, PN = (size_t)P * N;
+  if (pod_self) {
+    bool any = false;
+    for (int32_t p = 0; p < P && !any; ++p) any = pod_self[p] >= 0;
+    if (!any) pod_self = nullptr;
+  }
+  if (pod_self)
+    for (int32_t p = 0; p < P; ++p)
+      if (pod_self[p] >= c->n_res) return c->fail(GS_ERR_INVALID, "gs_score_decisions: pod_self[%d] beyond residents", p);
+  int rc;
+  cudaStream_t s = c->stream;
+  if ((rc = c->upload(c->b_pod_app, pod_app, sizeof(uint32_t) * (size_t)P, "pod_app"))) return rc;
+  if ((rc = c->upload(c->b_pod_slo, pod_slo, sizeof(float) * (size_t)P, "pod_slo"))) return rc;
+  if (pod_self && (rc = c->upload(c->b_pod_self, pod_self, sizeof(int32_t) * (size_t)P, "pod_self"))) return rc;
+  if ((rc = c->reserve(c->b_score, PN ? PN : 1, "scores"))) return rc;
+  if ((rc = c->reserve(c->b_sel, PN ? PN : 1, "selections"))) return rc;
+  if ((rc = c->reserve(c->b_extrema, sizeof(uint64_t) * 2 * (size_t)P, "extrema"))) return rc;
+  if ((rc = c->reserve(c->b_misc, sizeof(gs_decision) * (size_t)P, "decisions"))) return rc;
+  uint64_t* d_hi = (uint64_t*)c->b_extrema.p;
+  uint64_t* d_neg = d_hi + P;
+  rc = score_raw_locked(c, (const uint32_t*)c->b_pod_app.p, (const float*)c->b_pod_slo.p,
+                        pod_self ? (const int32_t*)c->b_pod_self.p : nullptr, P, flags, (uint8_t*)c->b_score.p,
+                        (uint8_t*)c->b_sel.p, d_hi, d_neg, s);
+  if (rc) return rc;
+  gs::DevTables T = c->tables();
+  cudaError_t e = gs::launch_decisions(T, (const uint32_t*)c->b_pod_app.p, (const float*)c->b_pod_slo.p, P,
+                                       (const uint8_t*)c->b_sel.p, (const unsigned long long*)d_hi,
+                                       (const unsigned long long*)d_neg, (gs::Decision*)c->b_misc.p, s);
+  if (e != cudaSuccess) return c->cuda_fail(e, "decisions");
+  GS_CUDA(c, cudaMemcpyAsync(out, c->b_misc.p, sizeof(gs_decision) * (size_t)P, cudaMemcpyDeviceToHost, s));
+  GS_CUDA(c, cudaStreamSynchronize(s));
+  return GS_OK;
+}
+
 int gs_normalize_scores(gs_ctx* c, int64_t* scores, int32_t n) {
   if (!c) return GS_ERR_INVALID;
   GS_LOCK(c);

@@ -184,6 +184,8 @@ struct gsp_plugin {
   gsp_builder* b = nullptr;
   std::vector<uint8_t> row_score, row_sel;
   bool have_row = false;
+  uint32_t app = GS_APP_UNKNOWN;  // the cycle's pod, as PreScore saw it
+  float slo = 0.0f;
   std::string status;
 };
 
@@ -401,6 +403,8 @@ int gsp_plugin_prescore(gsp_plugin* p, const char* pod_name, const char* slo_env
   p->have_row = false;
   uint32_t app = p->b->app_of(pod_name);
   float slo = gsp_parse_slo(slo_env, nullptr);
+  p->app = app;
+  p->slo = slo;
   int rc = gs_score_batch(p->ctx, &app, &slo, nullptr, 1, GS_SCORE_RAW, p->row_score.data(), p->row_sel.data(), nullptr);
   if (rc != GS_OK) {
     p->status = std::string("Error in Logic() in Score(): ") + gs_last_error(p->ctx);  // :805
@@ -437,6 +441,67 @@ int gsp_plugin_score(gsp_plugin* p, const char* node_name, int64_t* out_score, c
   }
   p->status.clear();
   return GSP_SUCCESS;
+}
+
+int gsp_plugin_postbind(gsp_plugin* p, const char* node_name, char* out_uuid, int uuid_cap, char* out_mps_mem,
+                        int mem_cap, char* out_mps_threads, int threads_cap) {
+  auto put = [](char* dst, int cap, const char* src) {
+    if (dst && cap > 0) {
+      strncpy(dst, src, (size_t)cap - 1);
+      dst[cap - 1] = '\0';
+    }
+  };
+  put(out_uuid, uuid_cap, "");
+  put(out_mps_mem, mem_cap, "");
+  put(out_mps_threads, threads_cap, "");
+  if (!p || !node_name) return -GSP_ERROR;
+  auto it = p->b->node_index.find(node_name);
+  if (it == p->b->node_index.end() || !p->have_row) {
+    p->status = "PostBind: unknown node or no PreScore for this cycle";
+    return -GSP_ERROR;
+  }
+  if (!p->b->redis_reachable) {  // klog.Fatal("Redis not found"), gpu_plugins.go:852
+    p->status = "Redis not found";
+    return -GSP_ERROR;
+  }
+  const Node& n = p->b->nodes[it->second];
+  // cfgMap.Data[nodeName]: Logic's selectedUUID for this node (:759-768).  When Logic failed for the
+  // node the key is missing and the reference keeps a RANDOM UUID of the node (:889); the first one
+  // stands in for it here.
+  std::string uuid;
+  if (n.slo_error) {
+    if (!n.uuids.empty()) uuid = n.uuids[0];
+  } else {
+    const unsigned sel = GS_SEL_GPU(p->row_sel[it->second]);
+    if (sel != GS_SEL_NONE && sel < n.uuids.size()) uuid = n.uuids[sel];
+  }
+  // cfgMap.Data["MPS_"+nodeName]: the confIndex Logic recorded on V100 nodes inside its GPU loop
+  // (:640-665): "1P_V100" unless a smaller-than-current prediction above the SLO is found
+  if (!n.slo_error && n.model == GS_MODEL_V100 && !n.uuids.empty()) {
+    int which = 1;
+    float best = -1.0f;
+    if (p->app != GS_APP_UNKNOWN) {
+      for (int i = 0; i < 3; ++i) {
+        const int col = p->b->col_of[(GS_MODEL_V100 - 1) * (GS_MAX_GPUS_PER_NODE + 1) + (1 << i)];
+        if (col < 0) continue;
+        const float v = p->b->conf[(size_t)p->app * p->b->columns.size() + (size_t)col];
+        if (v > p->slo && (best == -1.0f || v < best)) {
+          best = v;
+          which = 1 << i;
+        }
+      }
+    }
+    if (which == 2) {  // strings.Contains(value, "2"), :897-899
+      put(out_mps_mem, mem_cap, "0=16350MB");
+      put(out_mps_threads, threads_cap, "50");
+    } else if (which == 4) {  // :900-902
+      put(out_mps_mem, mem_cap, "0=8175MB");
+      put(out_mps_threads, threads_cap, "25");
+    }
+  }
+  put(out_uuid, uuid_cap, uuid.c_str());
+  p->status.clear();
+  return uuid.empty() ? 0 : 1;  // the reference writes the three keys only when uuid != "" (:907)
 }
 
 int gsp_plugin_score_all(gsp_plugin* p, int64_t* out_scores, int n) {

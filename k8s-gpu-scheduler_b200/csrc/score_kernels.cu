@@ -483,6 +483,61 @@ cudaError_t launch_normalize_i64(long long* scores, int n, cudaStream_t s) {
   return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------ decisions --------
+
+// What the host needs of a scheduling decision, per pod: the chosen node, the selection byte there
+// (Logic's {nodeName: selectedUUID} record, gpu_plugins.go:759-768, which PostBind reads back at
+// :894-895), the raw score extrema, and which V100 configuration Logic recorded as MPS_<node>
+// (:640-665; PostBind turns it into the MPS limits at :896-903).
+__global__ void decisions_kernel(DevTables T, const uint32_t* __restrict__ pod_app, const float* __restrict__ pod_slo,
+                                 int n_pods, const uint8_t* __restrict__ sel,
+                                 const unsigned long long* __restrict__ hi_arg,
+                                 const unsigned long long* __restrict__ neg_lo, Decision* __restrict__ out) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_pods) return;
+  Decision d;
+  d.node = -1;
+  d.sel = (uint8_t)kSelNone;
+  d.raw_hi = d.raw_lo = d.mps = 0;
+  if (T.n_nodes > 0) {
+    const unsigned long long ha = hi_arg[p];
+    const uint32_t node = 0xFFFFFFFFu - (uint32_t)(ha & 0xFFFFFFFFull);  // global index
+    const int local = (int)node - T.node_base;
+    d.node = (int32_t)node;
+    d.raw_hi = (uint8_t)(ha >> 32);
+    d.raw_lo = (uint8_t)(100 - (int)neg_lo[p]);
+    if (local >= 0 && local < T.n_nodes) {  // on a node shard the winner may live on another rank
+      d.sel = sel[(size_t)p * T.n_nodes + local];
+      if (T.redis_reachable && T.node_model[local] == kModelV100 && T.node_ngpu[local] > 0) {
+        // confIndex starts as "1P_V100" and moves to the smallest prediction above the SLO
+        const uint32_t app = pod_app[p];
+        const float slo = pod_slo[p];
+        float c = -1.0f;
+        int which = 1;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          float tmp;
+          if (conf_lookup(T, app, kModelV100, 1 << i, &tmp) && tmp > slo && (c == -1.0f || tmp < c)) {
+            c = tmp;
+            which = 1 << i;
+          }
+        }
+        d.mps = (uint8_t)which;
+      }
+    }
+  }
+  out[p] = d;
+}
+
+cudaError_t launch_decisions(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
+                             const uint8_t* sel, const unsigned long long* hi_arg, const unsigned long long* neg_lo,
+                             Decision* out, cudaStream_t s) {
+  if (n_pods == 0) return cudaSuccess;
+  note_launch();
+  decisions_kernel<<<(n_pods + 255) / 256, 256, 0, s>>>(T, pod_app, pod_slo, n_pods, sel, hi_arg, neg_lo, out);
+  return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------ MIG choice -------
 
 // reconfigure()'s arithmetic, gpu_plugins.go:366-399; one thread per pod.

@@ -161,6 +161,14 @@ cudaError_t launch_score_main(const DevTables& T, const PodScratch& sc, uint8_t*
 cudaError_t launch_normalize(int n_pods, int n_nodes, int rescale, uint8_t* score,
                              const unsigned long long* hi_arg, const unsigned long long* neg_lo,
                              int32_t* best, cudaStream_t s);
+// one scheduling decision (mirrors gs_decision of include/gpusched.h)
+struct Decision {
+  int32_t node;
+  uint8_t sel, raw_hi, raw_lo, mps;
+};
+cudaError_t launch_decisions(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
+                             const uint8_t* sel, const unsigned long long* hi_arg, const unsigned long long* neg_lo,
+                             Decision* out, cudaStream_t s);
 cudaError_t launch_select_mig(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
                               uint8_t* out, cudaStream_t s);
 
