@@ -479,7 +479,8 @@ int gs_score_batch(gs_ctx* c, const uint32_t* pod_app, const float* pod_slo, con
     // the residents' sums once, for every app bucket present anywhere in the batch
     gs::PodScratch whole = c->scratch_view(P);
     cudaError_t e = gs::launch_pod_histogram(d_app, P, c->n_apps, (uint32_t*)c->sc_counts_all.p, s);
-    if (e == cudaSuccess) e = gs::launch_stage_a(T, (const uint32_t*)c->sc_counts_all.p, whole.stage, s);
+    const bool ln = c->lanes_nodes || (flags & GS_SCORE_LANES_NODES);
+    if (e == cudaSuccess) e = gs::launch_stage_any(T, (const uint32_t*)c->sc_counts_all.p, whole, s, ln);
     if (e != cudaSuccess) return c->cuda_fail(e, "stage_a (batch)");
     const int per = (P + n_slices - 1) / n_slices;
     for (int k = 0; k < n_slices; ++k) {
@@ -491,7 +492,7 @@ int gs_score_batch(gs_ctx* c, const uint32_t* pod_app, const float* pod_slo, con
       e = gs::launch_pod_bucketing(T, d_app + p0, d_slo + p0, np, sc, s);
       if (e == cudaSuccess)
         e = gs::launch_score_any(T, sc, d_score + row0, d_sel + row0, (unsigned long long*)(d_hi + p0),
-                                 (unsigned long long*)(d_neg + p0), s, c->lanes_nodes || (flags & GS_SCORE_LANES_NODES));
+                                 (unsigned long long*)(d_neg + p0), s, ln);
       if (e == cudaSuccess)
         e = gs::launch_expand_classes(T, sc.rep, np, d_score + row0, d_sel + row0, (unsigned long long*)(d_hi + p0),
                                       (unsigned long long*)(d_neg + p0), s);

@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(kTile, GS_MIN_CTAS) score_fast_kernel(DevTable
   if (blockIdx.x >= *n_chunks) return;
   const int tid = threadIdx.x;
   const ChunkDesc cd = chunks[blockIdx.x];
-  if (skip_plain && (cd.kind & 0xFFu) == (uint32_t)kKindPlain) return;  // served by score_pods_kernel
+  (void)skip_plain;
   if (tid < kLutSize) sm->lut[tid] = make_double2(tid ? __ddiv_rn(1.0, (double)tid) : 0.0, (double)tid);
 
   const uint32_t tile_node0 = blockIdx.y * kTile;
@@ -592,17 +592,27 @@ cudaError_t launch_score_main(const DevTables& T, const PodScratch& sc, uint8_t*
   return cudaGetLastError();
 }
 
-// the lanes-are-pods kernel needs the stage-A table and at most 8 GPU slots; everything else (small
-// batches, tables beyond the budget, the no-allocation entry point) runs the one-thread-per-node kernel
+// the lanes-are-pods kernel needs the per-batch table (here: in its folded form) and at most 8 GPU
+// slots; everything else (small batches, tables beyond the budget, the no-allocation entry point)
+// runs the one-thread-per-node kernel
+bool use_pods_kernel(const DevTables& T, const PodScratch& sc, bool lanes_nodes) {
+  return !lanes_nodes && sc.stage.n0 != nullptr && T.max_gpus <= kFastMaxGpus;
+}
+
+cudaError_t launch_stage_any(const DevTables& T, const uint32_t* counts, const PodScratch& sc, cudaStream_t s,
+                             bool lanes_nodes) {
+  return use_pods_kernel(T, sc, lanes_nodes) ? launch_stage_fold(T, counts, sc.stage, s)
+                                             : launch_stage_a(T, counts, sc.stage, s);
+}
+
 cudaError_t launch_score_any(const DevTables& T, const PodScratch& sc, uint8_t* score, uint8_t* sel,
                              unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s, bool lanes_nodes) {
-  if (!lanes_nodes && sc.stage.n0 != nullptr && T.max_gpus == kFastMaxGpus)
-    return launch_score_pods(T, sc, score, sel, hi_arg, neg_lo, s);
+  if (use_pods_kernel(T, sc, lanes_nodes)) return launch_score_pods(T, sc, score, sel, hi_arg, neg_lo, s);
   return launch_score_main(T, sc, score, sel, hi_arg, neg_lo, s, false);
 }
 
-// prof (optional) = three events: before stage A, between stage A and the scoring kernel, after the
-// scoring kernel (the class expansion that follows is outside the bracket)
+// prof (optional) = three events: before the stage kernel, between it and the scoring kernel, after
+// the scoring kernel (the class expansion that follows is outside the bracket)
 cudaError_t launch_score_fast(const DevTables& T, const uint32_t* pod_app, const float* pod_slo, int n_pods,
                               const PodScratch& sc, uint8_t* score, uint8_t* sel, unsigned long long* hi_arg,
                               unsigned long long* neg_lo, cudaStream_t s, const cudaEvent_t* prof, bool lanes_nodes) {
@@ -610,7 +620,7 @@ cudaError_t launch_score_fast(const DevTables& T, const uint32_t* pod_app, const
   cudaError_t e = launch_pod_bucketing(T, pod_app, pod_slo, n_pods, sc, s);
   if (e != cudaSuccess) return e;
   if (prof && (e = cudaEventRecord(prof[0], s)) != cudaSuccess) return e;
-  if ((e = launch_stage_a(T, sc.counts, sc.stage, s)) != cudaSuccess) return e;
+  if ((e = launch_stage_any(T, sc.counts, sc, s, lanes_nodes)) != cudaSuccess) return e;
   if (prof && (e = cudaEventRecord(prof[1], s)) != cudaSuccess) return e;
   if ((e = launch_score_any(T, sc, score, sel, hi_arg, neg_lo, s, lanes_nodes)) != cudaSuccess) return e;
   if (prof && (e = cudaEventRecord(prof[2], s)) != cudaSuccess) return e;

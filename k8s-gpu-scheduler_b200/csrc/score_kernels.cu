@@ -275,11 +275,16 @@ __global__ void __launch_bounds__(1024) pod_scan_kernel(int n_apps, const uint32
   for (int base = 0; base < n_buckets; base += 1024) {
     int b = base + threadIdx.x;
     uint32_t c = b < n_buckets ? counts[b] : 0u;
-    // work items: the kKindPlain and kKindNoV100 pods of an app are neighbours in the sorted order and
-    // share work items (the first bucket emits them for both); the other kinds get their own
+    // work items: the four kind buckets of an app are neighbours in the sorted order and share work
+    // items (the app's first bucket emits them)
     const int kind_b = b % kKinds;
-    const uint32_t c_items = kind_b == kKindPlain ? c + (b + 1 < n_buckets ? counts[b + 1] : 0u)
-                                                  : (kind_b == kKindNoV100 ? 0u : c);
+    uint32_t ck[kKinds] = {0u, 0u, 0u, 0u};
+    uint32_t c_items = 0u;
+    if (kind_b == 0 && b < n_buckets)
+      for (int q = 0; q < kKinds; ++q) {
+        ck[q] = counts[b + q];
+        c_items += ck[q];
+      }
     uint32_t n = (c_items + kChunk - 1) / kChunk;
     uint32_t ic = c, in = n;  // inclusive warp scans
 #pragma unroll
@@ -322,12 +327,15 @@ __global__ void __launch_bounds__(1024) pod_scan_kernel(int n_apps, const uint32
         if (off_n + j < max_chunks) {
           uint32_t len = c_items - j * kChunk;
           len = len < (uint32_t)kChunk ? len : (uint32_t)kChunk;
-          // kind field: bits 0..7 the kind; for kKindPlain items bits 8.. = how many of the item's pods are
-          // kKindPlain (they come first; the rest are kKindNoV100)
-          uint32_t n_plain = c > j * kChunk ? c - j * kChunk : 0u;
-          n_plain = n_plain < len ? n_plain : len;
-          chunks[off_n + j] = ChunkDesc{app, off_c + j * kChunk, len,
-                                        kind_b == kKindPlain ? ((uint32_t)kKindPlain | (n_plain << 8)) : (uint32_t)kind_b};
+          // pods of each kind inside [j * kChunk, j * kChunk + len) of the app's range
+          const uint32_t lo = j * kChunk, hi = lo + len;
+          uint32_t inside[kKinds], pos = 0u;
+          for (int q = 0; q < kKinds; ++q) {
+            const uint32_t a = pos > lo ? pos : lo, e = pos + ck[q] < hi ? pos + ck[q] : hi;
+            inside[q] = e > a ? e - a : 0u;
+            pos += ck[q];
+          }
+          chunks[off_n + j] = ChunkDesc{app, off_c + lo, len, pack_kinds(inside[0], inside[1], inside[2])};
         }
       }
     }
@@ -338,7 +346,10 @@ __global__ void __launch_bounds__(1024) pod_scan_kernel(int n_apps, const uint32
     }
     __syncthreads();
   }
-  if (threadIdx.x == 0) *n_chunks = s_carry_n < max_chunks ? s_carry_n : max_chunks;
+  if (threadIdx.x == 0) {
+    n_chunks[0] = s_carry_n < max_chunks ? s_carry_n : max_chunks;
+    n_chunks[1] = 0u;  // work counter of the persistent scoring kernel
+  }
 }
 
 __global__ void pod_scatter_kernel(DevTables T, const uint32_t* __restrict__ pod_app,

@@ -61,13 +61,19 @@ __host__ __device__ inline int bucket_of(uint32_t app, int n_apps, int kind) {
 }
 inline int n_buckets_for(int n_apps) { return (n_apps + 1) * kKinds; }
 
-// A work item of the restructured kernels: up to kChunk pods of one (app, kind) bucket.
+// A work item of the restructured kernels: up to kChunk pods of one app, ordered by kind.
 struct ChunkDesc {
   uint32_t app;
   uint32_t start;
   uint32_t len;
   uint32_t kind;
 };
+
+// ChunkDesc::kind of a work item: how many of its pods are of each kind, in the order they are stored
+// (plain | no V100 configuration | no SLO | the rest are general); kChunk <= 256 fits 9 bits each
+__host__ __device__ inline uint32_t pack_kinds(uint32_t n_plain, uint32_t n_nov, uint32_t n_inf) {
+  return n_plain | (n_nov << 9) | (n_inf << 18);
+}
 
 #ifndef GS_KCHUNK
 #define GS_KCHUNK 256
@@ -91,11 +97,27 @@ struct StageA {
   size_t stride;  // slots = n_nodes * max_gpus
 };
 
+// The same table after the fold (stage_fold_kernel, for the lanes-are-pods kernel): per (app bucket,
+// GPU slot) the float32 filter constants, the candidate's interference sum and the three integer
+// scores that do not depend on the pod's SLO.  24 bytes per entry as well: it lives in the same buffer.
+struct FoldTab {
+  float4* ab;    // {An, Bn, Ap, Bp}: tmp ~ A + B*v per branch; B = 0 with A = 0 means "filter off"
+  float* ci;     // the candidate's interference sum on that GPU
+  uint32_t* pk;  // residents-only score | score with a zero term, negative side << 8 | positive side << 16 | kFoldGeneral
+  size_t stride;
+};
+inline FoldTab fold_view(const StageA& st) {  // the stage buffer, seen as a fold table
+  const size_t e8 = (size_t)(st.p0 - st.n0);
+  char* base = (char*)st.n0;
+  return FoldTab{(float4*)base, (float*)(base + 16 * e8), (uint32_t*)(base + 20 * e8), st.stride};
+}
+constexpr uint32_t kFoldGeneral = 1u << 24;  // the slot's sums fall outside the streamlined domain
+
 // Scratch of the restructured path (owned by the context).
 struct PodScratch {
   uint32_t* counts;   // [(A+1)*kKinds + 1] pods per (app, kind) bucket (app A = unknown app)
   uint32_t* cursor;   // [(A+1)*kKinds + 1] scatter cursors
-  uint32_t* n_chunks; // [1]
+  uint32_t* n_chunks; // [2]: number of work items, and the work counter of the persistent scoring kernel
   ChunkDesc* chunks;  // [max_chunks]
   PodRec* sorted;     // [P]
   uint32_t* bucket;   // [P] bucket of each pod, kNoBucket for pods that are not scored themselves (duplicates)
@@ -141,8 +163,11 @@ cudaError_t launch_score_fast(const DevTables& T, const uint32_t* pod_app, const
                               const PodScratch& scratch, uint8_t* score, uint8_t* sel,
                               unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s,
                               const cudaEvent_t* prof = nullptr, bool lanes_nodes = false);
+cudaError_t launch_stage_any(const DevTables& T, const uint32_t* counts, const PodScratch& sc, cudaStream_t s,
+                             bool lanes_nodes);
 cudaError_t launch_score_any(const DevTables& T, const PodScratch& sc, uint8_t* score, uint8_t* sel,
                              unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s, bool lanes_nodes);
+cudaError_t launch_stage_fold(const DevTables& T, const uint32_t* counts, const StageA& stage, cudaStream_t s);
 cudaError_t launch_score_pods(const DevTables& T, const PodScratch& sc, uint8_t* score, uint8_t* sel,
                               unsigned long long* hi_arg, unsigned long long* neg_lo, cudaStream_t s);
 cudaError_t launch_expand_classes(const DevTables& T, const uint32_t* rep, int n_pods, uint8_t* score, uint8_t* sel,

@@ -46,6 +46,7 @@ def _lib():
     L.gsp_plugin_score.argtypes = [vp, cp, C.POINTER(C.c_int64), C.c_char_p, C.c_int]
     L.gsp_plugin_normalize_score.argtypes = [vp, vp, C.c_int]
     L.gsp_plugin_score_all.argtypes = [vp, vp, C.c_int]
+    L.gsp_plugin_postbind.argtypes = [vp, cp, C.c_char_p, C.c_int, C.c_char_p, C.c_int, C.c_char_p, C.c_int]
     L._gsp_ready = True
     return L
 
@@ -55,7 +56,7 @@ HOST_EXPORTS = [
     "gsp_builder_add_node", "gsp_builder_add_pod", "gsp_builder_set_redis_reachable", "gsp_builder_app_of",
     "gsp_parse_slo", "gsp_builder_build", "gsp_builder_cluster", "gsp_builder_predictions", "gsp_builder_last_error",
     "gsp_plugin_create", "gsp_plugin_destroy", "gsp_plugin_name", "gsp_plugin_last_status", "gsp_plugin_prescore",
-    "gsp_plugin_score", "gsp_plugin_score_all", "gsp_plugin_normalize_score",
+    "gsp_plugin_score", "gsp_plugin_score_all", "gsp_plugin_normalize_score", "gsp_plugin_postbind",
 ]
 
 
@@ -161,6 +162,15 @@ class Plugin:
         buf = C.create_string_buffer(128)
         rc = self._L.gsp_plugin_score(self._h, _enc(node_name), C.byref(s), buf, 128)
         return int(s.value), rc, self._L.gsp_plugin_last_status(self._h).decode(), buf.value.decode()
+
+    def postbind(self, node_name):
+        """PostBind's record for the last PreScore'd pod on node_name: (would_write, CUDA_VISIBLE_DEVICES,
+        CUDA_MPS_PINNED_DEVICE_MEM_LIMIT, CUDA_MPS_ACTIVE_THREAD_PERCENTAGE)."""
+        u, m, t = C.create_string_buffer(128), C.create_string_buffer(32), C.create_string_buffer(16)
+        rc = self._L.gsp_plugin_postbind(self._h, _enc(node_name), u, 128, m, 32, t, 16)
+        if rc < 0:
+            raise RuntimeError(self._L.gsp_plugin_last_status(self._h).decode())
+        return bool(rc), u.value.decode(), m.value.decode(), t.value.decode()
 
     def score_all(self, n_nodes, out=None):
         a = out if out is not None else np.empty(n_nodes, dtype=np.int64)

@@ -98,3 +98,47 @@ def test_redis_unreachable_returns_zero_everywhere(pkg, sched, world):
         assert (score, code, uuid) == (0, 0, "")
     plugin.close()
     b.close()
+
+
+def test_postbind_record_and_decisions(pkg, sched, oracle_mod, world):
+    """PostBind's data path (gpu_plugins.go:843-926): for the bound node, CUDA_VISIBLE_DEVICES is the
+    UUID Logic selected there, the MPS limits follow the V100 configuration Logic recorded; and the
+    batched decisions call returns the same facts in 8 bytes per pod."""
+    host, b, node_names, uuids, apps = world
+    plugin = host.Plugin(sched, b)
+    preds, cluster = b.build()
+    ora = oracle_mod.Oracle(preds, cluster)
+    v100_cols = [int(preds.col_of[1, k]) for k in (1, 2, 4)]
+    names, slos = [f"{apps[3]}-new", f"{apps[10]}-new", f"{apps[0]}-new", "busybox", f"{apps[16]}-new"], \
+        ["100", "12.5", None, "10", "650"]
+    pod_app = np.array([b.app_of(n) for n in names], dtype=np.uint32)
+    pod_slo = np.array([host.parse_slo(s)[0] for s in slos], dtype=np.float32)
+    dec = sched.score_decisions(pkg.Pods(app=pod_app, slo=pod_slo))
+    raw, sel, best = ora.score_batch(pkg.Pods(app=pod_app, slo=pod_slo), normalize=False)
+    for i, (pod_name, slo) in enumerate(zip(names, slos)):
+        rc, msg = plugin.pre_score(pod_name, slo)
+        assert rc == 0, msg
+        # expected MPS configuration: "1P_V100" unless a smaller prediction above the SLO exists (:640-651)
+        which, cur = 1, -1.0
+        if pod_app[i] != pkg.APP_UNKNOWN:
+            for k, col in zip((1, 2, 4), v100_cols):
+                v = preds.conf[pod_app[i], col] if col >= 0 else None
+                if v is not None and v > pod_slo[i] and (cur == -1.0 or v < cur):
+                    which, cur = k, v
+        for n, node in enumerate(node_names):
+            would, uuid, mem, thr = plugin.postbind(node)
+            g = int(sel[i, n]) & 31
+            want_uuid = uuids[node][g] if g != 31 and node != node_names[5] else ""
+            assert uuid == want_uuid and would == (want_uuid != "")
+            is_v100 = cluster.node_model[n] == pkg.MODEL_V100 and cluster.node_ngpu[n] > 0
+            want_mps = {2: ("0=16350MB", "50"), 4: ("0=8175MB", "25")}.get(which if is_v100 else 0, ("", ""))
+            assert (mem, thr) == want_mps
+        # the batched decision of the same pod
+        assert dec["node"][i] == best[i]
+        assert dec["sel"][i] == sel[i, best[i]]
+        assert dec["raw_hi"][i] == raw[i].max() and dec["raw_lo"][i] == raw[i].min()
+        bn = int(best[i])
+        is_v100 = cluster.node_model[bn] == pkg.MODEL_V100 and cluster.node_ngpu[bn] > 0
+        assert dec["mps"][i] == (which if is_v100 else 0)
+    with pytest.raises(RuntimeError):
+        plugin.postbind("no-such-node")
