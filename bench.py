@@ -250,6 +250,7 @@ def main():
     ap.add_argument("--app-dist", default="zipf", choices=["zipf", "uniform"], help="sensitivity runs only")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -350,6 +351,47 @@ def main():
     evals_per_step = P * NL * world
     value = evals_per_step * args.steps / (total_ms * 1e-3)
 
+    # ---- extras (N = 1): what class dedupe buys, and the same step on a Deployment-like batch
+    extras = {}
+    if world == 1 and not args.no_extras:
+        def timed(app_t, slo_t, flags, n=5):
+            def one():
+                st = torch.cuda.current_stream().cuda_stream
+                sch.score_raw_dev(app_t, slo_t, P, d_score, d_sel, d_ext[0], d_ext[1], stream=st, flags=flags)
+                sch.normalize_dev(P, d_score, d_ext[0], d_ext[1], d_best, stream=st)
+            for _ in range(3):
+                one()
+            evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n)]
+            torch.cuda.synchronize()
+            for a, b in evs:
+                flush.zero_()
+                a.record()
+                one()
+                b.record()
+            torch.cuda.synchronize()
+            ms = sum(a.elapsed_time(b) for a, b in evs) / n
+            return {"ms_per_step": ms, "value": P * NL / (ms * 1e-3), "unit": UNIT,
+                    "hbm_frac_of_whole_step": abytes_all / (ms * 1e-3) / 1e9 / measured_peak_gbs()[0]}
+
+        abytes_all = algorithmic_bytes(P, NL, int(cluster.res_app.size), n_apps, preds.conf.shape[1], GPUS_PER_NODE)
+        extras["all_classes_unique"] = dict(timed(d_app, d_slo, pkg.SCORE_NO_DEDUPE),
+                                            note="same batch, every pod scored itself (GS_SCORE_NO_DEDUPE): the worst case")
+        dp = pkg.synth.make_pods(P, n_apps, app_dist=args.app_dist, slo_levels=16)
+        dd_app = torch.from_numpy(dp.app.view(np.int32)).to(dev)
+        dd_slo = torch.from_numpy(dp.slo).to(dev)
+        r = timed(dd_app, dd_slo, 0)
+        sch.score_raw_dev(dd_app, dd_slo, P, d_score, d_sel, d_ext[0], d_ext[1],
+                          stream=torch.cuda.current_stream().cuda_stream)
+        sch.normalize_dev(P, d_score, d_ext[0], d_ext[1], d_best, stream=torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        r.update(distinct_app_slo_classes=pkg.synth.distinct_classes(dp),
+                 parity_ok=parity_check(pkg, preds, cluster_all, dp, rank, NL, d_score, d_sel, d_best),
+                 note="Deployment-like batch: 16 SLO values per app, same apps and cluster; pods with equal "
+                      "(app, SLO) are scored once and their rows copied")
+        extras["discrete_slo"] = r
+        r2 = timed(dd_app, dd_slo, pkg.SCORE_NO_DEDUPE)
+        extras["discrete_slo"]["ms_per_step_without_dedupe"] = r2["ms_per_step"]
+
     # ---- e2e: host buffers through gs_score_batch (pinned), copies inside the timed region
     e2e = None
     if not args.no_e2e:
@@ -427,6 +469,8 @@ def main():
                          "frac_of_whole_step": abytes / (total_ms / args.steps * 1e-3) / 1e9 / peak,
                          "note": "achieved = the step's algorithmic bytes / the scoring kernels' duration; the kernel is bound by the FP32/ALU pipes (about 13 instructions per (pod,node,GPU) evaluation), not by HBM: DESIGN.md 4.2 states why 50 % of HBM is out of reach without (app, SLO) duplicates"},
         }
+        if extras:
+            line["extras"] = extras
         if e2e:
             line["e2e"] = e2e
         if not args.no_cpu_baseline and world == 1:

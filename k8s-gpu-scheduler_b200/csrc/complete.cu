@@ -1032,9 +1032,10 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
         bayes_ridge_kernel<<<1, 256, bayes_smem, s>>>(dG, dMu, dNobs, d, j, dV, mm, 1, dEv,
                                                       dCoef + (size_t)step * (d - 1), dIcpt + step, dIters + step);
       }
-      if (missing[j] > 0)
+      if (missing[j] > 0) {
         gs::note_launch();
         predict_kernel<<<(n + 7) / 8, 256, 0, s>>>(dXt, dMask, n, d, j, dCoef + (size_t)step * (d - 1), dIcpt + step);
+      }
       if (big_gram && dead_off[j + 1] > dead_off[j]) {  // column j changed on this rank: row/column j of dH
         gs::note_launch();
         h_row_partial_kernel<<<h_blocks, 256, 0, s>>>(dXt, n, d, j, dMeans, dHPart);

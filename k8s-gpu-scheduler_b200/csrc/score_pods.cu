@@ -144,9 +144,10 @@ constexpr int kNW = 32 / kPW;  // nodes per pass
 
 struct NodeHdr {
   uint32_t nocand;  // score << 8 | selected GPU of the residents alone (:667-696)
-  uint32_t flags;   // bits 0..7 selection-byte flags of the node; kHdrV100; bits 16.. = GPUs of the node
+  uint32_t flags;   // bits 0..7 selection-byte flags of the node; kHdrV100; bits 16..23 = GPUs of the node;
+                    // bits 24..31 = the flags of a pod with a candidate term here (node flags | F6 on V100 | F7)
   float bound;      // |conf| (A30) + max_g |ci_g|: the node's part of the bound on |t|
-  uint32_t pad;
+  uint32_t keybase;  // lane_key(0, node): the node's part of the per-pod (score, lowest node) key
 };
 constexpr uint32_t kHdrV100 = 1u << 8;
 
@@ -327,9 +328,10 @@ __global__ void __launch_bounds__(32, 16) score_pods_kernel(DevTables T, FoldTab
       }
       NodeHdr h;
       h.nocand = ((uint32_t)nc_score << 8) | nc_sel;
-      h.flags = node_flags | (model == kModelV100 ? kHdrV100 : 0u) | ((uint32_t)k << 16);
+      h.flags = node_flags | (model == kModelV100 ? kHdrV100 : 0u) | ((uint32_t)k << 16) |
+                ((node_flags | (model == kModelV100 ? kFlagF6 : 0u) | kFlagF7) << 24);
       h.bound = (model == kModelA30 ? fabsf(conf_a30) : 0.0f) + ci_max;
-      h.pad = 0u;
+      h.keybase = lane_key(0, (uint32_t)node);
       sm->hdr[lane] = h;
       // evaluation lists and template rows: [0] every node with a GPU loop, [1] A30 nodes only (pods that
       // no V100 configuration satisfies have no candidate term on V100 nodes, :667).
@@ -372,7 +374,7 @@ __global__ void __launch_bounds__(32, 16) score_pods_kernel(DevTables T, FoldTab
 
     // -------------------------------------------------------------- phase 2: lane = (pod, node)
     const float2 one2 = make_float2(1.0f, 1.0f), mone2 = make_float2(-1.0f, -1.0f);
-    const float2 magic2 = make_float2(8388608.0f, 8388608.0f), nmagic2 = make_float2(-8388608.0f, -8388608.0f);
+    const float2 magic2 = make_float2(8388608.0f, 8388608.0f), nmagic2 = make_float2(-8388607.5f, -8388607.5f);
     const float2 eight2 = make_float2(8.0f, 8.0f);
     // the work item's pods by kind: [0, e0) plain, [e0, e1) no V100 configuration, [e1, e2) no SLO, [e2, len) general
     const uint32_t e0 = cd.kind & 0x1FFu, e1 = e0 + ((cd.kind >> 9) & 0x1FFu), e2 = e1 + ((cd.kind >> 18) & 0x1FFu);
@@ -422,7 +424,7 @@ __global__ void __launch_bounds__(32, 16) score_pods_kernel(DevTables T, FoldTab
           best = sc > 0 ? sc * 8 + (GT - 1 - (int)g) : 0;
         }
       } else {
-        float fbest = 0.f, rlo = 0.5f, rhi = 0.5f;
+        float fbest = 0.f, rdev = 0.f;  // rdev = max over GPUs of |frac(est) - 0.5|
 #pragma unroll
         for (int gp = 0; gp < GT / 2; ++gp) {
           const float2 st2 = *reinterpret_cast<const float2*>(&sm->st[n][2 * gp]);
@@ -439,25 +441,26 @@ __global__ void __launch_bounds__(32, 16) score_pods_kernel(DevTables T, FoldTab
           const float2 estn = __ffma2_rn(make_float2(abn.z, abn.w), v2, make_float2(abn.x, abn.y));
           const float2 estp = __ffma2_rn(make_float2(abp.z, abp.w), v2, make_float2(abp.x, abp.y));
           const float2 est = make_float2(neg0 ? estn.x : estp.x, neg1 ? estn.y : estp.y);
-          const float2 fl = __fadd2_rn(__fadd2_rz(est, magic2), nmagic2);  // floor for 0 <= est < 2^22, exact
-          const float2 r = __ffma2_rn(fl, mone2, est);                     // est - floor(est), exact
-          const float2 key = __ffma2_rn(fl, eight2, make_float2((float)(GT - 1 - 2 * gp), (float)(GT - 2 - 2 * gp)));
-          rlo = fminf(fminf(rlo, r.x), r.y);
-          rhi = fmaxf(fmaxf(rhi, r.x), r.y);
+          // flh = floor(est) + 0.5 (exact for 0 <= est < 2^22: 2^23 - 0.5 is a float), rc = frac(est) - 0.5 (exact)
+          const float2 flh = __fadd2_rn(__fadd2_rz(est, magic2), nmagic2);
+          const float2 rc = __ffma2_rn(flh, mone2, est);
+          // key = floor(est) * 8 + (GT - 1 - g) = flh * 8 + (GT - 5 - g)
+          const float2 key = __ffma2_rn(flh, eight2, make_float2((float)(GT - 5 - 2 * gp), (float)(GT - 6 - 2 * gp)));
+          rdev = fmaxf(fmaxf(rdev, fabsf(rc.x)), fabsf(rc.y));
           fbest = fmaxf(fmaxf(fbest, key.x), key.y);
         }
-        best = (int)fbest;
-        const bool unsure = has_cand && !(rlo >= kFilterDelta && rhi <= 1.0f - kFilterDelta);
+        best = __float_as_int(fbest + 8388608.0f) & 0x7FFFFF;  // fbest is a small non-negative integer: no F2I
+        const bool unsure = has_cand && !(rdev <= 0.5f - kFilterDelta);  // some estimate within kFilterDelta of an integer
         if (__any_sync(0xFFFFFFFFu, unsure)) {
-          best = redo_pass<GT>(sm, T, app, node0 + n, n, (int)(h.flags >> 16), s, arinv, negconf, has_cand);
+          best = redo_pass<GT>(sm, T, app, node0 + n, n, (int)((h.flags >> 16) & 0xFFu), s, arinv, negconf, has_cand);
         }
       }
       const int score = best >> 3;
       const unsigned sel = score > 0 ? (unsigned)(GT - 1 - (best & 7)) : kSelNone;
       if (has_cand) {
         sm->stage_score[pi][n] = (uint8_t)score;
-        sm->stage_sel[pi][n] = (uint8_t)(sel | (h.flags & 0xFFu) | (is_v ? kFlagF6 : 0u) | kFlagF7);
-        hi = max(hi, lane_key(score, (uint32_t)(node0 + n)));
+        sm->stage_sel[pi][n] = (uint8_t)(sel | (h.flags >> 24));
+        hi = max(hi, ((uint32_t)score << 24) + h.keybase);
         ng = max(ng, (uint32_t)(100 - score));
       }
     }

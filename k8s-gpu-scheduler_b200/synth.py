@@ -138,7 +138,10 @@ def make_cluster(
 
 
 def make_pods(n_pods: int, n_apps: int = 1024, seed: int = SEED, p_unknown_app: float = 0.0,
-              app_dist: str = "zipf") -> Pods:
+              app_dist: str = "zipf", slo_levels: int = 0) -> Pods:
+    """slo_levels > 0: Deployment-like batch — every app has that many distinct SLO values and its
+    pods draw from them (pods of one Deployment share app and SLO, deploy/busybox/busybox.yaml:26-28);
+    0: the survey's synthetic batch with continuous SLOs."""
     rng = _rng(seed, 3)
     if app_dist == "uniform":  # sensitivity runs: small, equal app buckets
         app = rng.integers(0, n_apps, size=n_pods).astype(np.uint32)
@@ -148,7 +151,12 @@ def make_pods(n_pods: int, n_apps: int = 1024, seed: int = SEED, p_unknown_app: 
     if p_unknown_app > 0:
         app[rng.random(n_pods) < p_unknown_app] = APP_UNKNOWN
     slo = rng.uniform(10.0, 600.0, size=n_pods)
-    slo[rng.random(n_pods) < 0.10] = 0.0  # SLO env missing
+    missing = rng.random(n_pods) < 0.10
+    if slo_levels > 0:
+        levels = np.round(_rng(seed, 4).uniform(10.0, 600.0, size=(n_apps + 1, slo_levels)), 1)
+        row = np.where(app < n_apps, app, n_apps).astype(np.int64)
+        slo = levels[row, _rng(seed, 5).integers(0, slo_levels, size=n_pods)]
+    slo[missing] = 0.0  # SLO env missing
     return Pods(app=app, slo=slo.astype(np.float32))
 
 
