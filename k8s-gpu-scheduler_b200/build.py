@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libgpusched.so")
-SOURCES = ["context.cu", "score_kernels.cu", "score_fast.cu", "score_pods.cu", "complete.cu", "noalloc.cu"]
+SOURCES = ["context.cu", "score_kernels.cu", "score_fast.cu", "score_pods.cu", "complete.cu", "eig_jacobi.cu", "noalloc.cu"]
 HOST_SOURCES = ["host/gpu_plugin.cpp"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -72,7 +72,7 @@ def build(force: bool = False, verbose: bool = False, tag: str = "", defines=())
         if p.returncode != 0:
             raise RuntimeError(f"nvcc failed on {src}:\n{out}")
     cmd = [_nvcc(), "-shared", "-ccbin", "/usr/bin/g++", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB, *objs,
-           "-Xcompiler", "-fPIC", "-cudart", "static", "-ldl"]
+           "-Xcompiler", "-fPIC", "-cudart", "static"]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}")

@@ -13,7 +13,6 @@
 //     sse = y^T y - 2 coef~.b~ + sum(coef~^2 s);
 //   * rows where j is missing get x.coef + intercept (predict_kernel).
 // Everything is float64; parity bar: 1e-5 relative against Imputer.predict (tests/golden).
-#include <dlfcn.h>
 
 #include <algorithm>
 #include <cmath>
@@ -24,7 +23,7 @@
 #include <new>
 #include <vector>
 
-#include <cusolverDn.h>  // types and prototypes only: the library is dlopen'ed when a large fit needs it
+#include "eig_jacobi.h"
 
 #include "../../include/gpusched.h"
 #include "context.h"
@@ -32,7 +31,7 @@
 namespace gs {
 
 constexpr int kMaxFeatures = 1024; // d - 1 <= 1023 (shared arrays of the evidence iteration)
-constexpr int kJacobiMax = 24;     // d - 1 <= 24: hand-written one-CTA Jacobi (covers the reference tables); beyond: cuSOLVER syevd
+constexpr int kJacobiMax = 24;     // d - 1 <= 24: one-CTA Jacobi (covers the reference tables); beyond: block Jacobi (eig_jacobi.cu)
 constexpr int kGramTile = 32;
 constexpr int kRounds = 10;        // IterativeImputer(max_iter=10), recommender.py:16
 constexpr double kRoundTol = 1e-3; // IterativeImputer tol
@@ -517,15 +516,6 @@ __global__ void __launch_bounds__(1024) jacobi_eig_kernel(const double* __restri
   if (tid == 0) *sweeps_out = sweep;
 }
 
-// A = G without row/column j (input of the library eigensolver)
-__global__ void extract_minor_kernel(const double* __restrict__ G, int d, int j, double* __restrict__ A) {
-  const int m = d - 1;
-  int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= m * m) return;
-  int a = e / m, b = e % m;
-  A[e] = G[(size_t)(a < j ? a : a + 1) * d + (b < j ? b : b + 1)];
-}
-
 // ---- BayesianRidge's evidence iteration in the eigenbasis, one CTA ----
 __device__ __forceinline__ double block_sum(double v, double* s_red) {
   const int tid = threadIdx.x;
@@ -733,37 +723,6 @@ struct gs_model {
 
 namespace {
 
-// cuSOLVER's symmetric eigensolver for the larger Gram matrices, bound at run time so that the
-// library loads (and everything else works) without it.
-struct Cusolver {
-  void* lib = nullptr;
-  cusolverDnHandle_t h = nullptr;
-  decltype(&cusolverDnCreate) create = nullptr;
-  decltype(&cusolverDnDestroy) destroy = nullptr;
-  decltype(&cusolverDnSetStream) set_stream = nullptr;
-  decltype(&cusolverDnDsyevd_bufferSize) bufsize = nullptr;
-  decltype(&cusolverDnDsyevd) syevd = nullptr;
-  bool open(cudaStream_t s) {
-    const char* names[] = {"libcusolver.so.11", "/usr/local/cuda/lib64/libcusolver.so.11", "libcusolver.so.12",
-                           "libcusolver.so"};
-    for (const char* n : names)
-      if ((lib = dlopen(n, RTLD_NOW | RTLD_LOCAL))) break;
-    if (!lib) return false;
-    create = (decltype(create))dlsym(lib, "cusolverDnCreate");
-    destroy = (decltype(destroy))dlsym(lib, "cusolverDnDestroy");
-    set_stream = (decltype(set_stream))dlsym(lib, "cusolverDnSetStream");
-    bufsize = (decltype(bufsize))dlsym(lib, "cusolverDnDsyevd_bufferSize");
-    syevd = (decltype(syevd))dlsym(lib, "cusolverDnDsyevd");
-    if (!create || !destroy || !set_stream || !bufsize || !syevd) return false;
-    if (create(&h) != CUSOLVER_STATUS_SUCCESS) return false;
-    return set_stream(h, s) == CUSOLVER_STATUS_SUCCESS;
-  }
-  ~Cusolver() {
-    if (h && destroy) destroy(h);
-    // the library stays loaded for the life of the process
-  }
-};
-
 struct DevMem {
   std::vector<void*> ptrs;
   ~DevMem() {
@@ -883,23 +842,14 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
     CK(mem.alloc(&dH, (size_t)d * d));
     CK(mem.alloc(&dHPart, (size_t)h_blocks * d));
   }
-  // eigen-solver: hand-written Jacobi up to kJacobiMax, cuSOLVER's syevd beyond
+  // eigen-solver: the one-CTA Jacobi up to kJacobiMax, the multi-CTA block Jacobi (eig_jacobi.cu) beyond
   const int mm = d - 1;
-  const bool use_lib = mm > kJacobiMax;
-  Cusolver cus;
-  double* dWork = nullptr;
-  int* dInfo = nullptr;
-  int lwork = 0;
-  if (use_lib) {
-    if (!cus.open(s))
-      return c->fail(GS_ERR_UNSUPPORTED, "gs_complete_fit: %d columns need cuSOLVER (libcusolver.so.11), which could "
-                     "not be loaded: %s", d, dlerror() ? dlerror() : "symbol or handle error");
-    if (cus.bufsize(cus.h, CUSOLVER_EIG_MODE_VECTOR, CUBLAS_FILL_MODE_LOWER, mm, dA, mm, dEv, &lwork) !=
-        CUSOLVER_STATUS_SUCCESS)
-      return c->fail(GS_ERR_CUDA, "cusolverDnDsyevd_bufferSize failed");
-    CK(mem.alloc(&dWork, (size_t)lwork));
-    CK(mem.alloc(&dInfo, max_steps));
-    CK(cudaMemsetAsync(dInfo, 0, sizeof(int) * max_steps, s));
+  const bool use_block = mm > kJacobiMax;
+  double* dEigWork = nullptr;
+  const int eig_mp = use_block ? eig_padded_size(mm) : 0;
+  std::vector<int> block_sweeps;
+  if (use_block) {
+    CK(mem.alloc(&dEigWork, eig_work_doubles(mm)));
     CK(cudaMemsetAsync(dSweeps, 0, sizeof(int) * max_steps, s));
   }
   const size_t bayes_smem = sizeof(double) * 6 * (size_t)(mm > 0 ? mm : 1);
@@ -1012,17 +962,15 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
         gs::note_launch();
         recentre_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dG, d, dMu, dMeans, dNobs);
       }
-      if (use_lib) {
+      if (use_block) {
+        int sw = 0;
+        const cudaError_t ee = eig_block_jacobi(dG, d, j, dEigWork, dEv, &sw, s);
+        if (ee != cudaSuccess) return c->cuda_fail(ee, "completion: block Jacobi eigensolver");
+        block_sweeps.push_back(sw);
+        // eigenvectors in the columns of V = work + mp*mp, row stride mp
         gs::note_launch();
-        extract_minor_kernel<<<(mm * mm + 255) / 256, 256, 0, s>>>(dG, d, j, dA);
-        if (cus.syevd(cus.h, CUSOLVER_EIG_MODE_VECTOR, CUBLAS_FILL_MODE_LOWER, mm, dA, mm, dEv, dWork, lwork,
-                      dInfo + step) != CUSOLVER_STATUS_SUCCESS) {
-          return c->fail(GS_ERR_CUDA, "cusolverDnDsyevd failed at step %d", step);
-        }
-        // eigenvectors come back column-major in dA: V[i][k] = dA[i + k*mm]
-        gs::note_launch();
-        bayes_ridge_kernel<<<1, 256, bayes_smem, s>>>(dG, dMu, dNobs, d, j, dA, 1, mm, dEv,
-                                                      dCoef + (size_t)step * (d - 1), dIcpt + step, dIters + step);
+        bayes_ridge_kernel<<<1, 256, bayes_smem, s>>>(dG, dMu, dNobs, d, j, dEigWork + (size_t)eig_mp * eig_mp, eig_mp, 1,
+                                                      dEv, dCoef + (size_t)step * (d - 1), dIcpt + step, dIters + step);
       } else {
         int jt = 32;
         while (jt < 1024 && jt < mm * mm / 4) jt <<= 1;
@@ -1072,12 +1020,10 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
   if (e != cudaSuccess) {
     return c->cuda_fail(e, "completion: model download");
   }
-  if (use_lib) e = cudaMemcpy(sweeps.data(), dInfo, sizeof(int) * step, cudaMemcpyDeviceToHost);
-  if (e != cudaSuccess) {
-    return c->cuda_fail(e, "completion: eigen-solver status download");
-  }
+  if (use_block)
+    for (int k = 0; k < step && k < (int)block_sweeps.size(); ++k) sweeps[k] = block_sweeps[k] >= 40 ? 60 : block_sweeps[k];
   for (int k = 0; k < step; ++k)
-    if (use_lib ? sweeps[k] != 0 : sweeps[k] >= 60) {
+    if (sweeps[k] >= 60) {
       return c->fail(GS_ERR_NOCONV, "gs_complete_fit: the eigen-solver did not converge at step %d", k);
     }
   // the completed training rows: what transform(X) would return (observed entries are never written)

@@ -1,0 +1,308 @@
+// eig_jacobi.cu — symmetric eigendecomposition for the recommender's completion (sm_100a).
+//
+// BayesianRidge.fit takes an SVD of the centred design matrix per feature
+// (pkg/recommender/recommender/recommender.py:15-17 -> sklearn linear_model/_bayes.py:262-306:
+// eigen_vals_ = S^2, Vh); here that is the eigendecomposition of the centred Gram matrix G without
+// row/column j.  Up to 24 columns complete.cu's one-CTA Jacobi serves; beyond, this file: a
+// two-sided BLOCK Jacobi across CTAs (round 1 called cuSOLVER's syevd there).
+//
+//   The m x m matrix is padded to mp = nb * kB (nb even) and split into nb block columns of kB = 16.
+//   A sweep is nb - 1 steps of a round-robin tournament; in a step the nb / 2 disjoint block pairs
+//   (I, J) are processed independently:
+//     bj_pivot_kernel  one CTA per pair: the 32 x 32 pivot [A_II A_IJ; A_JI A_JJ] is diagonalised in
+//                      shared memory by cyclic Jacobi (parallel ordering, 16 rotations per step) and
+//                      the accumulated rotation Q (32 x 32, orthogonal) written out;
+//     bj_rows_kernel   A <- Q^T A on the pair's 32 rows;
+//     bj_cols_kernel   A <- A Q and V <- V Q on the pair's 32 columns.
+//   Sweeps repeat until off(A)^2 <= 1e-30 ||A||^2 (or the off-norm stagnates on the rounding floor),
+//   the same stopping rule as the one-CTA kernel.  Padding rows/columns are zero and never rotate.
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "eig_jacobi.h"
+#include "tables.h"
+
+namespace gs {
+
+constexpr int kB = 16;       // block size
+constexpr int kP = 2 * kB;   // pivot size
+
+__host__ __device__ inline void bj_pair(int nb, int step, int p, int* I, int* J) {
+  int a, b;
+  if (p == 0) {
+    a = nb - 1;
+    b = step;
+  } else {
+    a = (step + p) % (nb - 1);
+    b = (step - p + (nb - 1)) % (nb - 1);
+  }
+  *I = a < b ? a : b;
+  *J = a < b ? b : a;
+}
+
+// A = G without row/column j, padded with zeros to mp x mp; V = identity
+__global__ void bj_init_kernel(const double* __restrict__ G, int d, int j, int mp, double* __restrict__ A,
+                               double* __restrict__ V) {
+  const int m = d - 1;
+  const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= (size_t)mp * mp) return;
+  const int a = (int)(e / mp), b = (int)(e % mp);
+  double v = 0.0;
+  if (a < m && b < m) v = G[(size_t)(a < j ? a : a + 1) * d + (b < j ? b : b + 1)];
+  A[e] = v;
+  if (V) V[e] = a == b ? 1.0 : 0.0;
+}
+
+// norms[0] += sum of squares off the diagonal, norms[1] += sum of all squares
+__global__ void __launch_bounds__(256) bj_norm_kernel(const double* __restrict__ A, int mp, double* norms) {
+  __shared__ double s_off[256], s_tot[256];
+  double off = 0.0, tot = 0.0;
+  const size_t n = (size_t)mp * mp;
+  for (size_t e = (size_t)blockIdx.x * 256 + threadIdx.x; e < n; e += (size_t)gridDim.x * 256) {
+    const double v = A[e];
+    tot += v * v;
+    if (e / mp != e % mp) off += v * v;
+  }
+  s_off[threadIdx.x] = off;
+  s_tot[threadIdx.x] = tot;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) {
+      s_off[threadIdx.x] += s_off[threadIdx.x + s];
+      s_tot[threadIdx.x] += s_tot[threadIdx.x + s];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    atomicAdd(&norms[0], s_off[0]);
+    atomicAdd(&norms[1], s_tot[0]);
+  }
+}
+
+// One CTA per block pair: diagonalise the 32 x 32 pivot, write the accumulated rotation Q.
+__global__ void __launch_bounds__(256) bj_pivot_kernel(const double* __restrict__ A, int mp, int nb, int step,
+                                                      double* __restrict__ Qout) {
+  __shared__ double S[kP][kP + 1], Q[kP][kP + 1];
+  __shared__ double s_c[kB], s_s[kB];
+  __shared__ int s_p[kB], s_q[kB];
+  __shared__ double s_red[256];
+  __shared__ double s_offn, s_totn;
+  const int tid = threadIdx.x;
+  int I, J;
+  bj_pair(nb, step, blockIdx.x, &I, &J);
+  for (int e = tid; e < kP * kP; e += 256) {
+    const int r = e / kP, c = e % kP;
+    const int gr = (r < kB ? I * kB + r : J * kB + r - kB), gc = (c < kB ? I * kB + c : J * kB + c - kB);
+    S[r][c] = A[(size_t)gr * mp + gc];
+    Q[r][c] = r == c ? 1.0 : 0.0;
+  }
+  __syncthreads();
+  for (int sweep = 0; sweep < 16; ++sweep) {
+    double off = 0.0, tot = 0.0;
+    for (int e = tid; e < kP * kP; e += 256) {
+      const double v = S[e / kP][e % kP];
+      tot += v * v;
+      if (e / kP != e % kP) off += v * v;
+    }
+    s_red[tid] = off;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+      if (tid < s) s_red[tid] += s_red[tid + s];
+      __syncthreads();
+    }
+    if (tid == 0) s_offn = s_red[0];
+    __syncthreads();
+    s_red[tid] = tot;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+      if (tid < s) s_red[tid] += s_red[tid + s];
+      __syncthreads();
+    }
+    if (tid == 0) s_totn = s_red[0];
+    __syncthreads();
+    if (s_offn <= 1e-32 * s_totn || s_totn == 0.0) break;
+    for (int st = 0; st < kP - 1; ++st) {
+      if (tid < kB) {
+        int p, q;
+        if (tid == 0) {
+          p = kP - 1;
+          q = st;
+        } else {
+          p = (st + tid) % (kP - 1);
+          q = (st - tid + (kP - 1)) % (kP - 1);
+        }
+        if (p > q) {
+          const int t = p;
+          p = q;
+          q = t;
+        }
+        double c = 1.0, s = 0.0;
+        const double apq = S[p][q], app = S[p][p], aqq = S[q][q];
+        if (fabs(apq) > 1e-300 && fabs(apq) > 1e-18 * sqrt(fabs(app * aqq))) {
+          const double theta = (aqq - app) / (2.0 * apq);
+          const double t = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+          c = 1.0 / sqrt(t * t + 1.0);
+          s = t * c;
+        }
+        s_p[tid] = p;
+        s_q[tid] = q;
+        s_c[tid] = c;
+        s_s[tid] = s;
+      }
+      __syncthreads();
+      // columns: S <- S J, Q <- Q J
+      for (int e = tid; e < kB * kP; e += 256) {
+        const int pr = e / kP, i = e % kP;
+        const double c = s_c[pr], s = s_s[pr];
+        if (s == 0.0) continue;
+        const int p = s_p[pr], q = s_q[pr];
+        const double aip = S[i][p], aiq = S[i][q];
+        S[i][p] = c * aip - s * aiq;
+        S[i][q] = s * aip + c * aiq;
+        const double vip = Q[i][p], viq = Q[i][q];
+        Q[i][p] = c * vip - s * viq;
+        Q[i][q] = s * vip + c * viq;
+      }
+      __syncthreads();
+      // rows: S <- J^T S
+      for (int e = tid; e < kB * kP; e += 256) {
+        const int pr = e / kP, i = e % kP;
+        const double c = s_c[pr], s = s_s[pr];
+        if (s == 0.0) continue;
+        const int p = s_p[pr], q = s_q[pr];
+        const double api = S[p][i], aqi = S[q][i];
+        S[p][i] = c * api - s * aqi;
+        S[q][i] = s * api + c * aqi;
+      }
+      __syncthreads();
+    }
+  }
+  double* out = Qout + (size_t)blockIdx.x * kP * kP;
+  for (int e = tid; e < kP * kP; e += 256) out[e] = Q[e / kP][e % kP];
+}
+
+// A <- Q^T A on the 32 rows of every pair; grid (pairs, column tiles of 128)
+__global__ void __launch_bounds__(256) bj_rows_kernel(double* __restrict__ A, int mp, int nb, int step,
+                                                     const double* __restrict__ Qin) {
+  __shared__ double Q[kP][kP + 1];
+  int I, J;
+  bj_pair(nb, step, blockIdx.x, &I, &J);
+  const double* q = Qin + (size_t)blockIdx.x * kP * kP;
+  for (int e = threadIdx.x; e < kP * kP; e += 256) Q[e / kP][e % kP] = q[e];
+  __syncthreads();
+  const int c = blockIdx.y * 128 + (threadIdx.x & 127);
+  const int r0 = (threadIdx.x >> 7) * kB;  // this thread's 16 output rows of the 32
+  if (c >= mp) return;
+  double in[kP];
+#pragma unroll
+  for (int k = 0; k < kP; ++k) in[k] = A[(size_t)(k < kB ? I * kB + k : J * kB + k - kB) * mp + c];
+#pragma unroll
+  for (int r = 0; r < kB; ++r) {
+    double acc = 0.0;
+#pragma unroll
+    for (int k = 0; k < kP; ++k) acc += Q[k][r0 + r] * in[k];
+    const int rr = r0 + r;
+    A[(size_t)(rr < kB ? I * kB + rr : J * kB + rr - kB) * mp + c] = acc;
+  }
+}
+
+// M <- M Q on the 32 columns of every pair, for M = A (z = 0) and M = V (z = 1);
+// grid (pairs, row tiles of 64, 2)
+__global__ void __launch_bounds__(256) bj_cols_kernel(double* __restrict__ A, double* __restrict__ V, int mp, int nb,
+                                                     int step, const double* __restrict__ Qin) {
+  __shared__ double Q[kP][kP + 1];
+  __shared__ double T[64][kP + 1];
+  double* M = blockIdx.z == 0 ? A : V;
+  if (!M) return;
+  int I, J;
+  bj_pair(nb, step, blockIdx.x, &I, &J);
+  const double* q = Qin + (size_t)blockIdx.x * kP * kP;
+  for (int e = threadIdx.x; e < kP * kP; e += 256) Q[e / kP][e % kP] = q[e];
+  const int row0 = blockIdx.y * 64;
+  for (int e = threadIdx.x; e < 64 * kP; e += 256) {
+    const int r = e / kP, k = e % kP;
+    const int gr = row0 + r, gc = k < kB ? I * kB + k : J * kB + k - kB;
+    T[r][k] = gr < mp ? M[(size_t)gr * mp + gc] : 0.0;
+  }
+  __syncthreads();
+  // thread -> row r, eight output columns c0..c0+7
+  const int r = threadIdx.x >> 2, c0 = (threadIdx.x & 3) * 8;
+  double acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.0;
+#pragma unroll
+  for (int k = 0; k < kP; ++k) {
+    const double t = T[r][k];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] += t * Q[k][c0 + i];
+  }
+  const int gr = row0 + r;
+  if (gr < mp) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int c = c0 + i;
+      M[(size_t)gr * mp + (c < kB ? I * kB + c : J * kB + c - kB)] = acc[i];
+    }
+  }
+}
+
+__global__ void bj_diag_kernel(const double* __restrict__ A, int mp, int m, double* __restrict__ evals) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < m) evals[k] = fmax(A[(size_t)k * mp + k], 0.0);  // S^2 >= 0
+}
+
+int eig_padded_size(int m) {
+  int nb = (m + kB - 1) / kB;
+  if (nb & 1) ++nb;
+  if (nb < 2) nb = 2;
+  return nb * kB;
+}
+
+size_t eig_work_doubles(int m) {
+  const size_t mp = (size_t)eig_padded_size(m);
+  return 2 * mp * mp + (mp / kP) * kP * kP + 8;
+}
+
+// Eigendecomposition of G (d x d) without row/column j: evals[m], eigenvectors in the columns of
+// V = work + mp*mp (row-major, row stride mp).  Synchronises the stream once per sweep (the stopping
+// rule is evaluated on the host).  *sweeps_out (host memory) = sweeps run.
+cudaError_t eig_block_jacobi(const double* G, int d, int j, double* work, double* evals, int* sweeps_out,
+                             cudaStream_t s) {
+  const int m = d - 1, mp = eig_padded_size(m), nb = mp / kB;
+  double* A = work;
+  double* V = work + (size_t)mp * mp;
+  double* Q = V + (size_t)mp * mp;
+  double* norms = Q + (size_t)(nb / 2) * kP * kP;
+  const size_t n2 = (size_t)mp * mp;
+  note_launch();
+  bj_init_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, s>>>(G, d, j, mp, A, V);
+  double prev_off = -1.0;
+  int sweep = 0;
+  for (; sweep < 40; ++sweep) {
+    cudaError_t e = cudaMemsetAsync(norms, 0, 2 * sizeof(double), s);
+    if (e != cudaSuccess) return e;
+    note_launch();
+    bj_norm_kernel<<<296, 256, 0, s>>>(A, mp, norms);
+    double h[2];
+    if ((e = cudaMemcpyAsync(h, norms, sizeof h, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return e;
+    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return e;
+    // converged at off/||A|| <= 1e-15, or stagnating on the rounding floor
+    if (h[0] <= 1e-30 * h[1] || h[1] == 0.0) break;
+    if (h[0] <= 1e-24 * h[1] && prev_off >= 0.0 && h[0] > 0.25 * prev_off) break;
+    prev_off = h[0];
+    for (int step = 0; step < nb - 1; ++step) {
+      note_launch();
+      bj_pivot_kernel<<<nb / 2, 256, 0, s>>>(A, mp, nb, step, Q);
+      note_launch();
+      bj_rows_kernel<<<dim3(nb / 2, (mp + 127) / 128), 256, 0, s>>>(A, mp, nb, step, Q);
+      note_launch();
+      bj_cols_kernel<<<dim3(nb / 2, (mp + 63) / 64, 2), 256, 0, s>>>(A, V, mp, nb, step, Q);
+    }
+  }
+  note_launch();
+  bj_diag_kernel<<<(m + 255) / 256, 256, 0, s>>>(A, mp, m, evals);
+  if (sweeps_out) *sweeps_out = sweep;
+  return cudaGetLastError();
+}
+
+}  // namespace gs

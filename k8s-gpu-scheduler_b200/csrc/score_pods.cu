@@ -139,6 +139,9 @@ cudaError_t launch_stage_fold(const DevTables& T, const uint32_t* counts, const 
 
 // ------------------------------------------------------------------ scoring kernel --------
 
+#ifndef GS_PODS_MIN_CTAS
+#define GS_PODS_MIN_CTAS 20
+#endif
 constexpr int kPW = 8;         // pods per pass
 constexpr int kNW = 32 / kPW;  // nodes per pass
 
@@ -151,18 +154,21 @@ struct NodeHdr {
 };
 constexpr uint32_t kHdrV100 = 1u << 8;
 
+// Row strides are padded so that the records of any four nodes out of eight consecutive ones (what a
+// pass reads side by side) start in different banks: 80 B (20 words: 20k mod 32 is a different
+// multiple of 4 for k = 0..7), 40 B (10 words), and 40-byte staging rows for the eight pods.
 template <int GT>
 struct PodsSmem {
-  float4 abn[kSlice][GT / 2];  // per GPU pair {An[g], An[g+1], Bn[g], Bn[g+1]}
-  float4 abp[kSlice][GT / 2];  // the same for the positive branch
-  float st[kSlice][GT];        // A30: ci - conf (= -(conf - ci), :716);  V100: ci (the pod's conf is subtracted per lane)
-  uint32_t pk[kSlice][GT];     // FoldTab::pk of the node's GPUs (scores with a zero candidate term, for pods without an SLO)
+  float4 abn[kSlice][GT / 2 + 1];  // per GPU pair {An[g], An[g+1], Bn[g], Bn[g+1]}
+  float4 abp[kSlice][GT / 2 + 1];  // the same for the positive branch
+  float st[kSlice][GT + 2];        // A30: ci - conf (= -(conf - ci), :716);  V100: ci (the pod's conf is subtracted per lane)
+  uint32_t pk[kSlice][GT];         // FoldTab::pk of the node's GPUs (scores with a zero candidate term, for pods without an SLO)
   NodeHdr hdr[kSlice];
   double2 lut[kLutSize];
-  uint8_t list[2][kSlice];     // [V100 nodes wanted?] nodes of the slice to evaluate (streamlined domain)
-  uint8_t glist[2][kSlice];    // ... nodes to evaluate op for op (sums outside the domain)
+  uint8_t list[2][kSlice];         // [V100 nodes wanted?] nodes of the slice to evaluate (streamlined domain)
+  uint8_t glist[2][kSlice];        // ... nodes to evaluate op for op (sums outside the domain)
   uint8_t tmpl_score[2][kSlice], tmpl_sel[2][kSlice];  // results of the nodes that are not evaluated
-  uint8_t stage_score[kPW][kSlice], stage_sel[kPW][kSlice];
+  uint8_t stage_score[kPW][kSlice + 8], stage_sel[kPW][kSlice + 8];
   uint32_t n_list[2], n_glist[2], key_c[2], neg_c[2];  // extrema of the template nodes
 };
 
@@ -231,7 +237,7 @@ static __device__ __noinline__ int redo_pass(const PodsSmem<GT>* sm, const DevTa
 }
 
 template <int GT>
-__global__ void __launch_bounds__(32, 16) score_pods_kernel(DevTables T, FoldTab fold, const PodRec* __restrict__ pods,
+__global__ void __launch_bounds__(32, GS_PODS_MIN_CTAS) score_pods_kernel(DevTables T, FoldTab fold, const PodRec* __restrict__ pods,
                                                              const ChunkDesc* __restrict__ chunks,
                                                              uint32_t* __restrict__ n_chunks,
                                                              uint8_t* __restrict__ out_score,
@@ -573,7 +579,7 @@ cudaError_t launch_score_pods(const DevTables& T, const PodScratch& sc, uint8_t*
     cudaGetDevice(&dev);
     if (cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n_sm <= 0) n_sm = 148;
   }
-  const unsigned grid = (unsigned)n_sm * 16u;  // 16 resident one-warp CTAs per SM (__launch_bounds__(32, 16))
+  const unsigned grid = (unsigned)n_sm * (unsigned)GS_PODS_MIN_CTAS;  // as many one-warp CTAs as stay resident
   const FoldTab fold = fold_view(sc.stage);
   note_launch();
   if (T.max_gpus <= 2)

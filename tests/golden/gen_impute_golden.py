@@ -51,6 +51,10 @@ def main():
     cases["synth_500x32"] = synthetic(500, 32, 6, 0.30, 4)
     cases["synth_400x72"] = synthetic(400, 72, 8, 0.30, 6)      # beyond the Jacobi range: library eigensolver path
     cases["synth_300x136"] = synthetic(300, 136, 8, 0.25, 7)    # wide enough for the 128x128-tile Gram kernel
+    cases["synth_320x264"] = synthetic(320, 264, 12, 0.25, 9)   # > 256 columns: block Jacobi on a 17-block pivot grid
+    only = [a for a in sys.argv[1:] if not a.startswith("-")]
+    if only:
+        cases = {k: v for k, v in cases.items() if k in only}
     for name, X in cases.items():
         with warnings.catch_warnings():
             warnings.simplefilter("ignore")
@@ -64,6 +68,8 @@ def main():
             q_out = imp.predict(Xq)
         feats = np.array([t.feat_idx for t in m.imputation_sequence_], dtype=np.int32)
         coefs = np.array([t.estimator.coef_ for t in m.imputation_sequence_], dtype=np.float64).reshape(len(feats), -1)
+        if X.shape[1] > 200:
+            coefs = coefs[-X.shape[1]:]      # the last round only: keeps the fixture small
         inter = np.array([t.estimator.intercept_ for t in m.imputation_sequence_], dtype=np.float64)
         np.savez_compressed(os.path.join(HERE, f"impute_{name}.npz"), X=X, completed=completed, n_iter=m.n_iter_,
                             feats=feats, coefs=coefs, intercepts=inter, means=m.initial_imputer_.statistics_,
