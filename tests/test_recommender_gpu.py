@@ -50,6 +50,20 @@ def test_replies_match_reference_imputer_and_reload(pkg, sched, oracle_mod, tmp_
     assert np.allclose(res, gi["completed"][k].astype(np.float32), rtol=1e-5)     # incl. the imputed A30 diagonal entry
     res, cols = r.impute_configurations("busybox")                                  # recom_server.py:157-160
     assert res.tolist() == [0.0] and cols == []
+    # the same replies over the wire: recom.proto served from the GPU-completed tables
+    from k8s_gpu_scheduler_b200 import recom_grpc
+
+    server, port = recom_grpc.make_server(r, port=0)
+    server.start()
+    try:
+        cl = recom_grpc.Client(f"127.0.0.1:{port}")
+        res_w, cols_w = cl.impute_interference("tensorflow-mobilenet-4096_A30")
+        assert cols_w == list(names["interference_columns"])
+        assert np.array_equal(np.float32(res_w), res)
+        assert cl.impute_configurations("busybox") == ([0.0], [])
+        cl.close()
+    finally:
+        server.stop(0)
     # hot reload on md5 change (recom_server.py:84-97)
     assert r.maybe_reload() == []
     X2 = gc["X"].copy()
