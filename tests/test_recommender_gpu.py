@@ -59,7 +59,7 @@ def test_replies_match_reference_imputer_and_reload(pkg, sched, oracle_mod, tmp_
         cl = recom_grpc.Client(f"127.0.0.1:{port}")
         res_w, cols_w = cl.impute_interference("tensorflow-mobilenet-4096_A30")
         assert cols_w == list(names["interference_columns"])
-        assert np.array_equal(np.float32(res_w), res)
+        assert np.array_equal(np.float32(res_w), r.impute_interference("tensorflow-mobilenet-4096_A30")[0])
         assert cl.impute_configurations("busybox") == ([0.0], [])
         cl.close()
     finally:
