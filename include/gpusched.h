@@ -222,6 +222,43 @@ GS_API int gs_normalize_dev(gs_ctx* ctx, int32_t n_pods, uint8_t* d_score,
                      const uint64_t* d_hi_arg, const uint64_t* d_neg_lo, int32_t* d_best,
                      void* stream);
 
+/* The best node alone from the (global) extrema, without rescaling any score: d_best[p] as gs_normalize_dev
+ * decodes it.  For callers that keep raw scores. */
+GS_API int gs_best_dev(gs_ctx* ctx, int32_t n_pods, const uint64_t* d_hi_arg, const uint64_t* d_neg_lo,
+                       int32_t* d_best, void* stream);
+
+/* gs_score_decisions' last step on DEVICE pointers, after gs_score_raw_dev (and, on a node shard, after
+ * the extrema were made global): d_out[p] as in gs_decision; on a shard whose nodes do not include
+ * pod p's winner, sel = GS_SEL_NONE and mps = 0 (the owning shard reports them). */
+GS_API int gs_decisions_dev(gs_ctx* ctx, const uint32_t* d_pod_app, const float* d_pod_slo, int32_t n_pods,
+                            const uint8_t* d_sel, const uint64_t* d_hi_arg, const uint64_t* d_neg_lo,
+                            gs_decision* d_out, void* stream);
+
+/* ---------------------------------------------------------------- several GPUs ----- */
+
+/* Node-sharded scoring over several GPUs of one box in ONE process (no counterpart
+ * in the reference, which scores one (pod, node) per call on the CPU).  The cluster's nodes are
+ * block-partitioned over the devices inside the library, pods and prediction tables are replicated,
+ * and the per-pod extrema that NormalizeScore (gpu_plugins.go:818-827) and host selection need are
+ * merged with atomicMax over the peer mapping (NVLink) into device 0's copy — no NCCL, no second
+ * process.  Needs peer access from every device to the first one (GS_ERR_UNSUPPORTED otherwise).
+ * Results are bit-identical to one device holding all nodes.
+ *
+ *   gs_mscore_batch      same arguments and results as gs_score_batch (no self table): full
+ *                        [n_pods x n_nodes] matrices in the caller's node order + best node per pod
+ *   gs_mscore_decisions  same results as gs_score_decisions */
+typedef struct gs_mctx gs_mctx;
+GS_API int gs_create_multi(const int* devices, int n_devices, gs_mctx** out);
+GS_API void gs_destroy_multi(gs_mctx* mctx);
+GS_API const char* gs_multi_last_error(const gs_mctx* mctx);
+GS_API int gs_multi_device_count(const gs_mctx* mctx);
+GS_API int gs_mupload_predictions(gs_mctx* mctx, const gs_predictions* preds);
+GS_API int gs_mupload_cluster(gs_mctx* mctx, const gs_cluster* cluster);
+GS_API int gs_mscore_batch(gs_mctx* mctx, const uint32_t* pod_app, const float* pod_slo, int32_t n_pods,
+                           uint32_t flags, uint8_t* out_score, uint8_t* out_sel, int32_t* out_best);
+GS_API int gs_mscore_decisions(gs_mctx* mctx, const uint32_t* pod_app, const float* pod_slo, int32_t n_pods,
+                               uint32_t flags, gs_decision* out);
+
 /* gs_score_raw_dev for callers that must not allocate.  (No counterpart in the reference.)
  *
  * The regular scoring entry points grow context-owned device buffers with cudaMalloc when a

@@ -30,7 +30,9 @@ ERR_NAMES = {-1: "GS_ERR_INVALID", -2: "GS_ERR_CUDA", -3: "GS_ERR_STATE", -4: "G
 # every symbol include/gpusched.h declares
 EXPORTS = [
     "gs_create", "gs_destroy", "gs_last_error", "gs_version", "gs_upload_cluster", "gs_upload_predictions",
-    "gs_score_batch", "gs_score_decisions", "gs_score_raw_dev", "gs_score_raw_dev_noalloc", "gs_normalize_dev", "gs_normalize_scores", "gs_select_mig",
+    "gs_score_batch", "gs_score_decisions", "gs_decisions_dev", "gs_best_dev", "gs_create_multi", "gs_destroy_multi",
+    "gs_multi_last_error", "gs_multi_device_count", "gs_mupload_predictions", "gs_mupload_cluster", "gs_mscore_batch",
+    "gs_mscore_decisions", "gs_score_raw_dev", "gs_score_raw_dev_noalloc", "gs_normalize_dev", "gs_normalize_scores", "gs_select_mig",
     "gs_set_profiling", "gs_last_score_kernel_ms", "gs_last_stage_a_ms", "gs_selftest", "gs_selftest_filter", "gs_launch_count", "gs_complete_fit", "gs_complete_fit_sharded", "gs_complete_fit_transform", "gs_complete_transform", "gs_model_info", "gs_model_step", "gs_model_destroy",
 ]
 
@@ -80,6 +82,18 @@ def load_library():
     L.gs_upload_predictions.argtypes = [vp, C.POINTER(_GsPredictions)]
     L.gs_score_batch.argtypes = [vp, vp, vp, vp, i32, u32, vp, vp, vp]
     L.gs_score_decisions.argtypes = [vp, vp, vp, vp, i32, u32, vp]
+    L.gs_decisions_dev.argtypes = [vp, vp, vp, i32, vp, vp, vp, vp, vp]
+    L.gs_best_dev.argtypes = [vp, i32, vp, vp, vp, vp]
+    L.gs_create_multi.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(vp)]
+    L.gs_destroy_multi.argtypes = [vp]
+    L.gs_destroy_multi.restype = None
+    L.gs_multi_last_error.argtypes = [vp]
+    L.gs_multi_last_error.restype = C.c_char_p
+    L.gs_multi_device_count.argtypes = [vp]
+    L.gs_mupload_predictions.argtypes = [vp, C.POINTER(_GsPredictions)]
+    L.gs_mupload_cluster.argtypes = [vp, C.POINTER(_GsCluster)]
+    L.gs_mscore_batch.argtypes = [vp, vp, vp, i32, u32, vp, vp, vp]
+    L.gs_mscore_decisions.argtypes = [vp, vp, vp, i32, u32, vp]
     L.gs_score_raw_dev.argtypes = [vp, vp, vp, vp, i32, u32, vp, vp, vp, vp, vp]
     L.gs_score_raw_dev_noalloc.argtypes = [vp, vp, vp, i32, vp, vp, vp, vp, vp]
     L.gs_normalize_dev.argtypes = [vp, i32, vp, vp, vp, vp, vp]
@@ -257,6 +271,63 @@ class Scheduler:
         slo = np.ascontiguousarray(pods.slo, dtype=np.float32)
         out = np.empty(app.shape[0], dtype=np.uint8)
         self._check(self._L.gs_select_mig(self._h, _ptr(app), _ptr(slo), int(app.shape[0]), _ptr(out)))
+        return out
+
+
+class MultiScheduler:
+    """gs_mctx: node-sharded scoring over several GPUs of one box in this process, through the C ABI alone
+    (nodes block-partitioned inside the library; extrema merged over the peer mapping)."""
+
+    def __init__(self, devices):
+        self._L = load_library()
+        devs = (C.c_int * len(devices))(*[int(d) for d in devices])
+        h = C.c_void_p()
+        rc = self._L.gs_create_multi(devs, len(devices), C.byref(h))
+        if rc != GS_OK:
+            raise GsError(rc, f"gs_create_multi({list(devices)}) failed (no peer access, or no such device)")
+        self._h = h
+        self.n_nodes = 0
+
+    def _check(self, rc):
+        if rc != GS_OK:
+            raise GsError(rc, self._L.gs_multi_last_error(self._h).decode())
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.gs_destroy_multi(self._h)
+            self._h = None
+
+    def upload_predictions(self, pr: Predictions):
+        conf = np.ascontiguousarray(pr.conf, dtype=np.float32)
+        interf = np.ascontiguousarray(pr.interf, dtype=np.float32)
+        col_of = np.ascontiguousarray(pr.col_of, dtype=np.int32)
+        s = _GsPredictions(int(conf.shape[0]), int(conf.shape[1]) if conf.ndim == 2 else 0, _ptr(conf), _ptr(interf),
+                           _ptr(col_of))
+        self._check(self._L.gs_mupload_predictions(self._h, C.byref(s)))
+
+    def upload_cluster(self, cl: Cluster):
+        keep = [np.ascontiguousarray(cl.node_model, dtype=np.uint8), np.ascontiguousarray(cl.node_ngpu, dtype=np.uint8),
+                np.ascontiguousarray(cl.gpu_off, dtype=np.uint32), np.ascontiguousarray(cl.res_app, dtype=np.uint32),
+                np.ascontiguousarray(cl.res_slo, dtype=np.float32)]
+        s = _GsCluster(int(keep[0].shape[0]), int(cl.max_gpus), *[_ptr(a) for a in keep], int(cl.redis_reachable))
+        self._check(self._L.gs_mupload_cluster(self._h, C.byref(s)))
+        self.n_nodes = int(keep[0].shape[0])
+
+    def score_batch(self, pods: Pods, normalize: bool = True, flags: int = 0, out=None):
+        app = np.ascontiguousarray(pods.app, dtype=np.uint32)
+        slo = np.ascontiguousarray(pods.slo, dtype=np.float32)
+        P, N = int(app.shape[0]), self.n_nodes
+        score, sel, best = out if out is not None else (np.empty((P, N), np.uint8), np.empty((P, N), np.uint8),
+                                                        np.empty(P, np.int32))
+        self._check(self._L.gs_mscore_batch(self._h, _ptr(app), _ptr(slo), P, int(flags) | (SCORE_NORMALIZE if normalize else 0),
+                                            _ptr(score), _ptr(sel), _ptr(best)))
+        return score, sel, best
+
+    def score_decisions(self, pods: Pods, flags: int = 0) -> np.ndarray:
+        app = np.ascontiguousarray(pods.app, dtype=np.uint32)
+        slo = np.ascontiguousarray(pods.slo, dtype=np.float32)
+        out = np.empty(app.shape[0], dtype=Scheduler.DECISION_DTYPE)
+        self._check(self._L.gs_mscore_decisions(self._h, _ptr(app), _ptr(slo), int(app.shape[0]), int(flags), _ptr(out)))
         return out
 
 

@@ -419,6 +419,20 @@ int gs_normalize_dev(gs_ctx* c, int32_t n_pods, uint8_t* d_score, const uint64_t
   return c->note_use(stream ? (cudaStream_t)stream : c->stream);
 }
 
+int gs_best_dev(gs_ctx* c, int32_t n_pods, const uint64_t* d_hi_arg, const uint64_t* d_neg_lo, int32_t* d_best,
+                void* stream) {
+  if (!c) return GS_ERR_INVALID;
+  GS_LOCK(c);
+  if (n_pods < 0 || (n_pods && (!d_hi_arg || !d_neg_lo || !d_best)))
+    return c->fail(GS_ERR_INVALID, "gs_best_dev: null pointer or negative n_pods");
+  GS_CUDA(c, cudaSetDevice(c->device));
+  cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+  cudaError_t e = gs::launch_normalize(n_pods, c->n_nodes, 0, nullptr, (const unsigned long long*)d_hi_arg,
+                                       (const unsigned long long*)d_neg_lo, d_best, s);
+  if (e != cudaSuccess) return c->cuda_fail(e, "best node");
+  return c->note_use(s);
+}
+
 int gs_score_batch(gs_ctx* c, const uint32_t* pod_app, const float* pod_slo, const int32_t* pod_self, int32_t P,
                    uint32_t flags, uint8_t* out_score, uint8_t* out_sel, int32_t* out_best) {
   if (!c) return GS_ERR_INVALID;
@@ -577,6 +591,23 @@ int gs_score_decisions(gs_ctx* c, const uint32_t* pod_app, const float* pod_slo,
   GS_CUDA(c, cudaMemcpyAsync(out, c->b_misc.p, sizeof(gs_decision) * (size_t)P, cudaMemcpyDeviceToHost, s));
   GS_CUDA(c, cudaStreamSynchronize(s));
   return GS_OK;
+}
+
+int gs_decisions_dev(gs_ctx* c, const uint32_t* d_pod_app, const float* d_pod_slo, int32_t n_pods, const uint8_t* d_sel,
+                     const uint64_t* d_hi_arg, const uint64_t* d_neg_lo, gs_decision* d_out, void* stream) {
+  if (!c) return GS_ERR_INVALID;
+  GS_LOCK(c);
+  if (n_pods < 0 || (n_pods && (!d_pod_app || !d_pod_slo || !d_sel || !d_hi_arg || !d_neg_lo || !d_out)))
+    return c->fail(GS_ERR_INVALID, "gs_decisions_dev: null pointer or negative n_pods");
+  if (!c->have_cluster || !c->have_preds)
+    return c->fail(GS_ERR_STATE, "gs_decisions_dev needs gs_upload_cluster and gs_upload_predictions first");
+  GS_CUDA(c, cudaSetDevice(c->device));
+  cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+  gs::DevTables T = c->tables();
+  cudaError_t e = gs::launch_decisions(T, d_pod_app, d_pod_slo, n_pods, d_sel, (const unsigned long long*)d_hi_arg,
+                                       (const unsigned long long*)d_neg_lo, (gs::Decision*)d_out, s);
+  if (e != cudaSuccess) return c->cuda_fail(e, "decisions");
+  return c->note_use(s);
 }
 
 int gs_normalize_scores(gs_ctx* c, int64_t* scores, int32_t n) {
