@@ -26,6 +26,7 @@ namespace gs {
 
 constexpr int kB = 16;       // block size
 constexpr int kP = 2 * kB;   // pivot size
+constexpr int kInnerSweeps = 3;
 
 __host__ __device__ inline void bj_pair(int nb, int step, int p, int* I, int* J) {
   int a, b;
@@ -85,8 +86,6 @@ __global__ void __launch_bounds__(256) bj_pivot_kernel(const double* __restrict_
   __shared__ double S[kP][kP + 1], Q[kP][kP + 1];
   __shared__ double s_c[kB], s_s[kB];
   __shared__ int s_p[kB], s_q[kB];
-  __shared__ double s_red[256];
-  __shared__ double s_offn, s_totn;
   const int tid = threadIdx.x;
   int I, J;
   bj_pair(nb, step, blockIdx.x, &I, &J);
@@ -97,30 +96,11 @@ __global__ void __launch_bounds__(256) bj_pivot_kernel(const double* __restrict_
     Q[r][c] = r == c ? 1.0 : 0.0;
   }
   __syncthreads();
-  for (int sweep = 0; sweep < 16; ++sweep) {
-    double off = 0.0, tot = 0.0;
-    for (int e = tid; e < kP * kP; e += 256) {
-      const double v = S[e / kP][e % kP];
-      tot += v * v;
-      if (e / kP != e % kP) off += v * v;
-    }
-    s_red[tid] = off;
-    __syncthreads();
-    for (int s = 128; s > 0; s >>= 1) {
-      if (tid < s) s_red[tid] += s_red[tid + s];
-      __syncthreads();
-    }
-    if (tid == 0) s_offn = s_red[0];
-    __syncthreads();
-    s_red[tid] = tot;
-    __syncthreads();
-    for (int s = 128; s > 0; s >>= 1) {
-      if (tid < s) s_red[tid] += s_red[tid + s];
-      __syncthreads();
-    }
-    if (tid == 0) s_totn = s_red[0];
-    __syncthreads();
-    if (s_offn <= 1e-32 * s_totn || s_totn == 0.0) break;
+  // a few cyclic sweeps: the pivot need not be diagonalised exactly for the block iteration to
+  // converge, and every barrier here is latency on the critical path of the step.  A sweep in which
+  // no rotation passes the threshold ends the loop.
+  for (int sweep = 0; sweep < kInnerSweeps; ++sweep) {
+    bool rotated = false;
     for (int st = 0; st < kP - 1; ++st) {
       if (tid < kB) {
         int p, q;
@@ -148,8 +128,9 @@ __global__ void __launch_bounds__(256) bj_pivot_kernel(const double* __restrict_
         s_q[tid] = q;
         s_c[tid] = c;
         s_s[tid] = s;
+        rotated = rotated || s != 0.0;
       }
-      __syncthreads();
+      if (!__syncthreads_or(tid < kB && s_s[tid] != 0.0)) continue;  // nothing to rotate in this step
       // columns: S <- S J, Q <- Q J
       for (int e = tid; e < kB * kP; e += 256) {
         const int pr = e / kP, i = e % kP;
@@ -176,6 +157,7 @@ __global__ void __launch_bounds__(256) bj_pivot_kernel(const double* __restrict_
       }
       __syncthreads();
     }
+    if (!__syncthreads_or(rotated)) break;
   }
   double* out = Qout + (size_t)blockIdx.x * kP * kP;
   for (int e = tid; e < kP * kP; e += 256) out[e] = Q[e / kP][e % kP];
