@@ -187,8 +187,11 @@ def bench_config(pkg, world, P, NL, n_apps, app_dist, pods, n_res_rank0):
     return {"workload": workload_name(world, P, NL), "pods": P, "nodes_per_rank": NL, "gpus_per_node": GPUS_PER_NODE,
             "apps": n_apps, "app_distribution": app_dist, "residents_rank0": n_res_rank0,
             "distinct_app_slo_classes": pkg.synth.distinct_classes(pods), "seed": hex(pkg.synth.SEED),
-            "l2": "flushed between timed iterations (256 MB memset, untimed); outputs 500 MB > L2",
-            "timing": "CUDA events per step on the launching stream, summed; max over ranks"}
+            "l2": ("flushed between timed iterations (256 MB memset, untimed); outputs 500 MB > L2" if world == 1 else
+                   "no flush: every step writes 500 MB of results per rank, four times the L2"),
+            "timing": ("CUDA events per step on the launching stream, summed" if world == 1 else
+                       "CUDA events around the K steps; step k's exchange (all-reduce + NormalizeScore, second stream) "
+                       "overlaps step k+1's scoring; max over ranks")}
 
 
 def run_reference(args, rank, world):
@@ -315,18 +318,52 @@ def main():
     barrier()
 
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    pipelined = world > 1
+    if pipelined:
+        # N > 1: the exchange of step k (all-reduce of the extrema + NormalizeScore) runs on a second stream
+        # and overlaps the scoring of step k + 1 (two result-buffer sets) — a serving loop; no L2 flush inside
+        # (each step writes 500 MB of results, four times the L2)
+        sets = [(d_score, d_sel, d_ext, d_best),
+                (torch.empty_like(d_score), torch.empty_like(d_sel), torch.zeros_like(d_ext), torch.empty_like(d_best))]
+        xchg_stream = torch.cuda.Stream(device=dev)
+        ev_scored = [torch.cuda.Event() for _ in range(2)]
+        ev_done = [torch.cuda.Event() for _ in range(2)]
+
+        def run_pipelined(k_steps):
+            t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0.record(work_stream)
+            for k in range(k_steps):
+                sc, se, ex, be = sets[k % 2]
+                if k >= 2:
+                    work_stream.wait_event(ev_done[k % 2])     # the buffers of step k - 2 are free again
+                sch.score_raw_dev(d_app, d_slo, P, sc, se, ex[0], ex[1], stream=work_stream.cuda_stream)
+                ev_scored[k % 2].record(work_stream)
+                with torch.cuda.stream(xchg_stream):
+                    xchg_stream.wait_event(ev_scored[k % 2])
+                    dist.all_reduce(ex, op=dist.ReduceOp.MAX)
+                    sch.normalize_dev(P, sc, ex[0], ex[1], be, stream=xchg_stream.cuda_stream)
+                    ev_done[k % 2].record(xchg_stream)
+            xchg_stream.wait_stream(work_stream)
+            t1.record(xchg_stream)
+            return t0, t1
+
+        run_pipelined(2)
+        torch.cuda.synchronize()
     with ClockSampler(local_rank) as clocks:
         barrier()
         launches0 = pkg.launch_count()
         t_wall0 = time.perf_counter()
-        for a, b in ev:
-            flush.zero_()          # evict L2 between timed iterations (not timed)
-            a.record()
-            step()
-            b.record()
+        if pipelined:
+            t0, t1 = run_pipelined(args.steps)
+        else:
+            for a, b in ev:
+                flush.zero_()          # evict L2 between timed iterations (not timed)
+                a.record()
+                step()
+                b.record()
         barrier()
         t_wall = time.perf_counter() - t_wall0
-    step_ms = [a.elapsed_time(b) for a, b in ev]
+    step_ms = [t0.elapsed_time(t1)] if pipelined else [a.elapsed_time(b) for a, b in ev]
     launches = pkg.launch_count() - launches0
     # dominant-kernel duration, live, from the library's own event bracket on the same stream
     kms, ams = [], []
@@ -442,6 +479,48 @@ def main():
                    "d2h_bytes_per_step": 2 * P * NL + 4 * P, "ms_per_step": dt * 1e3,
                    "api": "gs_score_raw_dev + all_reduce(MAX) + gs_normalize_dev with pinned host copies, per rank"}
 
+    # ---- e2e, decisions only: host pods in, 8 bytes per pod out (node, selected GPU there, extrema, MPS choice)
+    e2e_dec = None
+    if not args.no_e2e:
+        h_dec = torch.empty((P, 8), dtype=torch.uint8).pin_memory()
+        if world == 1:
+            dec_out = h_dec.numpy().view(sch.DECISION_DTYPE).reshape(P)
+            for _ in range(2):
+                sch.score_decisions(hp, out=dec_out)
+            n_e2e = max(3, min(args.steps, 10))
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(n_e2e):
+                sch.score_decisions(hp, out=dec_out)
+            barrier()
+            dt = (time.perf_counter() - t0) / n_e2e
+            api = "gs_score_decisions (host pods in, 8-byte decisions out)"
+        else:
+            d_dec = torch.empty((P, 8), dtype=torch.uint8, device=dev)
+
+            def dec_step():
+                st = torch.cuda.current_stream().cuda_stream
+                d_app.copy_(h_app, non_blocking=True)
+                d_slo.copy_(h_slo, non_blocking=True)
+                sch.score_raw_dev(d_app, d_slo, P, d_score, d_sel, d_ext[0], d_ext[1], stream=st)
+                dist.all_reduce(d_ext, op=dist.ReduceOp.MAX)
+                sch.decisions_dev(d_app, d_slo, P, d_sel, d_ext[0], d_ext[1], d_dec, stream=st)
+                h_dec.copy_(d_dec, non_blocking=True)
+                torch.cuda.synchronize()
+            dec_step()
+            n_e2e = max(3, min(args.steps, 10))
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(n_e2e):
+                dec_step()
+            barrier()
+            dtt = torch.tensor([(time.perf_counter() - t0) / n_e2e], dtype=torch.float64, device=dev)
+            dist.all_reduce(dtt, op=dist.ReduceOp.MAX)
+            dt = float(dtt.item())
+            api = "gs_score_raw_dev + all_reduce(MAX) + gs_decisions_dev with pinned host copies, per rank"
+        e2e_dec = {"value": evals_per_step / dt, "unit": UNIT, "h2d_bytes_per_step": 8 * P, "d2h_bytes_per_step": 8 * P,
+                   "ms_per_step": dt * 1e3, "api": api}
+
     if rank == 0:
         peak, peak_kind = measured_peak_gbs()
         kernel_ms = float(np.median(kms))
@@ -473,6 +552,8 @@ def main():
             line["extras"] = extras
         if e2e:
             line["e2e"] = e2e
+        if e2e_dec:
+            line["e2e_decisions"] = e2e_dec
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"], _ = cpu_reference_leg(preds, cluster, pods)
         print(json.dumps(line), flush=True)

@@ -33,7 +33,7 @@ EXPORTS = [
     "gs_score_batch", "gs_score_decisions", "gs_decisions_dev", "gs_best_dev", "gs_create_multi", "gs_destroy_multi",
     "gs_multi_last_error", "gs_multi_device_count", "gs_mupload_predictions", "gs_mupload_cluster", "gs_mscore_batch",
     "gs_mscore_decisions", "gs_score_raw_dev", "gs_score_raw_dev_noalloc", "gs_normalize_dev", "gs_normalize_scores", "gs_select_mig",
-    "gs_set_profiling", "gs_last_score_kernel_ms", "gs_last_stage_a_ms", "gs_selftest", "gs_selftest_filter", "gs_launch_count", "gs_complete_fit", "gs_complete_fit_sharded", "gs_complete_fit_transform", "gs_complete_transform", "gs_model_info", "gs_model_step", "gs_model_destroy",
+    "gs_set_profiling", "gs_last_score_kernel_ms", "gs_last_stage_a_ms", "gs_selftest", "gs_selftest_filter", "gs_launch_count", "gs_complete_fit", "gs_complete_fit_sharded", "gs_complete_fit_transform", "gs_complete_transform", "gs_model_info", "gs_model_step", "gs_model_destroy", "gs_eig_stats",
 ]
 
 
@@ -113,8 +113,16 @@ def load_library():
     L.gs_model_step.argtypes = [vp, i32, C.POINTER(i32), vp, C.POINTER(C.c_double)]
     L.gs_model_destroy.argtypes = [vp]
     L.gs_model_destroy.restype = None
+    L.gs_eig_stats.argtypes = [C.POINTER(C.c_uint64)]
+    L.gs_eig_stats.restype = C.c_uint64
     _lib = L
     return L
+
+
+def eig_stats():
+    """(decompositions, sweeps) the block Jacobi eigensolver has run so far in this process."""
+    sw = C.c_uint64(0)
+    return int(load_library().gs_eig_stats(C.byref(sw))), int(sw.value)
 
 
 def launch_count() -> int:
@@ -228,6 +236,11 @@ class Scheduler:
         library's fixed device array (no allocation); refuses batches beyond GS_NOALLOC_MAX_*."""
         self._check(self._L.gs_score_raw_dev_noalloc(self._h, _ptr(d_app), _ptr(d_slo), int(n_pods), _ptr(d_score),
                                                      _ptr(d_sel), _ptr(d_hi_arg), _ptr(d_neg_lo), _ptr(stream)))
+
+    def decisions_dev(self, d_app, d_slo, n_pods, d_sel, d_hi_arg, d_neg_lo, d_out, stream=None):
+        """gs_decisions_dev: 8-byte decisions from the selection matrix and the (global) extrema."""
+        self._check(self._L.gs_decisions_dev(self._h, _ptr(d_app), _ptr(d_slo), int(n_pods), _ptr(d_sel), _ptr(d_hi_arg),
+                                             _ptr(d_neg_lo), _ptr(d_out), _ptr(stream)))
 
     def normalize_dev(self, n_pods, d_score, d_hi_arg, d_neg_lo, d_best=None, stream=None):
         self._check(self._L.gs_normalize_dev(self._h, int(n_pods), _ptr(d_score), _ptr(d_hi_arg), _ptr(d_neg_lo),

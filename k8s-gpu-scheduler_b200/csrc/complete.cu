@@ -1035,6 +1035,13 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
   return GS_OK;
 }
 
+uint64_t gs_eig_stats(uint64_t* out_sweeps) {
+  unsigned long long f = 0, s = 0;
+  gs::eig_stats(&f, &s);
+  if (out_sweeps) *out_sweeps = s;
+  return f;
+}
+
 int gs_complete_transform(gs_ctx* c, const gs_model* m, const double* X, int32_t rows, double* out) {
   using namespace gs;
   if (!c) return GS_ERR_INVALID;

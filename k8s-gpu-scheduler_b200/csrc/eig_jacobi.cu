@@ -16,7 +16,9 @@
 //     bj_cols_kernel   A <- A Q and V <- V Q on the pair's 32 columns.
 //   Sweeps repeat until off(A)^2 <= 1e-30 ||A||^2 (or the off-norm stagnates on the rounding floor),
 //   the same stopping rule as the one-CTA kernel.  Padding rows/columns are zero and never rotate.
+#include <atomic>
 #include <cstdint>
+#include <cstdlib>
 #include <cuda_runtime.h>
 
 #include "eig_jacobi.h"
@@ -24,9 +26,15 @@
 
 namespace gs {
 
+static std::atomic<unsigned long long> g_eig_fits{0}, g_eig_sweeps{0};
+void eig_stats(unsigned long long* fits, unsigned long long* sweeps) {
+  *fits = g_eig_fits.load();
+  *sweeps = g_eig_sweeps.load();
+}
+
 constexpr int kB = 16;       // block size
 constexpr int kP = 2 * kB;   // pivot size
-constexpr int kInnerSweeps = 3;
+constexpr int kInnerSweeps = 1;  // default; GS_EIG_INNER overrides (measurement)
 
 __host__ __device__ inline void bj_pair(int nb, int step, int p, int* I, int* J) {
   int a, b;
@@ -82,7 +90,7 @@ __global__ void __launch_bounds__(256) bj_norm_kernel(const double* __restrict__
 
 // One CTA per block pair: diagonalise the 32 x 32 pivot, write the accumulated rotation Q.
 __global__ void __launch_bounds__(256) bj_pivot_kernel(const double* __restrict__ A, int mp, int nb, int step,
-                                                      double* __restrict__ Qout) {
+                                                      double* __restrict__ Qout, int inner_sweeps) {
   __shared__ double S[kP][kP + 1], Q[kP][kP + 1];
   __shared__ double s_c[kB], s_s[kB];
   __shared__ int s_p[kB], s_q[kB];
@@ -99,7 +107,7 @@ __global__ void __launch_bounds__(256) bj_pivot_kernel(const double* __restrict_
   // a few cyclic sweeps: the pivot need not be diagonalised exactly for the block iteration to
   // converge, and every barrier here is latency on the critical path of the step.  A sweep in which
   // no rotation passes the threshold ends the loop.
-  for (int sweep = 0; sweep < kInnerSweeps; ++sweep) {
+  for (int sweep = 0; sweep < inner_sweeps; ++sweep) {
     bool rotated = false;
     for (int st = 0; st < kP - 1; ++st) {
       if (tid < kB) {
@@ -258,6 +266,11 @@ cudaError_t eig_block_jacobi(const double* G, int d, int j, double* work, double
   const size_t n2 = (size_t)mp * mp;
   note_launch();
   bj_init_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, s>>>(G, d, j, mp, A, V);
+  static const int inner = [] {
+    const char* v = getenv("GS_EIG_INNER");
+    const int k = v ? atoi(v) : kInnerSweeps;
+    return k < 1 ? 1 : (k > 16 ? 16 : k);
+  }();
   double prev_off = -1.0;
   int sweep = 0;
   for (; sweep < 40; ++sweep) {
@@ -274,7 +287,7 @@ cudaError_t eig_block_jacobi(const double* G, int d, int j, double* work, double
     prev_off = h[0];
     for (int step = 0; step < nb - 1; ++step) {
       note_launch();
-      bj_pivot_kernel<<<nb / 2, 256, 0, s>>>(A, mp, nb, step, Q);
+      bj_pivot_kernel<<<nb / 2, 256, 0, s>>>(A, mp, nb, step, Q, inner);
       note_launch();
       bj_rows_kernel<<<dim3(nb / 2, (mp + 127) / 128), 256, 0, s>>>(A, mp, nb, step, Q);
       note_launch();
@@ -284,6 +297,8 @@ cudaError_t eig_block_jacobi(const double* G, int d, int j, double* work, double
   note_launch();
   bj_diag_kernel<<<(m + 255) / 256, 256, 0, s>>>(A, mp, m, evals);
   if (sweeps_out) *sweeps_out = sweep;
+  g_eig_fits.fetch_add(1, std::memory_order_relaxed);
+  g_eig_sweeps.fetch_add((unsigned long long)sweep, std::memory_order_relaxed);
   return cudaGetLastError();
 }
 

@@ -8,4 +8,5 @@ int eig_padded_size(int m);        // mp: row stride of the work matrices for an
 size_t eig_work_doubles(int m);    // doubles of work space: A (mp*mp), V (mp*mp), rotations, norms
 cudaError_t eig_block_jacobi(const double* G, int d, int j, double* work, double* evals, int* sweeps_host,
                              cudaStream_t s);
+void eig_stats(unsigned long long* fits, unsigned long long* sweeps);  // decompositions and sweeps so far (process-wide)
 }  // namespace gs

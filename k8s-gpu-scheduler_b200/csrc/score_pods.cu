@@ -86,7 +86,11 @@ __global__ void __launch_bounds__(256) stage_fold_kernel(DevTables T, const uint
     // a GPU the node does not have: estimate 0.5 on both sides — score 0, never near an integer
     float4 ab = make_float4(0.5f, 0.f, 0.5f, 0.f);
     uint32_t pk = 0u;
-    if (model != kModelNone) {
+    if (model != kModelNone && s_lo[sl] == s_hi[sl]) {
+      // a GPU without residents (warp-uniform): the fold of empty sums — tmp = 0 + 100*((1*(0+v))/1) on
+      // either side, nothing without a candidate
+      ab = make_float4(0.f, 100.f, 0.f, 100.f);
+    } else if (model != kModelNone) {
       const float* itab = T.interf + (size_t)(model - 1) * A * A + app_idx;
       const float* itab_t = T.interf_t + (size_t)(model - 1) * A * A + app_idx;
       const uint32_t lo = s_lo[sl], hi = s_hi[sl];

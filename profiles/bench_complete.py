@@ -38,14 +38,17 @@ def main():
     for spec in args.sizes.split(","):
         n, d = map(int, spec.split("x"))
         X, truth = synthetic(n, d, max(2, d // 8), 0.30, 5, return_truth=True)
+        e0 = pkg.eig_stats()
         t0 = time.perf_counter()
         m = pkg.complete_fit(sch, X)
         t_fit = time.perf_counter() - t0
+        e1 = pkg.eig_stats()
         t0 = time.perf_counter()
         out = m.transform(X)
         t_tr = time.perf_counter() - t0
         rec = {"n": n, "d": d, "missing": int(np.isnan(X).sum()), "gpu_fit_s": t_fit, "gpu_transform_s": t_tr,
-               "rounds": m.n_rounds, "steps": m.n_steps,
+               "rounds": m.n_rounds, "steps": m.n_steps, "ms_per_fit": 1e3 * t_fit / max(1, m.n_steps),
+               "eig_sweeps_per_fit": (e1[1] - e0[1]) / max(1, e1[0] - e0[0]),
                # sanity at sizes no CPU reference reaches: the data are low rank + N(0, 0.01^2) noise, so a
                # correct completion recovers the hidden entries to about the noise level
                "rmse_hidden_vs_truth": float(np.sqrt(np.mean((out - truth)[np.isnan(X)] ** 2))),
