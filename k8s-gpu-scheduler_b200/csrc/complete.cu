@@ -848,6 +848,19 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
   double* dEigWork = nullptr;
   const int eig_mp = use_block ? eig_padded_size(mm) : 0;
   std::vector<int> block_sweeps;
+  // warm start: keep every feature's eigenvectors for the next round (the Gram matrix of a feature
+  // changes little from one round to the next), if d * mp^2 doubles fit the budget (GS_EIG_WARM_GB, default 24)
+  double* dVstore = nullptr;
+  std::vector<char> have_v((size_t)d, 0);
+  if (use_block) {
+    size_t warm_gb = 24;
+    if (const char* v = getenv("GS_EIG_WARM_GB")) warm_gb = (size_t)strtoull(v, nullptr, 10);
+    const size_t per = (size_t)eig_mp * eig_mp;
+    if (per * (size_t)d * sizeof(double) <= (warm_gb << 30) && mem.alloc(&dVstore, per * (size_t)d) != cudaSuccess) {
+      cudaGetLastError();
+      dVstore = nullptr;  // no room: every decomposition starts cold
+    }
+  }
   if (use_block) {
     CK(mem.alloc(&dEigWork, eig_work_doubles(mm)));
     CK(cudaMemsetAsync(dSweeps, 0, sizeof(int) * max_steps, s));
@@ -964,7 +977,9 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
       }
       if (use_block) {
         int sw = 0;
-        const cudaError_t ee = eig_block_jacobi(dG, d, j, dEigWork, dEv, &sw, s);
+        double* vj = dVstore ? dVstore + (size_t)j * eig_mp * eig_mp : nullptr;
+        const cudaError_t ee = eig_block_jacobi(dG, d, j, dEigWork, dEv, &sw, s, (vj && have_v[j]) ? vj : nullptr, vj);
+        if (vj) have_v[j] = 1;
         if (ee != cudaSuccess) return c->cuda_fail(ee, "completion: block Jacobi eigensolver");
         block_sweeps.push_back(sw);
         // eigenvectors in the columns of V = work + mp*mp, row stride mp

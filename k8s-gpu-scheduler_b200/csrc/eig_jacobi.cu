@@ -241,6 +241,60 @@ __global__ void bj_diag_kernel(const double* __restrict__ A, int mp, int m, doub
   if (k < m) evals[k] = fmax(A[(size_t)k * mp + k], 0.0);  // S^2 >= 0
 }
 
+// C[i][j] = sum_k X[k][i] * Y[k][j]  (X^T Y; all n x n row-major).  64 x 64 tile per CTA, 4 x 4 per thread.
+// For the warm start: T = G V0 (G symmetric, so G V0 = G^T V0) and A = V0^T T.
+__global__ void __launch_bounds__(256) bj_gemm_tn_kernel(const double* __restrict__ X, const double* __restrict__ Y,
+                                                        double* __restrict__ C, int n) {
+  __shared__ double Xs[16][64 + 4], Ys[16][64 + 4];
+  const int i0 = blockIdx.y * 64, j0 = blockIdx.x * 64;
+  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+  double acc[4][4];
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+  for (int k0 = 0; k0 < n; k0 += 16) {
+    for (int e = threadIdx.x; e < 16 * 64; e += 256) {
+      const int kk = e >> 6, c = e & 63;
+      Xs[kk][c] = (k0 + kk < n && i0 + c < n) ? X[(size_t)(k0 + kk) * n + i0 + c] : 0.0;
+      Ys[kk][c] = (k0 + kk < n && j0 + c < n) ? Y[(size_t)(k0 + kk) * n + j0 + c] : 0.0;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < 16; ++kk) {
+      double xa[4], yb[4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a) xa[a] = Xs[kk][4 * ty + a];
+#pragma unroll
+      for (int b = 0; b < 4; ++b) yb[b] = Ys[kk][4 * tx + b];
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] += xa[a] * yb[b];
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const int i = i0 + 4 * ty + a, j = j0 + 4 * tx + b;
+      if (i < n && j < n) C[(size_t)i * n + j] = acc[a][b];
+    }
+}
+
+// A <- (A + A^T) / 2: V0^T (G V0) is symmetric only up to rounding
+__global__ void bj_symmetrise_kernel(double* __restrict__ A, int n) {
+  const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= (size_t)n * n) return;
+  const int i = (int)(e / n), j = (int)(e % n);
+  if (i < j) {
+    const double v = 0.5 * (A[(size_t)i * n + j] + A[(size_t)j * n + i]);
+    A[(size_t)i * n + j] = v;
+    A[(size_t)j * n + i] = v;
+  }
+}
+
 int eig_padded_size(int m) {
   int nb = (m + kB - 1) / kB;
   if (nb & 1) ++nb;
@@ -250,22 +304,36 @@ int eig_padded_size(int m) {
 
 size_t eig_work_doubles(int m) {
   const size_t mp = (size_t)eig_padded_size(m);
-  return 2 * mp * mp + (mp / kP) * kP * kP + 8;
+  return 3 * mp * mp + (mp / kP) * kP * kP + 8;
 }
 
 // Eigendecomposition of G (d x d) without row/column j: evals[m], eigenvectors in the columns of
 // V = work + mp*mp (row-major, row stride mp).  Synchronises the stream once per sweep (the stopping
 // rule is evaluated on the host).  *sweeps_out (host memory) = sweeps run.
 cudaError_t eig_block_jacobi(const double* G, int d, int j, double* work, double* evals, int* sweeps_out,
-                             cudaStream_t s) {
+                             cudaStream_t s, const double* V0, double* Vsave) {
   const int m = d - 1, mp = eig_padded_size(m), nb = mp / kB;
   double* A = work;
   double* V = work + (size_t)mp * mp;
-  double* Q = V + (size_t)mp * mp;
+  double* Tm = V + (size_t)mp * mp;
+  double* Q = Tm + (size_t)mp * mp;
   double* norms = Q + (size_t)(nb / 2) * kP * kP;
   const size_t n2 = (size_t)mp * mp;
   note_launch();
-  bj_init_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, s>>>(G, d, j, mp, A, V);
+  bj_init_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, s>>>(G, d, j, mp, A, V0 ? nullptr : V);
+  if (V0) {
+    // warm start from an earlier decomposition of (nearly) the same matrix: iterate on V0^T G V0, which
+    // is close to diagonal, and accumulate the rotations onto V0
+    const dim3 gg((mp + 63) / 64, (mp + 63) / 64);
+    note_launch();
+    bj_gemm_tn_kernel<<<gg, 256, 0, s>>>(A, V0, Tm, mp);   // Tm = G V0
+    note_launch();
+    bj_gemm_tn_kernel<<<gg, 256, 0, s>>>(V0, Tm, A, mp);   // A = V0^T Tm
+    note_launch();
+    bj_symmetrise_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, s>>>(A, mp);
+    cudaError_t e = cudaMemcpyAsync(V, V0, sizeof(double) * n2, cudaMemcpyDeviceToDevice, s);
+    if (e != cudaSuccess) return e;
+  }
   static const int inner = [] {
     const char* v = getenv("GS_EIG_INNER");
     const int k = v ? atoi(v) : kInnerSweeps;
@@ -296,6 +364,10 @@ cudaError_t eig_block_jacobi(const double* G, int d, int j, double* work, double
   }
   note_launch();
   bj_diag_kernel<<<(m + 255) / 256, 256, 0, s>>>(A, mp, m, evals);
+  if (Vsave) {
+    cudaError_t e = cudaMemcpyAsync(Vsave, V, sizeof(double) * n2, cudaMemcpyDeviceToDevice, s);
+    if (e != cudaSuccess) return e;
+  }
   if (sweeps_out) *sweeps_out = sweep;
   g_eig_fits.fetch_add(1, std::memory_order_relaxed);
   g_eig_sweeps.fetch_add((unsigned long long)sweep, std::memory_order_relaxed);
