@@ -148,6 +148,16 @@ GS_API const char* gs_version(void);
  * overwrites tables that an asynchronous gs_score_raw_dev is still reading. */
 GS_API int gs_upload_cluster(gs_ctx* ctx, const gs_cluster* cluster, int32_t node_base);
 
+/* Replace ONE node's GPU list and residents in the uploaded snapshot (node = index within this context's
+ * nodes): what a bind, a pod deletion or a profiler refresh changes.  gpu_counts[g] residents on GPU g
+ * (g < n_gpus, in Redis array order), their app ids and SLOs concatenated in res_app / res_slo.  The
+ * reference re-reads Redis and re-scans all pods on every Score (gpu_plugins.go:529-549, 87-160); here
+ * only this node's part of the tables (and what lies behind it in the arrays) is copied again.  Resident
+ * indices used by pod_self shift as they would in a rebuilt snapshot.  The node's model cannot change
+ * (it derives from the node's name). */
+GS_API int gs_update_node(gs_ctx* ctx, int32_t node, int32_t n_gpus, const uint32_t* gpu_counts,
+                          const uint32_t* res_app, const float* res_slo);
+
 /* Upload the completed prediction tables.  Replaces gpu_plugins.go:302-355 and the
  * serving side pkg/recommender/recom_server.py:138-204. */
 GS_API int gs_upload_predictions(gs_ctx* ctx, const gs_predictions* preds);

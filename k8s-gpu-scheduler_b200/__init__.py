@@ -29,7 +29,7 @@ ERR_NAMES = {-1: "GS_ERR_INVALID", -2: "GS_ERR_CUDA", -3: "GS_ERR_STATE", -4: "G
 
 # every symbol include/gpusched.h declares
 EXPORTS = [
-    "gs_create", "gs_destroy", "gs_last_error", "gs_version", "gs_upload_cluster", "gs_upload_predictions",
+    "gs_create", "gs_destroy", "gs_last_error", "gs_version", "gs_upload_cluster", "gs_update_node", "gs_upload_predictions",
     "gs_score_batch", "gs_score_decisions", "gs_decisions_dev", "gs_best_dev", "gs_create_multi", "gs_destroy_multi",
     "gs_multi_last_error", "gs_multi_device_count", "gs_mupload_predictions", "gs_mupload_cluster", "gs_mscore_batch",
     "gs_mscore_decisions", "gs_score_raw_dev", "gs_score_raw_dev_noalloc", "gs_normalize_dev", "gs_normalize_scores", "gs_select_mig",
@@ -80,6 +80,7 @@ def load_library():
     L.gs_launch_count.restype = C.c_uint64
     L.gs_upload_cluster.argtypes = [vp, C.POINTER(_GsCluster), i32]
     L.gs_upload_predictions.argtypes = [vp, C.POINTER(_GsPredictions)]
+    L.gs_update_node.argtypes = [vp, i32, i32, vp, vp, vp]
     L.gs_score_batch.argtypes = [vp, vp, vp, vp, i32, u32, vp, vp, vp]
     L.gs_score_decisions.argtypes = [vp, vp, vp, vp, i32, u32, vp]
     L.gs_decisions_dev.argtypes = [vp, vp, vp, i32, vp, vp, vp, vp, vp]
@@ -179,6 +180,13 @@ class Scheduler:
         self._check(self._L.gs_upload_cluster(self._h, C.byref(s), int(node_base)))
         self.n_nodes = int(keep[0].shape[0])
         self.n_res = int(keep[3].shape[0])
+
+    def update_node(self, node: int, gpu_counts, res_app, res_slo):
+        """gs_update_node: replace one node's GPU list and residents in place."""
+        counts = np.ascontiguousarray(gpu_counts, dtype=np.uint32)
+        app = np.ascontiguousarray(res_app, dtype=np.uint32)
+        slo = np.ascontiguousarray(res_slo, dtype=np.float32)
+        self._check(self._L.gs_update_node(self._h, int(node), int(counts.shape[0]), _ptr(counts), _ptr(app), _ptr(slo)))
 
     def upload_predictions(self, pr: Predictions):
         conf = np.ascontiguousarray(pr.conf, dtype=np.float32)

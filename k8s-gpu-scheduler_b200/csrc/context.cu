@@ -321,6 +321,72 @@ int gs_upload_cluster(gs_ctx* c, const gs_cluster* cl, int32_t node_base) {
   c->node_base = node_base;
   c->have_cluster = true;
   c->prep_dirty = true;
+  c->h_model.assign(p_model.begin(), p_model.begin() + N);
+  c->h_ngpu.assign(p_ngpu.begin(), p_ngpu.begin() + N);
+  c->h_off = p_off;
+  c->h_app.assign(p_app.begin(), p_app.begin() + R);
+  c->h_slo.assign(p_slo.begin(), p_slo.begin() + R);
+  return GS_OK;
+}
+
+int gs_update_node(gs_ctx* c, int32_t node, int32_t n_gpus, const uint32_t* gpu_counts, const uint32_t* res_app,
+                   const float* res_slo) {
+  if (!c) return GS_ERR_INVALID;
+  GS_LOCK(c);
+  if (!c->have_cluster) return c->fail(GS_ERR_STATE, "gs_update_node before gs_upload_cluster");
+  const size_t G = (size_t)c->max_gpus, N = (size_t)c->n_nodes;
+  if (node < 0 || (size_t)node >= N || n_gpus < 0 || n_gpus > c->max_gpus || (n_gpus && !gpu_counts))
+    return c->fail(GS_ERR_INVALID, "gs_update_node: node %d or GPU count %d out of range (%zu nodes, max_gpus %d)", node,
+                   n_gpus, N, c->max_gpus);
+  size_t n_new = 0;
+  for (int g = 0; g < n_gpus; ++g) {
+    if (gpu_counts[g] > (uint32_t)gs::kMaxResidentsPerSlot)
+      return c->fail(GS_ERR_INVALID, "gs_update_node: GPU %d holds %u residents; at most %d", g, gpu_counts[g],
+                     gs::kMaxResidentsPerSlot);
+    n_new += gpu_counts[g];
+  }
+  if (n_new && (!res_app || !res_slo)) return c->fail(GS_ERR_INVALID, "gs_update_node: null resident table");
+  GS_CUDA(c, cudaSetDevice(c->device));
+  if (int rcw = c->wait_last_use()) return rcw;
+  // splice the node's residents into the host mirror
+  const size_t s0 = (size_t)node * G;
+  const uint32_t lo = c->h_off[s0], hi = c->h_off[s0 + G];
+  const long long delta = (long long)n_new - (long long)(hi - lo);
+  c->h_app.erase(c->h_app.begin() + lo, c->h_app.begin() + hi);
+  c->h_slo.erase(c->h_slo.begin() + lo, c->h_slo.begin() + hi);
+  c->h_app.insert(c->h_app.begin() + lo, res_app, res_app + n_new);
+  c->h_slo.insert(c->h_slo.begin() + lo, res_slo, res_slo + n_new);
+  uint32_t w = lo;
+  for (size_t g = 0; g < G; ++g) {
+    w += g < (size_t)n_gpus ? gpu_counts[g] : 0u;
+    c->h_off[s0 + g + 1] = w;
+  }
+  for (size_t s = s0 + G + 1; s < c->h_off.size(); ++s) c->h_off[s] = (uint32_t)((long long)c->h_off[s] + delta);
+  c->h_ngpu[(size_t)node] = (uint8_t)n_gpus;
+  const size_t R = c->h_app.size();
+  // device: the node's GPU count, the offsets from this node on, the residents from this node on
+  int rc;
+  std::vector<uint32_t> ident(R ? R : 1);
+  for (size_t r = 0; r < R; ++r) ident[r] = (uint32_t)r;
+  if (sizeof(uint32_t) * R > c->res_app.cap || sizeof(float) * R > c->res_slo.cap || sizeof(uint32_t) * R > c->res_new.cap) {
+    // grew beyond the buffers: whole arrays (reserve reallocates)
+    if ((rc = c->upload(c->res_app, c->h_app.data(), sizeof(uint32_t) * R, "res_app"))) return rc;
+    if ((rc = c->upload(c->res_slo, c->h_slo.data(), sizeof(float) * R, "res_slo"))) return rc;
+    if ((rc = c->upload(c->res_new, ident.data(), sizeof(uint32_t) * R, "res_new"))) return rc;
+  } else if (R > lo) {
+    GS_CUDA(c, cudaMemcpyAsync((uint32_t*)c->res_app.p + lo, c->h_app.data() + lo, sizeof(uint32_t) * (R - lo),
+                               cudaMemcpyHostToDevice, c->stream));
+    GS_CUDA(c, cudaMemcpyAsync((float*)c->res_slo.p + lo, c->h_slo.data() + lo, sizeof(float) * (R - lo),
+                               cudaMemcpyHostToDevice, c->stream));
+    GS_CUDA(c, cudaMemcpyAsync((uint32_t*)c->res_new.p + lo, ident.data() + lo, sizeof(uint32_t) * (R - lo),
+                               cudaMemcpyHostToDevice, c->stream));
+  }
+  GS_CUDA(c, cudaMemcpyAsync((uint32_t*)c->gpu_off.p + s0, c->h_off.data() + s0, sizeof(uint32_t) * (c->h_off.size() - s0),
+                             cudaMemcpyHostToDevice, c->stream));
+  GS_CUDA(c, cudaMemcpyAsync((uint8_t*)c->node_ngpu.p + node, c->h_ngpu.data() + node, 1, cudaMemcpyHostToDevice, c->stream));
+  GS_CUDA(c, cudaStreamSynchronize(c->stream));
+  c->n_res = (int64_t)R;
+  c->prep_dirty = true;  // the per-resident records are rebuilt before the next scoring call
   return GS_OK;
 }
 

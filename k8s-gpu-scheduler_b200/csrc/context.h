@@ -3,6 +3,7 @@
 #include <cstdint>
 #include <mutex>
 #include <string>
+#include <vector>
 
 #include "tables.h"
 
@@ -24,6 +25,10 @@ struct Ctx {
   int n_nodes = 0, max_gpus = 1, redis_reachable = 1, node_base = 0;
   int64_t n_res = 0;
   DevBuf node_model, node_ngpu, gpu_off, res_app, res_slo, node_orig, res_new;
+  // host mirror of the snapshot, so that gs_update_node can splice one node's residents in
+  std::vector<uint8_t> h_model, h_ngpu;
+  std::vector<uint32_t> h_off, h_app;
+  std::vector<float> h_slo;
   // prediction tables
   bool have_preds = false;
   int n_apps = 0, n_cols = 0;

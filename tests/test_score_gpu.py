@@ -393,3 +393,38 @@ def test_best_only_and_thread_safety(pkg, sched, oracle_mod, synth):
     for t in threads:
         t.join(timeout=120)
     assert not errors, errors
+
+
+def test_update_node_equals_a_rebuilt_snapshot(sched, oracle_mod, synth):
+    """gs_update_node splices one node's GPUs/residents into the uploaded snapshot: after a series of
+    updates (grow, shrink, empty, fewer GPUs, first and last node) the scores equal those of the oracle
+    on the same cluster rebuilt from scratch."""
+    preds, cluster, pods = synth.make_workload(600, 90, gpus_per_node=8, n_apps=40)
+    sched.upload_predictions(preds)
+    sched.upload_cluster(cluster)
+    rng = np.random.default_rng(21)
+    G = 8
+    lists = [[(cluster.res_app[cluster.gpu_off[n * G + g]:cluster.gpu_off[n * G + g + 1]].copy(),
+               cluster.res_slo[cluster.gpu_off[n * G + g]:cluster.gpu_off[n * G + g + 1]].copy()) for g in range(G)]
+             for n in range(90)]
+    ngpu = cluster.node_ngpu.copy()
+    for node, k, fill in [(0, 8, 5), (89, 8, 0), (17, 3, 2), (17, 8, 9), (44, 0, 0), (45, 8, 1), (0, 1, 3), (60, 8, 40)]:
+        counts = rng.integers(0, fill + 1, size=k) if k else np.zeros(0, np.int64)
+        new = [(rng.integers(0, 40, size=int(c)).astype(np.uint32),
+                np.round(rng.uniform(10, 600, size=int(c)), 2).astype(np.float32)) for c in counts]
+        lists[node] = new + [(np.zeros(0, np.uint32), np.zeros(0, np.float32))] * (G - k)
+        ngpu[node] = k
+        sched.update_node(node, counts, np.concatenate([a for a, _ in new] + [np.zeros(0, np.uint32)]),
+                          np.concatenate([s for _, s in new] + [np.zeros(0, np.float32)]))
+        off = np.zeros(90 * G + 1, dtype=np.uint32)
+        off[1:] = np.cumsum([len(a) for n in range(90) for a, _ in lists[n]])
+        rebuilt = synth.Cluster(node_model=cluster.node_model, node_ngpu=ngpu.copy(), gpu_off=off,
+                                res_app=np.concatenate([a for n in range(90) for a, _ in lists[n]]).astype(np.uint32),
+                                res_slo=np.concatenate([s for n in range(90) for _, s in lists[n]]).astype(np.float32),
+                                max_gpus=G)
+        want = oracle_mod.Oracle(preds, rebuilt).score_batch(pods, normalize=True)
+        for kw in (dict(), dict(direct=True)):
+            got = sched.score_batch(pods, normalize=True, **kw)
+            assert all(np.array_equal(a, b) for a, b in zip(want, got)), f"after updating node {node} ({kw})"
+    with pytest.raises(Exception):
+        sched.update_node(90, [1], [0], [10.0])
