@@ -221,6 +221,45 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def completion_leg(pkg, sch, rank, world, n=5000, d=128, rank_k=16):
+    """Recommender completion proxy: Imputer.fit on n x d (rows sharded over the ranks at N > 1, per-feature
+    moments all-reduced through the library's callback), achieved vs the hidden ground truth, and the
+    200 x 12 golden of the reference's Imputer refitted here."""
+    rng = np.random.default_rng(5)
+    X = rng.normal(size=(n, rank_k)) @ rng.normal(size=(rank_k, d)) + rng.normal(scale=0.01, size=(n, d))
+    truth = X.copy()
+    mask = rng.random((n, d)) < 0.30
+    mask[rng.integers(0, n, size=d), np.arange(d)] = False
+    X[mask] = np.nan
+    lo, hi = rank * n // world, (rank + 1) * n // world
+    e0 = pkg.eig_stats()
+    t0 = time.perf_counter()
+    if world > 1:
+        m = pkg.complete_fit_sharded(sch, X[lo:hi], pkg.torch_allreduce())
+    else:
+        m = pkg.complete_fit(sch, X)
+    fit_s = time.perf_counter() - t0
+    e1 = pkg.eig_stats()
+    out = m.transform(X[lo:hi])
+    hid = mask[lo:hi]
+    rmse = float(np.sqrt(np.mean((out[hid] - truth[lo:hi][hid]) ** 2))) if hid.any() else 0.0
+    res = {"table": f"{n}x{d}, rank {rank_k} + N(0, 0.01^2) noise, 30 % missing", "rows_per_rank": hi - lo, "fit_s": fit_s,
+           "rounds": m.n_rounds, "estimator_fits": m.n_steps, "ms_per_fit": 1e3 * fit_s / max(1, m.n_steps),
+           "eig_sweeps_per_fit": (e1[1] - e0[1]) / max(1, e1[0] - e0[0]), "rmse_hidden_vs_truth": rmse,
+           "eigensolver": "block Jacobi across CTAs, warm-started from the previous round (csrc/eig_jacobi.cu)"}
+    m.close()
+    gpath = os.path.join(ROOT, "tests", "golden", "impute_synth_200x12.npz")
+    if os.path.exists(gpath):
+        g = np.load(gpath)
+        m2 = pkg.complete_fit(sch, g["X"])
+        got, want = m2.transform(g["X"]), g["completed"]
+        floor = 1e-2 * float(np.mean(np.abs(want)))
+        res["golden_max_rel_err"] = float(np.max(np.abs(got - want) / np.maximum(np.abs(want), floor)))
+        res["golden"] = "tests/golden/impute_synth_200x12.npz (reference Imputer, scikit-learn " + str(g["sklearn_version"]) + ")"
+        m2.close()
+    return res
+
+
 def parity_check(pkg, preds, cluster_all, pods, rank, NL, d_score, d_sel, d_best, n_check=64):
     """Untimed: n_check pods of this rank's node shard against the CPU oracle over the WHOLE cluster
     (global NormalizeScore extrema, global best node) — bit for bit."""
@@ -429,6 +468,53 @@ def main():
         r2 = timed(dd_app, dd_slo, pkg.SCORE_NO_DEDUPE)
         extras["discrete_slo"]["ms_per_step_without_dedupe"] = r2["ms_per_step"]
 
+    # ---- completion (BASELINE configs[2] in miniature): fit of a rank-16 + noise table with 30 % missing
+    # entries, and a small table against its committed golden (the reference's own Imputer) in the same run
+    completion = None
+    if not args.no_extras:
+        completion = completion_leg(pkg, sch, rank, world)
+
+    # ---- BASELINE configs[3] at N = 8: 1M pending pods x 20k nodes, 2 500 nodes per rank
+    config4 = None
+    if world == 8 and not args.no_extras:
+        P4, NL4 = 1_000_000, 2_500
+        cl4_all = pkg.synth.make_cluster(NL4 * world, n_apps, GPUS_PER_NODE, seed=pkg.synth.SEED + 4)
+        pods4 = pkg.synth.make_pods(P4, n_apps, seed=pkg.synth.SEED + 4)
+        s4 = pkg.Scheduler(local_rank)
+        s4.upload_predictions(preds)
+        s4.upload_cluster(cl4_all.shard(rank * NL4, (rank + 1) * NL4), node_base=rank * NL4)
+        a4 = torch.from_numpy(pods4.app.view(np.int32)).to(dev)
+        l4 = torch.from_numpy(pods4.slo).to(dev)
+        sc4 = torch.empty((P4, NL4), dtype=torch.uint8, device=dev)
+        se4 = torch.empty((P4, NL4), dtype=torch.uint8, device=dev)
+        ex4 = torch.zeros((2, P4), dtype=torch.int64, device=dev)
+        be4 = torch.empty(P4, dtype=torch.int32, device=dev)
+
+        def step4():
+            st = torch.cuda.current_stream().cuda_stream
+            s4.score_raw_dev(a4, l4, P4, sc4, se4, ex4[0], ex4[1], stream=st)
+            dist.all_reduce(ex4, op=dist.ReduceOp.MAX)
+            s4.normalize_dev(P4, sc4, ex4[0], ex4[1], be4, stream=st)
+
+        step4()
+        barrier()
+        t0e, t1e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0e.record()
+        for _ in range(3):
+            step4()
+        t1e.record()
+        barrier()
+        ms4 = torch.tensor([t0e.elapsed_time(t1e) / 3], dtype=torch.float64, device=dev)
+        dist.all_reduce(ms4, op=dist.ReduceOp.MAX)
+        ok4 = parity_check(pkg, preds, cl4_all, pods4, rank, NL4, sc4, se4, be4, n_check=8)
+        ok4_t = torch.tensor([1 if ok4 else 0], dtype=torch.int32, device=dev)
+        dist.all_reduce(ok4_t, op=dist.ReduceOp.MIN)
+        config4 = {"workload": f"{P4} pods x {NL4 * world} nodes x {GPUS_PER_NODE} GPUs/node, nodes sharded over {world} ranks",
+                   "ms_per_step": float(ms4.item()), "value": P4 * NL4 * world / (float(ms4.item()) * 1e-3), "unit": UNIT,
+                   "parity_ok": bool(int(ok4_t.item())), "distinct_app_slo_classes": pkg.synth.distinct_classes(pods4)}
+        del sc4, se4
+        s4.close()
+
     # ---- e2e: host buffers through gs_score_batch (pinned), copies inside the timed region
     e2e = None
     if not args.no_e2e:
@@ -550,6 +636,10 @@ def main():
         }
         if extras:
             line["extras"] = extras
+        if completion:
+            line["completion"] = completion
+        if config4:
+            line["config4"] = config4
         if e2e:
             line["e2e"] = e2e
         if e2e_dec:
