@@ -33,8 +33,7 @@ N_PODS, N_NODES, GPUS_PER_NODE, N_APPS = 50_000, 5_000, 8, 1024
 METRIC = "pod x node Filter+Score+NormalizeScore evals/sec (50k pods x 5k nodes x 8 GPUs/node per rank)"
 UNIT = "evals/s"
 # what the library's event bracket (gs_last_score_kernel_ms) spans
-BRACKET_KERNELS = ("score_pods_kernel + score_fast_kernel (the latter only for pods without an SLO / with a non-finite "
-                   "SLO); stage_a_kernel is bracketed separately (stage_a_ms)")
+BRACKET_KERNELS = "score_pods_kernel (stage_fold_kernel is bracketed separately: stage_a_ms)"
 
 
 def source_sha16():
