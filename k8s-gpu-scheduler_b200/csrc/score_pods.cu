@@ -394,9 +394,13 @@ __global__ void __launch_bounds__(32, GS_PODS_MIN_CTAS) score_pods_kernel(DevTab
     const uint32_t seg_end = kind == 0 ? e0 : (kind == 1 ? e1 : (kind == 2 ? e2 : cd.len));
     const int li = kind == kKindNoV100 ? 1 : 0;
 #pragma unroll 1
-    for (uint32_t base = seg0; base < seg_end; base += kPW) {  // a pass never mixes kinds
-    const bool valid = base + pi < seg_end;
-    const PodRec pr = pods[cd.start + (valid ? base + pi : base)];
+    // Pods without an SLO are few (after dedupe one per app): their passes take ONE pod x 32 nodes instead
+    // of 8 pods x 4 nodes, so that no lane idles; pk/qk/nwk are the lane's pod row, node lane and nodes per pass
+    const bool pod_major = kind == kKindInfInv;
+    const int pk = pod_major ? 0 : pi, qk = pod_major ? lane : q, nwk = pod_major ? 32 : kNW;
+    for (uint32_t base = seg0; base < seg_end; base += (pod_major ? 1 : kPW)) {  // a pass never mixes kinds
+    const bool valid = base + pk < seg_end;
+    const PodRec pr = pods[cd.start + (valid ? base + pk : base)];
     const uint32_t orig = pr.orig & kPodIndexMask;
     const float s = pr.slo, arinv = fabsf(pr.inv_slo);
     const float ncv = kind == kKindNoV100 ? -0.0f : -pr.conf_v100;  // that kind never evaluates a V100 node
@@ -478,9 +482,9 @@ __global__ void __launch_bounds__(32, GS_PODS_MIN_CTAS) score_pods_kernel(DevTab
       // 1/SLO is infinite: t = +-Inf * (slo - d), so the term is exactly 0 on either side (1/(1+Inf)), or
       // NaN when slo - d is 0 or NaN — int64(tmp) per (GPU, side) is the fold's z_neg / z_pos
 #pragma unroll 1
-      for (int it = 0; it < nL; it += kNW) {
-        if (it + q < nL && valid) {
-          const int n = sm->list[0][it + q];
+      for (int it = 0; it < nL; it += nwk) {
+        if (it + qk < nL && valid) {
+          const int n = sm->list[0][it + qk];
           const NodeHdr h = sm->hdr[n];
           const bool is_v = (h.flags & kHdrV100) != 0u;
           const bool has_cand = !is_v || pr.conf_v100 != -1.0f;
@@ -503,8 +507,8 @@ __global__ void __launch_bounds__(32, GS_PODS_MIN_CTAS) score_pods_kernel(DevTab
               }
             }
           }
-          sm->stage_score[pi][n] = (uint8_t)score;
-          sm->stage_sel[pi][n] = (uint8_t)(sel | (h.flags & 0xFFu) | ((is_v && (pr.orig & kPodF6)) ? kFlagF6 : 0u) |
+          sm->stage_score[pk][n] = (uint8_t)score;
+          sm->stage_sel[pk][n] = (uint8_t)(sel | (h.flags & 0xFFu) | ((is_v && (pr.orig & kPodF6)) ? kFlagF6 : 0u) |
                                            (has_cand ? kFlagF7 : 0u));
           hi = max(hi, lane_key(score, (uint32_t)(node0 + n)));
           ng = max(ng, (uint32_t)(100 - score));
@@ -528,15 +532,22 @@ __global__ void __launch_bounds__(32, GS_PODS_MIN_CTAS) score_pods_kernel(DevTab
     // nodes whose sums fall outside the streamlined domain: op for op
     const int nG = (int)sm->n_glist[li];
 #pragma unroll 1
-    for (int it = 0; it < nG; it += kNW) {
-      if (it + q < nG && valid) {
-        const int n = sm->glist[li][it + q];
+    for (int it = 0; it < nG; it += nwk) {
+      if (it + qk < nG && valid) {
+        const int n = sm->glist[li][it + qk];
         unsigned selbyte;
         const int sc = logic_eval(T, app, s, -1, node0 + n, &selbyte);
-        sm->stage_score[pi][n] = (uint8_t)sc;
-        sm->stage_sel[pi][n] = (uint8_t)selbyte;
+        sm->stage_score[pk][n] = (uint8_t)sc;
+        sm->stage_sel[pk][n] = (uint8_t)selbyte;
         hi = max(hi, lane_key(sc, (uint32_t)(node0 + n)));
         ng = max(ng, (uint32_t)(100 - sc));
+      }
+    }
+    if (pod_major) {  // all 32 lanes hold nodes of the one pod
+#pragma unroll
+      for (int dd = 1; dd < 8; dd <<= 1) {
+        hi = max(hi, __shfl_xor_sync(0xFFFFFFFFu, hi, dd));
+        ng = max(ng, __shfl_xor_sync(0xFFFFFFFFu, ng, dd));
       }
     }
     // per-pod extrema: the four node lanes of a pod, plus the template nodes
@@ -546,13 +557,17 @@ __global__ void __launch_bounds__(32, GS_PODS_MIN_CTAS) score_pods_kernel(DevTab
     ng = max(ng, __shfl_xor_sync(0xFFFFFFFFu, ng, 16));
     hi = max(hi, sm->key_c[li]);
     ng = max(ng, sm->neg_c[li]);
-    if (q == 0 && valid) publish_extrema(hi, ng, T.node_base, orig, hi_arg, neg_lo);
+    if ((pod_major ? lane == 0 : q == 0) && valid) publish_extrema(hi, ng, T.node_base, orig, hi_arg, neg_lo);
     __syncwarp();
     // write the tile out: lane -> pod row lane >> 2, nodes [8 * (lane & 3), +8)
     {
       const int row = lane >> 2, c8 = (lane & 3) * 8;
-      const uint32_t orow = __shfl_sync(0xFFFFFFFFu, orig, row);       // lanes 0..7 hold the eight pods
-      const bool rvalid = __shfl_sync(0xFFFFFFFFu, (int)valid, row) != 0;
+      uint32_t orow = __shfl_sync(0xFFFFFFFFu, orig, row);             // lanes 0..7 hold the eight pods
+      bool rvalid = __shfl_sync(0xFFFFFFFFu, (int)valid, row) != 0;
+      if (pod_major) {                                                  // one pod: staging row 0 only
+        orow = orig;
+        rvalid = row == 0;
+      }
       if (rvalid && c8 < n_in) {
         const size_t o = (size_t)orow * N + (size_t)(node0 + c8);
         if (vec8) {
