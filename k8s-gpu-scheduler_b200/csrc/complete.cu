@@ -291,15 +291,17 @@ constexpr int kBT = 128, kBK = 16;
 
 // kList = false: rows 0..n-1, those where feature j is observed (j < 0: every row).
 // kList = true: the rows rows[0..n-1] (a list of row numbers), all of them.
-template <bool kList>
+template <bool kList, bool kMma>
 __global__ void __launch_bounds__(256, 1) gram128_partial_kernel(const double* __restrict__ Xt,
                                                                 const uint8_t* __restrict__ mask,
                                                                 const int* __restrict__ rows, int n, int d,
                                                                 int j, const double* __restrict__ mu,
                                                                 int rows_per_part, double* __restrict__ partial) {
   if (blockIdx.x < blockIdx.y) return;
-  __shared__ __align__(16) double sa[kBK][kBT];
-  __shared__ __align__(16) double sb[kBK][kBT];
+  // rows padded by 4 doubles: the tensor-core fragments read 4 rows x 8 columns per load (a half-warp's
+  // sixteen 8-byte words then fall into sixteen different bank pairs)
+  __shared__ __align__(16) double sa[kBK][kBT + 4];
+  __shared__ __align__(16) double sb[kBK][kBT + 4];
   const int a0 = blockIdx.y * kBT, b0 = blockIdx.x * kBT;
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const int r_begin = blockIdx.z * rows_per_part;
@@ -362,6 +364,27 @@ __global__ void __launch_bounds__(256, 1) gram128_partial_kernel(const double* _
   for (int r0 = r_begin; r0 < r_end; r0 += kBK) {
     const bool more = r0 + kBK < r_end;
     if (more) fetch(r0 + kBK);
+    if constexpr (kMma) {
+      // FP64 tensor cores: mma.sync m8n8k4.  Warp w owns rows 32*(w>>1).., columns 64*(w&1).. of the tile:
+      // 4 x 8 blocks of 8 x 8; acc[i][2*jb + c] = block (i, jb), fragment element c.
+      const int lane = tid & 31, wrp = tid >> 5;
+      const int fa = 32 * (wrp >> 1) + (lane >> 2), fb = 64 * (wrp & 1) + (lane >> 2), fk = lane & 3;
+#pragma unroll
+      for (int k0 = 0; k0 < kBK; k0 += 4) {
+        double af[4], bf[8];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) af[i] = sa[k0 + fk][fa + 8 * i];
+#pragma unroll
+        for (int jb = 0; jb < 8; ++jb) bf[jb] = sb[k0 + fk][fb + 8 * jb];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int jb = 0; jb < 8; ++jb)
+            asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                         : "+d"(acc[i][2 * jb]), "+d"(acc[i][2 * jb + 1])
+                         : "d"(af[i]), "d"(bf[jb]));
+      }
+    } else {
 #pragma unroll
     for (int kk = 0; kk < kBK; ++kk) {
       double av[8], bv[8];
@@ -379,11 +402,27 @@ __global__ void __launch_bounds__(256, 1) gram128_partial_kernel(const double* _
 #pragma unroll
         for (int k = 0; k < 8; ++k) acc[i][k] = fma(av[i], bv[k], acc[i][k]);
     }
+    }
     __syncthreads();
     if (more) stage();
     __syncthreads();
   }
   double* out = partial + (size_t)blockIdx.z * d * d;
+  if constexpr (kMma) {
+    const int lane = tid & 31, wrp = tid >> 5;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int a = a0 + 32 * (wrp >> 1) + 8 * i + (lane >> 2);
+#pragma unroll
+      for (int jb = 0; jb < 8; ++jb)
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          const int b = b0 + 64 * (wrp & 1) + 8 * jb + 2 * (lane & 3) + c;
+          if (a < d && b < d) out[(size_t)a * d + b] = acc[i][2 * jb + c];
+        }
+    }
+    return;
+  }
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int a = a0 + 2 * ty + 32 * (i >> 1) + (i & 1);
@@ -920,10 +959,17 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
   for (int k = 0; k < d; ++k) mx = std::fmax(mx, max_abs[k]);
   const double norm_tol = kRoundTol * mx;
 
+  // wide tables: the Gram tiles on the FP64 tensor cores (mma.sync m8n8k4) unless GS_GRAM_MMA=0
+  bool gram_mma = true;
+  if (const char* v = getenv("GS_GRAM_MMA")) gram_mma = atoi(v) != 0;
   if (big_gram) {  // Gram over all rows, centred at the initial means
     gs::note_launch();
-    gram128_partial_kernel<false><<<dim3(tiles, tiles, parts), 256, 0, s>>>(dXt, dMask, nullptr, n, d, -1, dMeans,
-                                                                         rows_per_part, dPartial);
+    if (gram_mma)
+      gram128_partial_kernel<false, true><<<dim3(tiles, tiles, parts), 256, 0, s>>>(dXt, dMask, nullptr, n, d, -1, dMeans,
+                                                                                 rows_per_part, dPartial);
+    else
+      gram128_partial_kernel<false, false><<<dim3(tiles, tiles, parts), 256, 0, s>>>(dXt, dMask, nullptr, n, d, -1, dMeans,
+                                                                                  rows_per_part, dPartial);
     gs::note_launch();
     gram_reduce_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dPartial, d, parts, gtile, nullptr, dH);
   }
@@ -951,14 +997,22 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
           int rpp = (n_dead + parts - 1) / parts;
           rpp = (rpp + kBK - 1) / kBK * kBK;
           gs::note_launch();
-          gram128_partial_kernel<true><<<dim3(tiles, tiles, parts), 256, 0, s>>>(
-              dXt, dMask, dDead + dead_off[j], n_dead, d, j, dMeans, rpp > 0 ? rpp : kBK, dPartial);
+          if (gram_mma)
+            gram128_partial_kernel<true, true><<<dim3(tiles, tiles, parts), 256, 0, s>>>(
+                dXt, dMask, dDead + dead_off[j], n_dead, d, j, dMeans, rpp > 0 ? rpp : kBK, dPartial);
+          else
+            gram128_partial_kernel<true, false><<<dim3(tiles, tiles, parts), 256, 0, s>>>(
+                dXt, dMask, dDead + dead_off[j], n_dead, d, j, dMeans, rpp > 0 ? rpp : kBK, dPartial);
           gs::note_launch();
           gram_reduce_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dPartial, d, parts, gtile, dH, dG);
         } else {
           gs::note_launch();
-          gram128_partial_kernel<false><<<dim3(tiles, tiles, parts), 256, 0, s>>>(dXt, dMask, nullptr, n, d, j, dMeans,
-                                                                               rows_per_part, dPartial);
+          if (gram_mma)
+            gram128_partial_kernel<false, true><<<dim3(tiles, tiles, parts), 256, 0, s>>>(dXt, dMask, nullptr, n, d, j,
+                                                                                       dMeans, rows_per_part, dPartial);
+          else
+            gram128_partial_kernel<false, false><<<dim3(tiles, tiles, parts), 256, 0, s>>>(dXt, dMask, nullptr, n, d, j,
+                                                                                        dMeans, rows_per_part, dPartial);
           gs::note_launch();
           gram_reduce_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dPartial, d, parts, gtile, nullptr, dG);
         }
