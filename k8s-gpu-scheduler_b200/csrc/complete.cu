@@ -291,6 +291,8 @@ constexpr int kBT = 128, kBK = 16;
 
 // kList = false: rows 0..n-1, those where feature j is observed (j < 0: every row).
 // kList = true: the rows rows[0..n-1] (a list of row numbers), all of them.
+// the 64 accumulators seen as [4 row blocks][8 column blocks][2 fragment elements]
+#define GS_ACCM(i, jb, c) acc[((i) * 16 + 2 * (jb) + (c)) >> 3][((i) * 16 + 2 * (jb) + (c)) & 7]
 template <bool kList, bool kMma>
 __global__ void __launch_bounds__(256, 1) gram128_partial_kernel(const double* __restrict__ Xt,
                                                                 const uint8_t* __restrict__ mask,
@@ -366,7 +368,7 @@ __global__ void __launch_bounds__(256, 1) gram128_partial_kernel(const double* _
     if (more) fetch(r0 + kBK);
     if constexpr (kMma) {
       // FP64 tensor cores: mma.sync m8n8k4.  Warp w owns rows 32*(w>>1).., columns 64*(w&1).. of the tile:
-      // 4 x 8 blocks of 8 x 8; acc[i][2*jb + c] = block (i, jb), fragment element c.
+      // 4 x 8 blocks of 8 x 8; GS_ACCM(i, jb, c) = block (i, jb), fragment element c (the same 64 registers).
       const int lane = tid & 31, wrp = tid >> 5;
       const int fa = 32 * (wrp >> 1) + (lane >> 2), fb = 64 * (wrp & 1) + (lane >> 2), fk = lane & 3;
 #pragma unroll
@@ -381,7 +383,7 @@ __global__ void __launch_bounds__(256, 1) gram128_partial_kernel(const double* _
 #pragma unroll
           for (int jb = 0; jb < 8; ++jb)
             asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
-                         : "+d"(acc[i][2 * jb]), "+d"(acc[i][2 * jb + 1])
+                         : "+d"(GS_ACCM(i, jb, 0)), "+d"(GS_ACCM(i, jb, 1))
                          : "d"(af[i]), "d"(bf[jb]));
       }
     } else {
@@ -418,7 +420,7 @@ __global__ void __launch_bounds__(256, 1) gram128_partial_kernel(const double* _
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
           const int b = b0 + 64 * (wrp & 1) + 8 * jb + 2 * (lane & 3) + c;
-          if (a < d && b < d) out[(size_t)a * d + b] = acc[i][2 * jb + c];
+          if (a < d && b < d) out[(size_t)a * d + b] = GS_ACCM(i, jb, c);
         }
     }
     return;
