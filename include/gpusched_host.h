@@ -64,6 +64,21 @@ GS_API uint32_t gsp_builder_app_of(const gsp_builder* b, const char* pod_name);
  * *ok (may be NULL) tells whether the string parsed. */
 GS_API float gsp_parse_slo(const char* value, int* ok);
 
+/* The body of a Prometheus instant query against the node's DCGM exporter (GET /api/v1/query?query=<metric>
+ * {pod="<dcgm pod>"}, pkg/prom/fetch_prom_metrics/prom_metrics.go:63-118), parsed as ParseResponse does
+ * (:22-61).  Call once per metric (the reference queries DCGM_FI_PROF_GR_ENGINE_ACTIVE, DCGM_FI_DEV_MEM_COPY_UTIL,
+ * DCGM_FI_DEV_GPU_TEMP, DCGM_FI_DEV_FB_USED, DCGM_FI_DEV_FB_FREE).  Returns the number of samples, or a negative
+ * error.  An empty body is no samples. */
+GS_API int gsp_builder_add_dcgm_response(gsp_builder* b, const char* node_name, const char* prometheus_json);
+/* After gsp_builder_build: one metric as a structure-of-arrays column out[node * max_gpus + gpu], GPUs in
+ * Redis array order, keyed as GetDcgmMetricsForUUIDS keys them (gpu_plugins.go:193-228: by UUID, or on MIG
+ * nodes by the k-th distinct GPU_I_ID), float32(ParseFloat(value, 32)); slots without a sample keep
+ * default_value (the reference's commented-out consumer defaults to util = 0, fbFree = 1,
+ * gpu_plugins.go:668-673).  Nothing in Score reads these columns — in the reference that code is dead.
+ * Returns the number of slots filled, or a negative error. */
+GS_API int gsp_builder_dcgm_column(gsp_builder* b, const char* metric_name, float default_value, float* out,
+                                   int n_slots);
+
 /* Finish the tables.  After this the views below are valid until the builder is destroyed. */
 GS_API int gsp_builder_build(gsp_builder* b);
 GS_API const gs_cluster* gsp_builder_cluster(const gsp_builder* b);

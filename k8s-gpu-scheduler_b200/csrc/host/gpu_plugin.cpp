@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "../../../include/gpusched_host.h"
+#include "dcgm.h"
 
 namespace {
 
@@ -142,6 +143,7 @@ struct Node {
   int model = GS_MODEL_NONE;
   std::vector<std::string> uuids;
   bool slo_error = false;  // GetSLOs returned an error for this node
+  std::vector<gsp_dcgm::Sample> dcgm;  // Prometheus samples of the node's DCGM exporter
 };
 
 struct PodIn {
@@ -502,6 +504,46 @@ int gsp_plugin_postbind(gsp_plugin* p, const char* node_name, char* out_uuid, in
   put(out_uuid, uuid_cap, uuid.c_str());
   p->status.clear();
   return uuid.empty() ? 0 : 1;  // the reference writes the three keys only when uuid != "" (:907)
+}
+
+int gsp_builder_add_dcgm_response(gsp_builder* b, const char* node_name, const char* prometheus_json) {
+  if (!b || !node_name) return GS_ERR_INVALID;
+  auto it = b->node_index.find(node_name);
+  if (it == b->node_index.end()) {
+    b->err = std::string("gsp_builder_add_dcgm_response: unknown node ") + node_name;
+    return GS_ERR_INVALID;
+  }
+  std::string err;
+  const int n = gsp_dcgm::parse_response(prometheus_json, &b->nodes[it->second].dcgm, &err);
+  if (n < 0) {
+    b->err = "gsp_builder_add_dcgm_response: " + err;
+    return GS_ERR_INVALID;
+  }
+  return n;
+}
+
+int gsp_builder_dcgm_column(gsp_builder* b, const char* metric_name, float default_value, float* out, int n_slots) {
+  if (!b || !metric_name || !out) return GS_ERR_INVALID;
+  if (!b->built) {
+    b->err = "gsp_builder_dcgm_column before gsp_builder_build";
+    return GS_ERR_STATE;
+  }
+  if (n_slots != (int)b->nodes.size() * b->max_gpus) {
+    b->err = "gsp_builder_dcgm_column: the column holds n_nodes * max_gpus values";
+    return GS_ERR_INVALID;
+  }
+  int filled = 0;
+  for (size_t n = 0; n < b->nodes.size(); ++n) {
+    std::string err;
+    const int k = gsp_dcgm::node_column(b->nodes[n].dcgm, b->nodes[n].uuids, metric_name, default_value,
+                                        out + n * (size_t)b->max_gpus, b->max_gpus, &err);
+    if (k < 0) {
+      b->err = "gsp_builder_dcgm_column: node " + b->nodes[n].name + ": " + err;
+      return GS_ERR_INVALID;
+    }
+    filled += k;
+  }
+  return filled;
 }
 
 int gsp_plugin_score_all(gsp_plugin* p, int64_t* out_scores, int n) {

@@ -47,6 +47,8 @@ def _lib():
     L.gsp_plugin_normalize_score.argtypes = [vp, vp, C.c_int]
     L.gsp_plugin_score_all.argtypes = [vp, vp, C.c_int]
     L.gsp_plugin_postbind.argtypes = [vp, cp, C.c_char_p, C.c_int, C.c_char_p, C.c_int, C.c_char_p, C.c_int]
+    L.gsp_builder_add_dcgm_response.argtypes = [vp, cp, cp]
+    L.gsp_builder_dcgm_column.argtypes = [vp, cp, C.c_float, vp, C.c_int]
     L._gsp_ready = True
     return L
 
@@ -57,6 +59,7 @@ HOST_EXPORTS = [
     "gsp_parse_slo", "gsp_builder_build", "gsp_builder_cluster", "gsp_builder_predictions", "gsp_builder_last_error",
     "gsp_plugin_create", "gsp_plugin_destroy", "gsp_plugin_name", "gsp_plugin_last_status", "gsp_plugin_prescore",
     "gsp_plugin_score", "gsp_plugin_score_all", "gsp_plugin_normalize_score", "gsp_plugin_postbind",
+    "gsp_builder_add_dcgm_response", "gsp_builder_dcgm_column",
 ]
 
 
@@ -100,6 +103,22 @@ class SnapshotBuilder:
 
     def add_pod(self, name, phase="Running", cuda_visible_devices=None, slo=None, namespace="default"):
         self._L.gsp_builder_add_pod(self._h, _enc(name), _enc(namespace), _enc(phase), _enc(cuda_visible_devices), _enc(slo))
+
+    def add_dcgm_response(self, node_name, prometheus_json) -> int:
+        """One Prometheus instant-query body of the node's DCGM exporter -> number of samples."""
+        rc = self._L.gsp_builder_add_dcgm_response(self._h, _enc(node_name), _enc(prometheus_json))
+        if rc < 0:
+            raise ValueError(self._L.gsp_builder_last_error(self._h).decode())
+        return rc
+
+    def dcgm_column(self, metric_name, default, n_nodes, max_gpus) -> np.ndarray:
+        """After build(): one DCGM metric as f32[n_nodes, max_gpus] (GPUs in Redis array order)."""
+        out = np.empty((n_nodes, max_gpus), dtype=np.float32)
+        rc = self._L.gsp_builder_dcgm_column(self._h, _enc(metric_name), float(default), out.ctypes.data_as(C.c_void_p),
+                                             int(out.size))
+        if rc < 0:
+            raise ValueError(self._L.gsp_builder_last_error(self._h).decode())
+        return out
 
     def set_redis_reachable(self, flag):
         self._L.gsp_builder_set_redis_reachable(self._h, int(bool(flag)))

@@ -161,3 +161,54 @@ def test_recommender_table_reader(tmp_path, pkg):
     index, columns, X = rec.read_table(str(p))
     assert index == ["onnx_a", "onnx_b"] and columns == ["1P_A30", "2P_A30"]
     assert X[0, 0] == 1.5 and np.isnan(X[0, 1]) and np.isnan(X[1, 0]) and X[1, 1] == 2.25
+
+
+def _prom_body(samples):
+    """A Prometheus instant-query response of the shape of pkg/prom/test_data/prom_response_mock.txt."""
+    import json
+
+    res = []
+    for name, pod, value, uuid, gid in samples:
+        m = {"__name__": name, "pod": pod, "container": "exporter", "gpu": "0", "Hostname": pod}
+        if uuid is not None:
+            m["UUID"] = uuid
+        if gid is not None:
+            m["GPU_I_ID"] = gid
+        res.append({"metric": m, "value": [1674051092.003, value]})
+    return json.dumps({"status": "success", "data": {"resultType": "vector", "result": res}})
+
+
+def test_dcgm_columns_follow_the_prometheus_contract(host):
+    """pkg/prom ParseResponse (prom_metrics.go:22-61) + GetDcgmMetricsForUUIDS' keying
+    (gpu_plugins.go:193-228): samples by UUID on plain GPUs, by the k-th distinct GPU_I_ID on MIG nodes,
+    float32 values, defaults where nothing was reported."""
+    b = host.SnapshotBuilder()
+    b.set_configurations(["app_a"], ["1P_V100"], np.ones((1, 1), np.float32))
+    b.add_node("gpu-node-0", json_list(["GPU-aa", "GPU-bb", "GPU-cc"]))
+    b.add_node("k8s-a30-1", json_list(["MIG-x", "MIG-y"]))
+    b.add_node("gpu-node-2", json_list(["GPU-dd"]))
+    assert b.add_dcgm_response("gpu-node-0", _prom_body([
+        ("DCGM_FI_DEV_FB_FREE", "dcgm-0", "4005", "GPU-aa", None), ("DCGM_FI_DEV_FB_FREE", "dcgm-0", "77.5", "GPU-cc", None),
+        ("DCGM_FI_DEV_FB_FREE", "dcgm-0", "12", "GPU-zz", None)])) == 3          # an unknown UUID is parsed, fills nothing
+    assert b.add_dcgm_response("gpu-node-0", _prom_body([
+        ("DCGM_FI_PROF_GR_ENGINE_ACTIVE", "dcgm-0", "0.25", "GPU-bb", None),
+        ("DCGM_FI_PROF_GR_ENGINE_ACTIVE", "dcgm-0", "0.5", "GPU-bb", None)])) == 2  # the later sample wins
+    assert b.add_dcgm_response("k8s-a30-1", _prom_body([
+        ("DCGM_FI_DEV_FB_FREE", "dcgm-1", "100", "GPU-parent", "9"), ("DCGM_FI_DEV_FB_FREE", "dcgm-1", "200", "GPU-parent", "13")])) == 2
+    assert b.add_dcgm_response("gpu-node-2", "") == 0                             # empty body: no samples
+    assert b.add_dcgm_response("gpu-node-2", '{"status":"success","data":{"resultType":"vector","result":[]}}') == 0
+    with pytest.raises(ValueError):
+        b.add_dcgm_response("gpu-node-2", "not json")
+    with pytest.raises(ValueError):
+        b.add_dcgm_response("gpu-node-2", '{"data":{"result":[{"metric":{"pod":"p"},"value":[1,"2"]}]}}')   # no __name__
+    with pytest.raises(ValueError):
+        b.add_dcgm_response("no-such-node", "")
+    _, cl = b.build()
+    G = cl.max_gpus
+    free = b.dcgm_column("DCGM_FI_DEV_FB_FREE", 1.0, 3, G)
+    assert free[0, :3].tolist() == [4005.0, 1.0, 77.5]
+    assert free[1, :2].tolist() == [200.0, 100.0]      # GPU_I_ID sorted as STRINGS: "13" < "9" -> MIG-x = 13, MIG-y = 9
+    assert free[2, 0] == 1.0 and (free[:, 3:] == 1.0).all() if G > 3 else True
+    util = b.dcgm_column("DCGM_FI_PROF_GR_ENGINE_ACTIVE", 0.0, 3, G)
+    assert util[0, :3].tolist() == [0.0, 0.5, 0.0] and not util[1:].any()
+    b.close()
