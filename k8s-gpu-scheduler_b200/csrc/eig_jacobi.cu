@@ -12,8 +12,8 @@
 //     bj_pivot_kernel  one CTA per pair: the 32 x 32 pivot [A_II A_IJ; A_JI A_JJ] is diagonalised in
 //                      shared memory by cyclic Jacobi (parallel ordering, 16 rotations per step) and
 //                      the accumulated rotation Q (32 x 32, orthogonal) written out;
-//     bj_rows_kernel   A <- Q^T A on the pair's 32 rows;
-//     bj_cols_kernel   A <- A Q and V <- V Q on the pair's 32 columns.
+//     bj_update_kernel every 32 x 32 block (pair's rows x pair's columns) of A becomes Q_i^T A_blk Q_j and
+//                      every block of V becomes V_blk Q_j — one pass, each CTA owns its block.
 //   Sweeps repeat until off(A)^2 <= 1e-30 ||A||^2 (or the off-norm stagnates on the rounding floor),
 //   the same stopping rule as the one-CTA kernel.  Padding rows/columns are zero and never rotate.
 #include <atomic>
@@ -171,68 +171,58 @@ __global__ void __launch_bounds__(256) bj_pivot_kernel(const double* __restrict_
   for (int e = tid; e < kP * kP; e += 256) out[e] = Q[e / kP][e % kP];
 }
 
-// A <- Q^T A on the 32 rows of every pair; grid (pairs, column tiles of 128)
-__global__ void __launch_bounds__(256) bj_rows_kernel(double* __restrict__ A, int mp, int nb, int step,
-                                                     const double* __restrict__ Qin) {
-  __shared__ double Q[kP][kP + 1];
-  int I, J;
-  bj_pair(nb, step, blockIdx.x, &I, &J);
-  const double* q = Qin + (size_t)blockIdx.x * kP * kP;
-  for (int e = threadIdx.x; e < kP * kP; e += 256) Q[e / kP][e % kP] = q[e];
-  __syncthreads();
-  const int c = blockIdx.y * 128 + (threadIdx.x & 127);
-  const int r0 = (threadIdx.x >> 7) * kB;  // this thread's 16 output rows of the 32
-  if (c >= mp) return;
-  double in[kP];
-#pragma unroll
-  for (int k = 0; k < kP; ++k) in[k] = A[(size_t)(k < kB ? I * kB + k : J * kB + k - kB) * mp + c];
-#pragma unroll
-  for (int r = 0; r < kB; ++r) {
-    double acc = 0.0;
-#pragma unroll
-    for (int k = 0; k < kP; ++k) acc += Q[k][r0 + r] * in[k];
-    const int rr = r0 + r;
-    A[(size_t)(rr < kB ? I * kB + rr : J * kB + rr - kB) * mp + c] = acc;
-  }
-}
-
-// M <- M Q on the 32 columns of every pair, for M = A (z = 0) and M = V (z = 1);
-// grid (pairs, row tiles of 64, 2)
-__global__ void __launch_bounds__(256) bj_cols_kernel(double* __restrict__ A, double* __restrict__ V, int mp, int nb,
-                                                     int step, const double* __restrict__ Qin) {
-  __shared__ double Q[kP][kP + 1];
-  __shared__ double T[64][kP + 1];
-  double* M = blockIdx.z == 0 ? A : V;
+// One step's whole update in one pass: every 32 x 32 block (pair pi's rows x pair pj's columns) of A becomes
+// Q_pi^T A_blk Q_pj, and every block (row tile, pair pj's columns) of V becomes V_blk Q_pj.  A CTA owns its
+// block, so the update is in place without any ordering between CTAs.  grid (pairs, pairs, 2): z = 0 A, 1 V.
+__global__ void __launch_bounds__(256) bj_update_kernel(double* __restrict__ A, double* __restrict__ V, int mp, int nb,
+                                                       int step, const double* __restrict__ Qin) {
+  __shared__ double X[kP][kP + 1], T[kP][kP + 1], Qi[kP][kP + 1], Qj[kP][kP + 1];
+  const bool is_v = blockIdx.z == 1;
+  double* M = is_v ? V : A;
   if (!M) return;
-  int I, J;
-  bj_pair(nb, step, blockIdx.x, &I, &J);
-  const double* q = Qin + (size_t)blockIdx.x * kP * kP;
-  for (int e = threadIdx.x; e < kP * kP; e += 256) Q[e / kP][e % kP] = q[e];
-  const int row0 = blockIdx.y * 64;
-  for (int e = threadIdx.x; e < 64 * kP; e += 256) {
-    const int r = e / kP, k = e % kP;
-    const int gr = row0 + r, gc = k < kB ? I * kB + k : J * kB + k - kB;
-    T[r][k] = gr < mp ? M[(size_t)gr * mp + gc] : 0.0;
+  int Ii, Ji, Ij, Jj;
+  bj_pair(nb, step, blockIdx.y, &Ii, &Ji);
+  bj_pair(nb, step, blockIdx.x, &Ij, &Jj);
+  const double* qi = Qin + (size_t)blockIdx.y * kP * kP;
+  const double* qj = Qin + (size_t)blockIdx.x * kP * kP;
+  for (int e = threadIdx.x; e < kP * kP; e += 256) {
+    const int r = e / kP, c = e % kP;
+    // rows: the pair's rows for A, a plain 32-row tile for V
+    const int gr = is_v ? (int)blockIdx.y * kP + r : (r < kB ? Ii * kB + r : Ji * kB + r - kB);
+    const int gc = c < kB ? Ij * kB + c : Jj * kB + c - kB;
+    X[r][c] = M[(size_t)gr * mp + gc];
+    Qj[r][c] = qj[e];
+    if (!is_v) Qi[r][c] = qi[e];
   }
   __syncthreads();
-  // thread -> row r, eight output columns c0..c0+7
-  const int r = threadIdx.x >> 2, c0 = (threadIdx.x & 3) * 8;
-  double acc[8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i) acc[i] = 0.0;
+  // T = X Qj : thread -> row r, four columns
+  const int r = threadIdx.x >> 3, c0 = (threadIdx.x & 7) * 4;
+  double acc[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
   for (int k = 0; k < kP; ++k) {
-    const double t = T[r][k];
+    const double x = X[r][k];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) acc[i] += t * Q[k][c0 + i];
+    for (int i = 0; i < 4; ++i) acc[i] += x * Qj[k][c0 + i];
   }
-  const int gr = row0 + r;
-  if (gr < mp) {
+  if (!is_v) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int c = c0 + i;
-      M[(size_t)gr * mp + (c < kB ? I * kB + c : J * kB + c - kB)] = acc[i];
+    for (int i = 0; i < 4; ++i) T[r][c0 + i] = acc[i];
+    __syncthreads();
+    // out = Qi^T T
+#pragma unroll
+    for (int i = 0; i < 4; ++i) acc[i] = 0.0;
+#pragma unroll
+    for (int k = 0; k < kP; ++k) {
+      const double q = Qi[k][r];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) acc[i] += q * T[k][c0 + i];
     }
+  }
+  const int gr = is_v ? (int)blockIdx.y * kP + r : (r < kB ? Ii * kB + r : Ji * kB + r - kB);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = c0 + i;
+    M[(size_t)gr * mp + (c < kB ? Ij * kB + c : Jj * kB + c - kB)] = acc[i];
   }
 }
 
@@ -357,9 +347,7 @@ cudaError_t eig_block_jacobi(const double* G, int d, int j, double* work, double
       note_launch();
       bj_pivot_kernel<<<nb / 2, 256, 0, s>>>(A, mp, nb, step, Q, inner);
       note_launch();
-      bj_rows_kernel<<<dim3(nb / 2, (mp + 127) / 128), 256, 0, s>>>(A, mp, nb, step, Q);
-      note_launch();
-      bj_cols_kernel<<<dim3(nb / 2, (mp + 63) / 64, 2), 256, 0, s>>>(A, V, mp, nb, step, Q);
+      bj_update_kernel<<<dim3(nb / 2, nb / 2, 2), 256, 0, s>>>(A, V, mp, nb, step, Q);
     }
   }
   note_launch();
