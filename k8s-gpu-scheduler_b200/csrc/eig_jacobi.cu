@@ -9,11 +9,13 @@
 //   The m x m matrix is padded to mp = nb * kB (nb even) and split into nb block columns of kB = 16.
 //   A sweep is nb - 1 steps of a round-robin tournament; in a step the nb / 2 disjoint block pairs
 //   (I, J) are processed independently:
-//     bj_pivot_kernel  one CTA per pair: the 32 x 32 pivot [A_II A_IJ; A_JI A_JJ] is diagonalised in
-//                      shared memory by cyclic Jacobi (parallel ordering, 16 rotations per step) and
-//                      the accumulated rotation Q (32 x 32, orthogonal) written out;
-//     bj_update_kernel every 32 x 32 block (pair's rows x pair's columns) of A becomes Q_i^T A_blk Q_j and
-//                      every block of V becomes V_blk Q_j — one pass, each CTA owns its block.
+//     bj_pivot_kernel  one CTA per pair: the 32 x 32 pivot [A_II A_IJ; A_JI A_JJ] is rotated in shared memory
+//                      (16 Jacobi rotations per parallel step; all index pairs in step 0 of a sweep, only the
+//                      pairs across the two blocks afterwards) and the accumulated rotation Q (32 x 32,
+//                      orthogonal) written out;
+//     bj_update_kernel every 32 x 32 block (pair's rows x pair's columns) of A becomes Q_i^T A_blk Q_j (upper
+//                      triangle of blocks computed, mirrored below) and every block of V becomes V_blk Q_j —
+//                      one pass, each CTA owns what it writes; the products run on the FP64 tensor cores.
 //   Sweeps repeat until off(A)^2 <= 1e-30 ||A||^2 (or the off-norm stagnates on the rounding floor),
 //   the same stopping rule as the one-CTA kernel.  Padding rows/columns are zero and never rotate.
 #include <atomic>
@@ -88,141 +90,208 @@ __global__ void __launch_bounds__(256) bj_norm_kernel(const double* __restrict__
   }
 }
 
-// One CTA per block pair: diagonalise the 32 x 32 pivot, write the accumulated rotation Q.
+__device__ __forceinline__ double bj_rcp_approx(double x) {
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  return y;
+}
+
+// The Jacobi rotation for the pair (p, q): t = sgn(theta) / (|theta| + sqrt(theta^2 + 1)),
+// theta = (aqq - app) / (2 apq), c = 1 / sqrt(1 + t^2), s = t c.  This is the critical path of every pivot
+// step, so t is computed in float32 from an approximate quotient: with t good to ~1e-7 the rotated apq
+// shrinks by that factor instead of vanishing, and the next sweep (which is needed anyway) takes care of
+// the rest.  c gets two double-precision Newton steps: c^2 (1 + t^2) = 1 to rounding — whatever t is — is what
+// keeps the accumulated Q orthogonal.  No branches: a rotation that would change nothing becomes (1, 0).
+__device__ __forceinline__ void bj_angle(double app, double aqq, double apq, double* c, double* s) {
+  const bool rotate = fabs(apq) > 1e-300 && fabs(apq) > 1e-18 * fmax(fabs(app), fabs(aqq));
+  const double dl = aqq - app, u = 2.0 * apq;
+  const bool big = fabs(dl) >= fabs(u);
+  const double num = big ? u : dl, den = big ? dl : u;  // |num / den| <= 1; |den| >= 2 |apq| is not subnormal
+  const float r = (float)(num * bj_rcp_approx(rotate ? den : 1.0));  // big: 1 / theta, else theta
+  const float w1 = fmaf(r, r, 1.0f);  // in [1, 2]
+  const float sq = w1 * rsqrtf(w1);
+  const float tn = big ? r : (r >= 0.0f ? 1.0f : -1.0f);
+  const float td = (big ? 1.0f : fabsf(r)) + sq;
+  const double t = rotate ? (double)__fdividef(tn, td) : 0.0;
+  const double w = fma(t, t, 1.0);  // in [1, 2]
+  double yc = (double)rsqrtf((float)w);
+  yc = yc * fma(-0.5 * w, yc * yc, 1.5);
+  yc = yc * fma(-0.5 * w, yc * yc, 1.5);
+  *c = yc;
+  *s = t * yc;
+}
+
+// One CTA per block pair: rotate the 32 x 32 pivot [A_II A_IJ; A_JI A_JJ] in shared memory and write the
+// accumulated rotation Q.  `full` (step 0 of a sweep, where every block sits in exactly one pair): a cyclic
+// sweep over all 496 index pairs, 31 parallel steps of 16 rotations; otherwise only the 256 pairs ACROSS the
+// two blocks, 16 parallel steps — so an outer sweep rotates every index pair of the matrix exactly once.
+// A parallel step is one barrier: thread (a, b) owns the 2 x 2 block (pair a's rows) x (pair b's columns),
+// reads it from one copy of S, applies both rotations and writes it to the other copy; lane b of every warp
+// derives pair b's rotation, pair a's arrives by shuffle.
 __global__ void __launch_bounds__(256) bj_pivot_kernel(const double* __restrict__ A, int mp, int nb, int step,
-                                                      double* __restrict__ Qout, int inner_sweeps) {
-  __shared__ double S[kP][kP + 1], Q[kP][kP + 1];
-  __shared__ double s_c[kB], s_s[kB];
-  __shared__ int s_p[kB], s_q[kB];
+                                                      double* __restrict__ Qout, int inner_sweeps, int full) {
+  __shared__ double S[2][kP][kP + 1], Q[kP][kP + 1];
   const int tid = threadIdx.x;
   int I, J;
   bj_pair(nb, step, blockIdx.x, &I, &J);
   for (int e = tid; e < kP * kP; e += 256) {
     const int r = e / kP, c = e % kP;
     const int gr = (r < kB ? I * kB + r : J * kB + r - kB), gc = (c < kB ? I * kB + c : J * kB + c - kB);
-    S[r][c] = A[(size_t)gr * mp + gc];
+    S[0][r][c] = A[(size_t)gr * mp + gc];
     Q[r][c] = r == c ? 1.0 : 0.0;
   }
   __syncthreads();
-  // a few cyclic sweeps: the pivot need not be diagonalised exactly for the block iteration to
-  // converge, and every barrier here is latency on the critical path of the step.  A sweep in which
-  // no rotation passes the threshold ends the loop.
+  const int a = tid >> 4, b = tid & 15;
+  const int nst = full ? kP - 1 : kB;
+  int cur = 0;
   for (int sweep = 0; sweep < inner_sweeps; ++sweep) {
-    bool rotated = false;
-    for (int st = 0; st < kP - 1; ++st) {
-      if (tid < kB) {
-        int p, q;
-        if (tid == 0) {
-          p = kP - 1;
-          q = st;
-        } else {
-          p = (st + tid) % (kP - 1);
-          q = (st - tid + (kP - 1)) % (kP - 1);
-        }
-        if (p > q) {
-          const int t = p;
-          p = q;
-          q = t;
-        }
-        double c = 1.0, s = 0.0;
-        const double apq = S[p][q], app = S[p][p], aqq = S[q][q];
-        if (fabs(apq) > 1e-300 && fabs(apq) > 1e-18 * sqrt(fabs(app * aqq))) {
-          const double theta = (aqq - app) / (2.0 * apq);
-          const double t = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
-          c = 1.0 / sqrt(t * t + 1.0);
-          s = t * c;
-        }
-        s_p[tid] = p;
-        s_q[tid] = q;
-        s_c[tid] = c;
-        s_s[tid] = s;
-        rotated = rotated || s != 0.0;
+    for (int st = 0; st < nst; ++st) {
+      int pa, qa, pb, qb;
+      if (full) {
+        // round robin over the 32 indices, smaller index first
+        int x = a == 0 ? kP - 1 : (st + a) % (kP - 1), y = a == 0 ? st : (st - a + (kP - 1)) % (kP - 1);
+        pa = min(x, y);
+        qa = max(x, y);
+        x = b == 0 ? kP - 1 : (st + b) % (kP - 1);
+        y = b == 0 ? st : (st - b + (kP - 1)) % (kP - 1);
+        pb = min(x, y);
+        qb = max(x, y);
+      } else {
+        pa = a;
+        qa = kB + ((a + st) & (kB - 1));
+        pb = b;
+        qb = kB + ((b + st) & (kB - 1));
       }
-      if (!__syncthreads_or(tid < kB && s_s[tid] != 0.0)) continue;  // nothing to rotate in this step
-      // columns: S <- S J, Q <- Q J
-      for (int e = tid; e < kB * kP; e += 256) {
-        const int pr = e / kP, i = e % kP;
-        const double c = s_c[pr], s = s_s[pr];
-        if (s == 0.0) continue;
-        const int p = s_p[pr], q = s_q[pr];
-        const double aip = S[i][p], aiq = S[i][q];
-        S[i][p] = c * aip - s * aiq;
-        S[i][q] = s * aip + c * aiq;
-        const double vip = Q[i][p], viq = Q[i][q];
-        Q[i][p] = c * vip - s * viq;
-        Q[i][q] = s * vip + c * viq;
-      }
-      __syncthreads();
-      // rows: S <- J^T S
-      for (int e = tid; e < kB * kP; e += 256) {
-        const int pr = e / kP, i = e % kP;
-        const double c = s_c[pr], s = s_s[pr];
-        if (s == 0.0) continue;
-        const int p = s_p[pr], q = s_q[pr];
-        const double api = S[p][i], aqi = S[q][i];
-        S[p][i] = c * api - s * aqi;
-        S[q][i] = s * api + c * aqi;
-      }
+      const double(*Sc)[kP + 1] = S[cur];
+      double(*Sn)[kP + 1] = S[cur ^ 1];
+      // every load of the step first, so that they overlap the rotation arithmetic
+      const double bpp = Sc[pb][pb], bqq = Sc[qb][qb], bpq = Sc[pb][qb];
+      const double x00 = Sc[pa][pb], x01 = Sc[pa][qb], x10 = Sc[qa][pb], x11 = Sc[qa][qb];
+      const double v0 = Q[a][pb], v1 = Q[a][qb], v2 = Q[a + kB][pb], v3 = Q[a + kB][qb];
+      double cb, sb;
+      bj_angle(bpp, bqq, bpq, &cb, &sb);
+      const double ca = __shfl_sync(0xffffffffu, cb, a), sa = __shfl_sync(0xffffffffu, sb, a);  // lane a holds pair a
+      // columns (pair b), then rows (pair a): J^T S J
+      const double y00 = cb * x00 - sb * x01, y01 = sb * x00 + cb * x01;
+      const double y10 = cb * x10 - sb * x11, y11 = sb * x10 + cb * x11;
+      Sn[pa][pb] = ca * y00 - sa * y10;
+      Sn[pa][qb] = ca * y01 - sa * y11;
+      Sn[qa][pb] = sa * y00 + ca * y10;
+      Sn[qa][qb] = sa * y01 + ca * y11;
+      // Q <- Q J: rows a and a + 16, pair b's columns (in place: nobody else touches them in this step)
+      Q[a][pb] = cb * v0 - sb * v1;
+      Q[a][qb] = sb * v0 + cb * v1;
+      Q[a + kB][pb] = cb * v2 - sb * v3;
+      Q[a + kB][qb] = sb * v2 + cb * v3;
+      cur ^= 1;
       __syncthreads();
     }
-    if (!__syncthreads_or(rotated)) break;
   }
   double* out = Qout + (size_t)blockIdx.x * kP * kP;
   for (int e = tid; e < kP * kP; e += 256) out[e] = Q[e / kP][e % kP];
 }
 
-// One step's whole update in one pass: every 32 x 32 block (pair pi's rows x pair pj's columns) of A becomes
-// Q_pi^T A_blk Q_pj, and every block (row tile, pair pj's columns) of V becomes V_blk Q_pj.  A CTA owns its
-// block, so the update is in place without any ordering between CTAs.  grid (pairs, pairs, 2): z = 0 A, 1 V.
+// C (8 x 8, two elements per lane) += A (8 x 4, row-major fragment) * B (4 x 8, column-major fragment) on the
+// FP64 tensor cores.  Lane l holds A[l / 4][l % 4], B[l % 4][l / 4], C[l / 4][2 (l % 4) + {0, 1}].
+__device__ __forceinline__ void bj_dmma(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c0), "+d"(c1)
+               : "d"(a), "d"(b));
+}
+
+constexpr int kLd = kP + 4;  // shared row stride: the DMMA fragment loads below touch 16 distinct banks per half warp
+
+// One step's update.  `part` 0: A only, 1: V only, 2: both in one launch.
+//   A: CTAs over the upper triangle of pair blocks; the 32 x 32 block (pair pi's rows) x (pair pj's columns),
+//      pi <= pj, becomes Z = Q_pi^T A_blk Q_pj and its mirror image (pj, pi) becomes Z^T — A stays exactly
+//      symmetric off the pivots and a third of the step's flops goes away.
+//   V: CTAs over (row tile of 32 * vt rows, pair pj): every 32-row slab becomes V_blk Q_pj, Q_pj staged once.
+// A CTA owns what it writes, so the update is in place without any ordering between CTAs.  Products on the
+// FP64 tensor cores: warp w owns the 8-row band w / 2 and two 8-column tiles of a 32 x 32 result.
 __global__ void __launch_bounds__(256) bj_update_kernel(double* __restrict__ A, double* __restrict__ V, int mp, int nb,
-                                                       int step, const double* __restrict__ Qin) {
-  __shared__ double X[kP][kP + 1], T[kP][kP + 1], Qi[kP][kP + 1], Qj[kP][kP + 1];
-  const bool is_v = blockIdx.z == 1;
-  double* M = is_v ? V : A;
-  if (!M) return;
-  int Ii, Ji, Ij, Jj;
-  bj_pair(nb, step, blockIdx.y, &Ii, &Ji);
-  bj_pair(nb, step, blockIdx.x, &Ij, &Jj);
-  const double* qi = Qin + (size_t)blockIdx.y * kP * kP;
-  const double* qj = Qin + (size_t)blockIdx.x * kP * kP;
-  for (int e = threadIdx.x; e < kP * kP; e += 256) {
-    const int r = e / kP, c = e % kP;
-    // rows: the pair's rows for A, a plain 32-row tile for V
-    const int gr = is_v ? (int)blockIdx.y * kP + r : (r < kB ? Ii * kB + r : Ji * kB + r - kB);
-    const int gc = c < kB ? Ij * kB + c : Jj * kB + c - kB;
-    X[r][c] = M[(size_t)gr * mp + gc];
-    Qj[r][c] = qj[e];
-    if (!is_v) Qi[r][c] = qi[e];
-  }
-  __syncthreads();
-  // T = X Qj : thread -> row r, four columns
-  const int r = threadIdx.x >> 3, c0 = (threadIdx.x & 7) * 4;
-  double acc[4] = {0.0, 0.0, 0.0, 0.0};
-#pragma unroll
-  for (int k = 0; k < kP; ++k) {
-    const double x = X[r][k];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) acc[i] += x * Qj[k][c0 + i];
-  }
-  if (!is_v) {
-#pragma unroll
-    for (int i = 0; i < 4; ++i) T[r][c0 + i] = acc[i];
-    __syncthreads();
-    // out = Qi^T T
-#pragma unroll
-    for (int i = 0; i < 4; ++i) acc[i] = 0.0;
-#pragma unroll
-    for (int k = 0; k < kP; ++k) {
-      const double q = Qi[k][r];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) acc[i] += q * T[k][c0 + i];
+                                                       int step, const double* __restrict__ Qin, int part, int vt) {
+  __shared__ double X[kP][kLd], T[kP][kLd], Qi[kP][kLd], Qj[kP][kLd];
+  const int np = nb / 2, n_a = part == 1 ? 0 : np * (np + 1) / 2;
+  const bool is_v = (int)blockIdx.x >= n_a;
+  int bi, bj;  // A: pair indices (rows, columns); V: row tile, pair index
+  if (is_v) {
+    bi = ((int)blockIdx.x - n_a) / np;
+    bj = ((int)blockIdx.x - n_a) % np;
+  } else {
+    int rest = (int)blockIdx.x;
+    bi = 0;
+    while (rest >= np - bi) {
+      rest -= np - bi;
+      ++bi;
     }
+    bj = bi + rest;
   }
-  const int gr = is_v ? (int)blockIdx.y * kP + r : (r < kB ? Ii * kB + r : Ji * kB + r - kB);
+  double* M = is_v ? V : A;
+  int Ii = 0, Ji = 0, Ij, Jj;
+  if (!is_v) bj_pair(nb, step, bi, &Ii, &Ji);
+  bj_pair(nb, step, bj, &Ij, &Jj);
+  const double* qi = Qin + (size_t)bi * kP * kP;
+  const double* qj = Qin + (size_t)bj * kP * kP;
+  auto col_of = [&](int c) { return c < kB ? Ij * kB + c : Jj * kB + c - kB; };
+  const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+  const int fr = 8 * (wrp >> 1) + (lane >> 2), fk = lane & 3;  // fragment row / k offset
+  const int fc = 16 * (wrp & 1) + (lane >> 2);                 // first tile's fragment column
+  const int cr = fr, cc = 16 * (wrp & 1) + 2 * (lane & 3);     // accumulator row / first column
+  for (int e = threadIdx.x; e < kP * kP; e += 256) {
+    Qj[e / kP][e % kP] = qj[e];
+    if (!is_v) Qi[e / kP][e % kP] = qi[e];
+  }
+  const int n_sub = is_v ? vt : 1;
+  for (int sub = 0; sub < n_sub; ++sub) {
+    auto row_of = [&](int r) { return is_v ? (bi * vt + sub) * kP + r : (r < kB ? Ii * kB + r : Ji * kB + r - kB); };
+    if (sub) __syncthreads();  // the previous slab's stores out of X are done
+    for (int e = threadIdx.x; e < kP * kP; e += 256) {
+      const int r = e / kP, c = e % kP;
+      X[r][c] = M[(size_t)row_of(r) * mp + col_of(c)];
+    }
+    __syncthreads();
+    double acc[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+    // T = X Qj
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int c = c0 + i;
-    M[(size_t)gr * mp + (c < kB ? Ij * kB + c : Jj * kB + c - kB)] = acc[i];
+    for (int k0 = 0; k0 < kP; k0 += 4) {
+      const double a = X[fr][k0 + fk];
+      bj_dmma(acc[0][0], acc[0][1], a, Qj[k0 + fk][fc]);
+      bj_dmma(acc[1][0], acc[1][1], a, Qj[k0 + fk][fc + 8]);
+    }
+    if (!is_v) {
+#pragma unroll
+      for (int t = 0; t < 2; ++t) {
+        T[cr][cc + 8 * t] = acc[t][0];
+        T[cr][cc + 8 * t + 1] = acc[t][1];
+        acc[t][0] = acc[t][1] = 0.0;
+      }
+      __syncthreads();
+      // Z = Qi^T T
+#pragma unroll
+      for (int k0 = 0; k0 < kP; k0 += 4) {
+        const double a = Qi[k0 + fk][fr];
+        bj_dmma(acc[0][0], acc[0][1], a, T[k0 + fk][fc]);
+        bj_dmma(acc[1][0], acc[1][1], a, T[k0 + fk][fc + 8]);
+      }
+    }
+    // through shared memory (X again, once every warp is done reading it), then row segments to global memory
+    __syncthreads();
+#pragma unroll
+    for (int t = 0; t < 2; ++t) {
+      X[cr][cc + 8 * t] = acc[t][0];
+      X[cr][cc + 8 * t + 1] = acc[t][1];
+    }
+    __syncthreads();
+    const bool mirror = !is_v && bi != bj;
+    for (int e = threadIdx.x; e < kP * kP; e += 256) {
+      const int r = e / kP, c = e % kP;
+      M[(size_t)row_of(r) * mp + col_of(c)] = X[r][c];
+      if (mirror) {
+        // block (bj, bi): rows are pair bj's, columns pair bi's; element (r, c) there is Z[c][r]
+        const int gr = r < kB ? Ij * kB + r : Jj * kB + r - kB, gc = c < kB ? Ii * kB + c : Ji * kB + c - kB;
+        M[(size_t)gr * mp + gc] = X[c][r];
+      }
+    }
   }
 }
 
@@ -292,23 +361,67 @@ int eig_padded_size(int m) {
   return nb * kB;
 }
 
+// work: A, V, Tm (mp * mp each), a ring of rotation sets for two sweeps, norms
+static size_t q_set_doubles(int nb) { return (size_t)(nb / 2) * kP * kP; }
+
 size_t eig_work_doubles(int m) {
   const size_t mp = (size_t)eig_padded_size(m);
-  return 3 * mp * mp + (mp / kP) * kP * kP + 8;
+  const int nb = (int)(mp / kB);
+  return 3 * mp * mp + 2 * (size_t)(nb - 1) * q_set_doubles(nb) + 8;
+}
+
+// A second stream for the eigenvector accumulation (see eig_block_jacobi)
+struct EigSide {
+  cudaStream_t lo = nullptr;
+  cudaEvent_t ev_main = nullptr, ev_side = nullptr, ev_vdone[2] = {nullptr, nullptr};
+};
+
+EigSide* eig_side_create() {
+  EigSide* sd = new EigSide;
+  bool ok = cudaStreamCreateWithFlags(&sd->lo, cudaStreamNonBlocking) == cudaSuccess;
+  ok = ok && cudaEventCreateWithFlags(&sd->ev_main, cudaEventDisableTiming) == cudaSuccess;
+  ok = ok && cudaEventCreateWithFlags(&sd->ev_side, cudaEventDisableTiming) == cudaSuccess;
+  for (int i = 0; i < 2; ++i) ok = ok && cudaEventCreateWithFlags(&sd->ev_vdone[i], cudaEventDisableTiming) == cudaSuccess;
+  if (!ok) {
+    eig_side_destroy(sd);
+    return nullptr;
+  }
+  return sd;
+}
+
+void eig_side_destroy(EigSide* sd) {
+  if (!sd) return;
+  if (sd->lo) cudaStreamDestroy(sd->lo);
+  if (sd->ev_main) cudaEventDestroy(sd->ev_main);
+  if (sd->ev_side) cudaEventDestroy(sd->ev_side);
+  for (int i = 0; i < 2; ++i)
+    if (sd->ev_vdone[i]) cudaEventDestroy(sd->ev_vdone[i]);
+  delete sd;
 }
 
 // Eigendecomposition of G (d x d) without row/column j: evals[m], eigenvectors in the columns of
 // V = work + mp*mp (row-major, row stride mp).  Synchronises the stream once per sweep (the stopping
 // rule is evaluated on the host).  *sweeps_out (host memory) = sweeps run.
+//
+// Only A decides the rotations, so with `side` the critical path on `s` is pivot -> A update -> pivot ...,
+// and V follows on the side stream, a chunk of steps behind, from the rotations kept in the ring: V's
+// share (half of a step's memory traffic and a third of its flops at 1 000 columns) overlaps the next
+// steps' pivots, which leave most of the GPU idle.  Without `side` a step updates A and V in one launch.
 cudaError_t eig_block_jacobi(const double* G, int d, int j, double* work, double* evals, int* sweeps_out,
-                             cudaStream_t s, const double* V0, double* Vsave) {
-  const int m = d - 1, mp = eig_padded_size(m), nb = mp / kB;
+                             cudaStream_t s, const double* V0, double* Vsave, EigSide* side) {
+  const int m = d - 1, mp = eig_padded_size(m), nb = mp / kB, np = nb / 2;
   double* A = work;
   double* V = work + (size_t)mp * mp;
   double* Tm = V + (size_t)mp * mp;
-  double* Q = Tm + (size_t)mp * mp;
-  double* norms = Q + (size_t)(nb / 2) * kP * kP;
+  double* Qring = Tm + (size_t)mp * mp;
+  const size_t qset = q_set_doubles(nb);
+  double* norms = Qring + 2 * (size_t)(nb - 1) * qset;
   const size_t n2 = (size_t)mp * mp;
+  const int n_tri = np * (np + 1) / 2;
+  const int vt = (mp >= 512 && np % 2 == 0) ? 2 : 1;  // 64-row slabs of V per CTA for the wide matrices
+  const int n_vcta = (mp / (kP * vt)) * np;
+  constexpr int kChunk = 16;                 // steps of V launched per hand-over to the side stream
+  cudaError_t e;
   note_launch();
   bj_init_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, s>>>(G, d, j, mp, A, V0 ? nullptr : V);
   if (V0) {
@@ -321,19 +434,26 @@ cudaError_t eig_block_jacobi(const double* G, int d, int j, double* work, double
     bj_gemm_tn_kernel<<<gg, 256, 0, s>>>(V0, Tm, A, mp);   // A = V0^T Tm
     note_launch();
     bj_symmetrise_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, s>>>(A, mp);
-    cudaError_t e = cudaMemcpyAsync(V, V0, sizeof(double) * n2, cudaMemcpyDeviceToDevice, s);
-    if (e != cudaSuccess) return e;
+    if ((e = cudaMemcpyAsync(V, V0, sizeof(double) * n2, cudaMemcpyDeviceToDevice, s)) != cudaSuccess) return e;
+  }
+  if (side) {  // V is initialised: the side stream may touch it
+    if ((e = cudaEventRecord(side->ev_main, s)) != cudaSuccess) return e;
+    if ((e = cudaStreamWaitEvent(side->lo, side->ev_main, 0)) != cudaSuccess) return e;
   }
   static const int inner = [] {
     const char* v = getenv("GS_EIG_INNER");
     const int k = v ? atoi(v) : kInnerSweeps;
     return k < 1 ? 1 : (k > 16 ? 16 : k);
   }();
+  // GS_EIG_CROSS=0: a full cyclic sweep of every pivot (measurement; rotates pairs inside a block nb - 1 times per sweep)
+  static const int cross_only = [] {
+    const char* v = getenv("GS_EIG_CROSS");
+    return v ? atoi(v) : 1;
+  }();
   double prev_off = -1.0;
   int sweep = 0;
   for (; sweep < 40; ++sweep) {
-    cudaError_t e = cudaMemsetAsync(norms, 0, 2 * sizeof(double), s);
-    if (e != cudaSuccess) return e;
+    if ((e = cudaMemsetAsync(norms, 0, 2 * sizeof(double), s)) != cudaSuccess) return e;
     note_launch();
     bj_norm_kernel<<<296, 256, 0, s>>>(A, mp, norms);
     double h[2];
@@ -343,19 +463,40 @@ cudaError_t eig_block_jacobi(const double* G, int d, int j, double* work, double
     if (h[0] <= 1e-30 * h[1] || h[1] == 0.0) break;
     if (h[0] <= 1e-24 * h[1] && prev_off >= 0.0 && h[0] > 0.25 * prev_off) break;
     prev_off = h[0];
+    double* ring = Qring + (size_t)(sweep & 1) * (nb - 1) * qset;
+    // this half of the ring was last read by V's sweep before the previous one
+    if (side && sweep >= 2 && (e = cudaEventSynchronize(side->ev_vdone[sweep & 1])) != cudaSuccess) return e;
+    int v_from = 0;
     for (int step = 0; step < nb - 1; ++step) {
+      double* Q = ring + (size_t)step * qset;
       note_launch();
-      bj_pivot_kernel<<<nb / 2, 256, 0, s>>>(A, mp, nb, step, Q, inner);
+      bj_pivot_kernel<<<np, 256, 0, s>>>(A, mp, nb, step, Q, inner, step == 0 || cross_only == 0);
       note_launch();
-      bj_update_kernel<<<dim3(nb / 2, nb / 2, 2), 256, 0, s>>>(A, V, mp, nb, step, Q);
+      if (!side) {
+        bj_update_kernel<<<n_tri + n_vcta, 256, 0, s>>>(A, V, mp, nb, step, Q, 2, vt);
+        continue;
+      }
+      bj_update_kernel<<<n_tri, 256, 0, s>>>(A, V, mp, nb, step, Q, 0, vt);
+      if (step + 1 - v_from == kChunk || step == nb - 2) {
+        // rotations v_from .. step exist once `s` gets here
+        if ((e = cudaEventRecord(side->ev_main, s)) != cudaSuccess) return e;
+        if ((e = cudaStreamWaitEvent(side->lo, side->ev_main, 0)) != cudaSuccess) return e;
+        for (int t = v_from; t <= step; ++t) {
+          note_launch();
+          bj_update_kernel<<<n_vcta, 256, 0, side->lo>>>(A, V, mp, nb, t, ring + (size_t)t * qset, 1, vt);
+        }
+        v_from = step + 1;
+      }
     }
+    if (side && (e = cudaEventRecord(side->ev_vdone[sweep & 1], side->lo)) != cudaSuccess) return e;
+  }
+  if (side) {  // V complete before anything that follows on `s` reads it
+    if ((e = cudaEventRecord(side->ev_side, side->lo)) != cudaSuccess) return e;
+    if ((e = cudaStreamWaitEvent(s, side->ev_side, 0)) != cudaSuccess) return e;
   }
   note_launch();
   bj_diag_kernel<<<(m + 255) / 256, 256, 0, s>>>(A, mp, m, evals);
-  if (Vsave) {
-    cudaError_t e = cudaMemcpyAsync(Vsave, V, sizeof(double) * n2, cudaMemcpyDeviceToDevice, s);
-    if (e != cudaSuccess) return e;
-  }
+  if (Vsave && (e = cudaMemcpyAsync(Vsave, V, sizeof(double) * n2, cudaMemcpyDeviceToDevice, s)) != cudaSuccess) return e;
   if (sweeps_out) *sweeps_out = sweep;
   g_eig_fits.fetch_add(1, std::memory_order_relaxed);
   g_eig_sweeps.fetch_add((unsigned long long)sweep, std::memory_order_relaxed);
