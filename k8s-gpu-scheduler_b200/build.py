@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libgpusched.so")
-SOURCES = ["context.cu", "score_kernels.cu", "score_fast.cu", "score_pods.cu", "complete.cu", "eig_jacobi.cu", "multi.cu", "noalloc.cu"]
+SOURCES = ["context.cu", "score_kernels.cu", "score_fast.cu", "score_pods.cu", "complete.cu", "eig_jacobi.cu", "tridiag.cu", "multi.cu", "noalloc.cu"]
 HOST_SOURCES = ["host/gpu_plugin.cpp", "host/dcgm.cpp"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

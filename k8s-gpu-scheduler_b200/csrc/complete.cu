@@ -24,6 +24,7 @@
 #include <vector>
 
 #include "eig_jacobi.h"
+#include "tridiag.h"
 
 #include "../../include/gpusched.h"
 #include "context.h"
@@ -885,7 +886,22 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
   }
   // eigen-solver: the one-CTA Jacobi up to kJacobiMax, the multi-CTA block Jacobi (eig_jacobi.cu) beyond
   const int mm = d - 1;
-  const bool use_block = mm > kJacobiMax;
+  // ... unless the tridiagonal path (tridiag.cu) takes the wide tables: no eigendecomposition at all
+  // (GS_EIG_TRI=0 keeps the block Jacobi)
+  int n_sm = 148;
+  {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+      n_sm = 148;
+  }
+  const char* tri_env = getenv("GS_EIG_TRI");
+  const bool use_tri = mm > kJacobiMax && !(tri_env && atoi(tri_env) == 0) && mm <= tri_max_m(n_sm) && mm <= 1024;
+  const bool use_block = mm > kJacobiMax && !use_tri;
+  double* dTriWork = nullptr;
+  if (use_tri) {
+    CK(mem.alloc(&dTriWork, tri_work_doubles(mm)));
+    CK(cudaMemsetAsync(dSweeps, 0, sizeof(int) * max_steps, s));  // no sweeps on this path
+  }
   double* dEigWork = nullptr;
   const int eig_mp = use_block ? eig_padded_size(mm) : 0;
   std::vector<int> block_sweeps;
@@ -1039,7 +1055,11 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
         gs::note_launch();
         recentre_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dG, d, dMu, dMeans, dNobs);
       }
-      if (use_block) {
+      if (use_tri) {
+        const cudaError_t ee = tri_bayes_ridge(dG, dMu, dNobs, d, j, dTriWork, n_sm, dCoef + (size_t)step * (d - 1),
+                                               dIcpt + step, dIters + step, s);
+        if (ee != cudaSuccess) return c->cuda_fail(ee, "completion: tridiagonal BayesianRidge");
+      } else if (use_block) {
         int sw = 0;
         double* vj = dVstore ? dVstore + (size_t)j * eig_mp * eig_mp : nullptr;
         const cudaError_t ee =
