@@ -116,6 +116,17 @@ __device__ __forceinline__ void tri_sum2(double& a, double& b, double* s_red) {
   }
 }
 
+__device__ __forceinline__ void tri_sum1(double& a, double* s_red) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  if (lane == 0) s_red[warp] = a;
+  __syncthreads();
+  a = lane < nw ? s_red[lane] : 0.0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+}
+
 // ---- the exchange between CTAs: values that carry their own "ready" mark ----
 // A published double gives up its lowest mantissa bit to a tag that flips every time its slot is reused; a reader
 // spins on the slot until the tag is the one it expects.  The value IS the signal: no flag, no fence, no barrier
@@ -260,9 +271,9 @@ __global__ void __launch_bounds__(kTriThreads, 1) tri_reduce_kernel(const double
     const double pp0 = h0 ? tri_untag(p0) : 0.0, pp1 = h1 ? tri_untag(p1) : 0.0;
     if (h0) s_p[j0] = pp0;
     if (h1) s_p[j1] = pp1;
-    double pv = fma(pp0, v0, pp1 * v1), none = 0.0;
+    double pv = fma(pp0, v0, pp1 * v1);
     TRI_T(2)
-    tri_sum2(pv, none, s_red + 64 * (red_flip ^= 1));  // its barrier also completes s_p
+    tri_sum1(pv, s_red + 64 * (red_flip ^= 1));  // its barrier also completes s_p
     const double cw = -0.5 * tau * pv;                  // w = p + cw v
     TRI_T(3)
     const double w1 = s_p[k + 1] + cw;  // v[k+1] = 1
@@ -424,27 +435,34 @@ __global__ void __launch_bounds__(kTriThreads, 1) tri_bayes_kernel(const double*
     __syncthreads();
   };
 
-  // vec <- Q vec = H_0 H_1 ... H_{m-3} vec; thread-owned elements in registers, the next reflector's entries
-  // fetched while the current dot product is reduced
+  // vec <- Q vec = H_0 H_1 ... H_{m-3} vec; thread-owned elements in registers.  One reduction per reflection
+  // is the critical path, so the reflectors' entries are fetched four reflections ahead of it.
+  auto load_v = [&](int k, double* a, double* b) {
+    *a = (k >= 0 && has0 && e0 >= k + 1) ? tb.Vh[(size_t)k * vld + e0] : 0.0;
+    *b = (k >= 0 && has1 && e1 >= k + 1) ? tb.Vh[(size_t)k * vld + e1] : 0.0;
+  };
   auto apply_q = [&](double& r0, double& r1) {
-    double nv0 = 0.0, nv1 = 0.0;
-    int k = m - 3;
-    if (k >= 0) {
-      if (has0 && e0 >= k + 1) nv0 = tb.Vh[(size_t)k * vld + e0];
-      if (has1 && e1 >= k + 1) nv1 = tb.Vh[(size_t)k * vld + e1];
-    }
-    for (; k >= 0; --k) {
-      const double v0 = nv0, v1 = nv1;
-      nv0 = nv1 = 0.0;
-      if (k > 0) {
-        if (has0 && e0 >= k) nv0 = tb.Vh[(size_t)(k - 1) * vld + e0];
-        if (has1 && e1 >= k) nv1 = tb.Vh[(size_t)(k - 1) * vld + e1];
+    constexpr int kAhead = 4;
+    double nv0[kAhead], nv1[kAhead];
+#pragma unroll
+    for (int t = 0; t < kAhead; ++t) load_v(m - 3 - t, &nv0[t], &nv1[t]);
+    for (int k = m - 3; k >= 0; k -= kAhead) {
+      double v0[kAhead], v1[kAhead];
+#pragma unroll
+      for (int t = 0; t < kAhead; ++t) {
+        v0[t] = nv0[t];
+        v1[t] = nv1[t];
+        load_v(k - kAhead - t, &nv0[t], &nv1[t]);
       }
-      double dot = fma(v0, r0, v1 * r1), none = 0.0;
-      tri_sum2(dot, none, s_red + 64 * (red_flip ^= 1));
-      const double f = s_tau[k] * dot;
-      r0 = fma(-f, v0, r0);
-      r1 = fma(-f, v1, r1);
+#pragma unroll
+      for (int t = 0; t < kAhead; ++t) {
+        if (k - t < 0) break;
+        double dot = fma(v0[t], r0, v1[t] * r1);
+        tri_sum1(dot, s_red + 64 * (red_flip ^= 1));
+        const double f = s_tau[k - t] * dot;
+        r0 = fma(-f, v0[t], r0);
+        r1 = fma(-f, v1[t], r1);
+      }
     }
   };
 
@@ -482,8 +500,8 @@ __global__ void __launch_bounds__(kTriThreads, 1) tri_bayes_kernel(const double*
       if (!converged && dnorm < kBrTolT) {  // undecided: evaluate the rule itself
         double q0 = old0 - x0, q1 = old1 - x1;
         apply_q(q0, q1);
-        double l1 = fabs(q0) + fabs(q1), none = 0.0;
-        tri_sum2(l1, none, s_red + 64 * (red_flip ^= 1));
+        double l1 = fabs(q0) + fabs(q1);
+        tri_sum1(l1, s_red + 64 * (red_flip ^= 1));
         converged = l1 < kBrTolT;
       }
       if (converged) break;
@@ -494,7 +512,7 @@ __global__ void __launch_bounds__(kTriThreads, 1) tri_bayes_kernel(const double*
   solve(lambda / alpha);  // the coefficients with the final alpha, lambda
   double c0 = has0 ? s_x[e0] : 0.0, c1 = has1 ? s_x[e1] : 0.0;
   apply_q(c0, c1);
-  double dot = 0.0, none = 0.0;
+  double dot = 0.0;
   if (has0) {
     coef_out[e0] = c0;
     dot = fma(mu[e0 < j ? e0 : e0 + 1], c0, dot);
@@ -503,7 +521,7 @@ __global__ void __launch_bounds__(kTriThreads, 1) tri_bayes_kernel(const double*
     coef_out[e1] = c1;
     dot = fma(mu[e1 < j ? e1 : e1 + 1], c1, dot);
   }
-  tri_sum2(dot, none, s_red + 64 * (red_flip ^= 1));
+  tri_sum1(dot, s_red + 64 * (red_flip ^= 1));
   if (tid == 0) {
     *intercept_out = mu[j] - dot;
     *iters_out = it < kBrMaxIterT ? it + 1 : kBrMaxIterT;

@@ -48,6 +48,7 @@ def main():
         t_tr = time.perf_counter() - t0
         rec = {"n": n, "d": d, "missing": int(np.isnan(X).sum()), "gpu_fit_s": t_fit, "gpu_transform_s": t_tr,
                "rounds": m.n_rounds, "steps": m.n_steps, "ms_per_fit": 1e3 * t_fit / max(1, m.n_steps),
+               "solver": "block_jacobi" if e1[0] > e0[0] else "tridiagonal",
                "eig_sweeps_per_fit": (e1[1] - e0[1]) / max(1, e1[0] - e0[0]),
                # sanity at sizes no CPU reference reaches: the data are low rank + N(0, 0.01^2) noise, so a
                # correct completion recovers the hidden entries to about the noise level

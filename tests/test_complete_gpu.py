@@ -41,6 +41,27 @@ def test_fit_and_transform_match_reference_imputer(pkg, sched, path):
     m.close()
 
 
+@pytest.mark.parametrize("name", ["synth_400x72", "synth_320x264"])
+def test_wide_tables_both_solvers(pkg, sched, monkeypatch, name):
+    """Wide tables take the tridiagonal path (csrc/tridiag.cu: no eigendecomposition); GS_EIG_TRI=0 selects
+    the block Jacobi eigensolver (csrc/eig_jacobi.cu).  Both must reproduce the reference Imputer, and the
+    decomposition counter says which one ran."""
+    g = np.load([p for p in GOLD if name in p][0])
+    X = g["X"]
+    fits0 = pkg.eig_stats()[0]
+    m = pkg.complete_fit(sched, X)
+    assert pkg.eig_stats()[0] == fits0                      # no eigendecomposition on the default path
+    tri = m.transform(X)
+    m.close()
+    monkeypatch.setenv("GS_EIG_TRI", "0")
+    m = pkg.complete_fit(sched, X)
+    assert pkg.eig_stats()[0] == fits0 + len(g["feats"])    # one decomposition per estimator fit
+    jac = m.transform(X)
+    m.close()
+    assert rel_err(tri, g["completed"]) < RTOL and rel_err(jac, g["completed"]) < RTOL
+    assert rel_err(tri, jac) < RTOL
+
+
 def test_transform_is_row_independent_and_handles_complete_rows(pkg, sched):
     g = np.load([p for p in GOLD if "synth_200x12" in p][0])
     X = g["X"]
