@@ -918,17 +918,9 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
       dVstore = nullptr;  // no room: every decomposition starts cold
     }
   }
-  // second stream for the eigenvector accumulation (GS_EIG_SIDE=0: everything on `s`)
-  struct SideGuard {
-    EigSide* p = nullptr;
-    ~SideGuard() { eig_side_destroy(p); }
-  } side;
   if (use_block) {
     CK(mem.alloc(&dEigWork, eig_work_doubles(mm)));
     CK(cudaMemsetAsync(dSweeps, 0, sizeof(int) * max_steps, s));
-    const char* sv = getenv("GS_EIG_SIDE");
-    // pays from about 500 columns on (measured: +5 % at 1 000); below, the extra launches cost more than they hide
-    if (eig_mp >= 512 && !(sv && atoi(sv) == 0) && !(side.p = eig_side_create())) return GS_ERR_CUDA;
   }
   const size_t bayes_smem = sizeof(double) * 6 * (size_t)(mm > 0 ? mm : 1);
   CK(cudaFuncSetAttribute(bayes_ridge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bayes_smem));
@@ -1063,7 +1055,7 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
         int sw = 0;
         double* vj = dVstore ? dVstore + (size_t)j * eig_mp * eig_mp : nullptr;
         const cudaError_t ee =
-            eig_block_jacobi(dG, d, j, dEigWork, dEv, &sw, s, (vj && have_v[j]) ? vj : nullptr, vj, side.p);
+            eig_block_jacobi(dG, d, j, dEigWork, dEv, &sw, s, (vj && have_v[j]) ? vj : nullptr, vj);
         if (vj) have_v[j] = 1;
         if (ee != cudaSuccess) return c->cuda_fail(ee, "completion: block Jacobi eigensolver");
         block_sweeps.push_back(sw);

@@ -3,8 +3,10 @@
 // BayesianRidge.fit takes an SVD of the centred design matrix per feature
 // (pkg/recommender/recommender/recommender.py:15-17 -> sklearn linear_model/_bayes.py:262-306:
 // eigen_vals_ = S^2, Vh); here that is the eigendecomposition of the centred Gram matrix G without
-// row/column j.  Up to 24 columns complete.cu's one-CTA Jacobi serves; beyond, this file: a
-// two-sided BLOCK Jacobi across CTAs (round 1 called cuSOLVER's syevd there).
+// row/column j.  Up to 24 columns complete.cu's one-CTA Jacobi serves; beyond, tridiag.cu needs no
+// eigendecomposition at all and is what runs by default.  This file is the other round-2 solver (round 1 called
+// cuSOLVER's syevd there), selected with GS_EIG_TRI=0 or when tridiag.cu's matrix would not fit shared memory,
+// and kept as a cross-check: a two-sided BLOCK Jacobi across CTAs.
 //
 //   The m x m matrix is padded to mp = nb * kB (nb even) and split into nb block columns of kB = 16.
 //   A sweep is nb - 1 steps of a round-robin tournament; in a step the nb / 2 disjoint block pairs
@@ -201,7 +203,7 @@ __device__ __forceinline__ void bj_dmma(double& c0, double& c1, double a, double
 
 constexpr int kLd = kP + 4;  // shared row stride: the DMMA fragment loads below touch 16 distinct banks per half warp
 
-// One step's update.  `part` 0: A only, 1: V only, 2: both in one launch.
+// One step's update, A and V in one launch.
 //   A: CTAs over the upper triangle of pair blocks; the 32 x 32 block (pair pi's rows) x (pair pj's columns),
 //      pi <= pj, becomes Z = Q_pi^T A_blk Q_pj and its mirror image (pj, pi) becomes Z^T — A stays exactly
 //      symmetric off the pivots and a third of the step's flops goes away.
@@ -209,9 +211,9 @@ constexpr int kLd = kP + 4;  // shared row stride: the DMMA fragment loads below
 // A CTA owns what it writes, so the update is in place without any ordering between CTAs.  Products on the
 // FP64 tensor cores: warp w owns the 8-row band w / 2 and two 8-column tiles of a 32 x 32 result.
 __global__ void __launch_bounds__(256) bj_update_kernel(double* __restrict__ A, double* __restrict__ V, int mp, int nb,
-                                                       int step, const double* __restrict__ Qin, int part, int vt) {
+                                                       int step, const double* __restrict__ Qin, int vt) {
   __shared__ double X[kP][kLd], T[kP][kLd], Qi[kP][kLd], Qj[kP][kLd];
-  const int np = nb / 2, n_a = part == 1 ? 0 : np * (np + 1) / 2;
+  const int np = nb / 2, n_a = np * (np + 1) / 2;
   const bool is_v = (int)blockIdx.x >= n_a;
   int bi, bj;  // A: pair indices (rows, columns); V: row tile, pair index
   if (is_v) {
@@ -361,66 +363,30 @@ int eig_padded_size(int m) {
   return nb * kB;
 }
 
-// work: A, V, Tm (mp * mp each), a ring of rotation sets for two sweeps, norms
+// work: A, V, Tm (mp * mp each), one step's rotations, norms
 static size_t q_set_doubles(int nb) { return (size_t)(nb / 2) * kP * kP; }
 
 size_t eig_work_doubles(int m) {
   const size_t mp = (size_t)eig_padded_size(m);
   const int nb = (int)(mp / kB);
-  return 3 * mp * mp + 2 * (size_t)(nb - 1) * q_set_doubles(nb) + 8;
-}
-
-// A second stream for the eigenvector accumulation (see eig_block_jacobi)
-struct EigSide {
-  cudaStream_t lo = nullptr;
-  cudaEvent_t ev_main = nullptr, ev_side = nullptr, ev_vdone[2] = {nullptr, nullptr};
-};
-
-EigSide* eig_side_create() {
-  EigSide* sd = new EigSide;
-  bool ok = cudaStreamCreateWithFlags(&sd->lo, cudaStreamNonBlocking) == cudaSuccess;
-  ok = ok && cudaEventCreateWithFlags(&sd->ev_main, cudaEventDisableTiming) == cudaSuccess;
-  ok = ok && cudaEventCreateWithFlags(&sd->ev_side, cudaEventDisableTiming) == cudaSuccess;
-  for (int i = 0; i < 2; ++i) ok = ok && cudaEventCreateWithFlags(&sd->ev_vdone[i], cudaEventDisableTiming) == cudaSuccess;
-  if (!ok) {
-    eig_side_destroy(sd);
-    return nullptr;
-  }
-  return sd;
-}
-
-void eig_side_destroy(EigSide* sd) {
-  if (!sd) return;
-  if (sd->lo) cudaStreamDestroy(sd->lo);
-  if (sd->ev_main) cudaEventDestroy(sd->ev_main);
-  if (sd->ev_side) cudaEventDestroy(sd->ev_side);
-  for (int i = 0; i < 2; ++i)
-    if (sd->ev_vdone[i]) cudaEventDestroy(sd->ev_vdone[i]);
-  delete sd;
+  return 3 * mp * mp + q_set_doubles(nb) + 8;
 }
 
 // Eigendecomposition of G (d x d) without row/column j: evals[m], eigenvectors in the columns of
 // V = work + mp*mp (row-major, row stride mp).  Synchronises the stream once per sweep (the stopping
 // rule is evaluated on the host).  *sweeps_out (host memory) = sweeps run.
-//
-// Only A decides the rotations, so with `side` the critical path on `s` is pivot -> A update -> pivot ...,
-// and V follows on the side stream, a chunk of steps behind, from the rotations kept in the ring: V's
-// share (half of a step's memory traffic and a third of its flops at 1 000 columns) overlaps the next
-// steps' pivots, which leave most of the GPU idle.  Without `side` a step updates A and V in one launch.
 cudaError_t eig_block_jacobi(const double* G, int d, int j, double* work, double* evals, int* sweeps_out,
-                             cudaStream_t s, const double* V0, double* Vsave, EigSide* side) {
+                             cudaStream_t s, const double* V0, double* Vsave) {
   const int m = d - 1, mp = eig_padded_size(m), nb = mp / kB, np = nb / 2;
   double* A = work;
   double* V = work + (size_t)mp * mp;
   double* Tm = V + (size_t)mp * mp;
-  double* Qring = Tm + (size_t)mp * mp;
-  const size_t qset = q_set_doubles(nb);
-  double* norms = Qring + 2 * (size_t)(nb - 1) * qset;
+  double* Q = Tm + (size_t)mp * mp;
+  double* norms = Q + q_set_doubles(nb);
   const size_t n2 = (size_t)mp * mp;
   const int n_tri = np * (np + 1) / 2;
   const int vt = (mp >= 512 && np % 2 == 0) ? 2 : 1;  // 64-row slabs of V per CTA for the wide matrices
   const int n_vcta = (mp / (kP * vt)) * np;
-  constexpr int kChunk = 16;                 // steps of V launched per hand-over to the side stream
   cudaError_t e;
   note_launch();
   bj_init_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, s>>>(G, d, j, mp, A, V0 ? nullptr : V);
@@ -435,10 +401,6 @@ cudaError_t eig_block_jacobi(const double* G, int d, int j, double* work, double
     note_launch();
     bj_symmetrise_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, s>>>(A, mp);
     if ((e = cudaMemcpyAsync(V, V0, sizeof(double) * n2, cudaMemcpyDeviceToDevice, s)) != cudaSuccess) return e;
-  }
-  if (side) {  // V is initialised: the side stream may touch it
-    if ((e = cudaEventRecord(side->ev_main, s)) != cudaSuccess) return e;
-    if ((e = cudaStreamWaitEvent(side->lo, side->ev_main, 0)) != cudaSuccess) return e;
   }
   static const int inner = [] {
     const char* v = getenv("GS_EIG_INNER");
@@ -463,36 +425,12 @@ cudaError_t eig_block_jacobi(const double* G, int d, int j, double* work, double
     if (h[0] <= 1e-30 * h[1] || h[1] == 0.0) break;
     if (h[0] <= 1e-24 * h[1] && prev_off >= 0.0 && h[0] > 0.25 * prev_off) break;
     prev_off = h[0];
-    double* ring = Qring + (size_t)(sweep & 1) * (nb - 1) * qset;
-    // this half of the ring was last read by V's sweep before the previous one
-    if (side && sweep >= 2 && (e = cudaEventSynchronize(side->ev_vdone[sweep & 1])) != cudaSuccess) return e;
-    int v_from = 0;
     for (int step = 0; step < nb - 1; ++step) {
-      double* Q = ring + (size_t)step * qset;
       note_launch();
       bj_pivot_kernel<<<np, 256, 0, s>>>(A, mp, nb, step, Q, inner, step == 0 || cross_only == 0);
       note_launch();
-      if (!side) {
-        bj_update_kernel<<<n_tri + n_vcta, 256, 0, s>>>(A, V, mp, nb, step, Q, 2, vt);
-        continue;
-      }
-      bj_update_kernel<<<n_tri, 256, 0, s>>>(A, V, mp, nb, step, Q, 0, vt);
-      if (step + 1 - v_from == kChunk || step == nb - 2) {
-        // rotations v_from .. step exist once `s` gets here
-        if ((e = cudaEventRecord(side->ev_main, s)) != cudaSuccess) return e;
-        if ((e = cudaStreamWaitEvent(side->lo, side->ev_main, 0)) != cudaSuccess) return e;
-        for (int t = v_from; t <= step; ++t) {
-          note_launch();
-          bj_update_kernel<<<n_vcta, 256, 0, side->lo>>>(A, V, mp, nb, t, ring + (size_t)t * qset, 1, vt);
-        }
-        v_from = step + 1;
-      }
+      bj_update_kernel<<<n_tri + n_vcta, 256, 0, s>>>(A, V, mp, nb, step, Q, vt);
     }
-    if (side && (e = cudaEventRecord(side->ev_vdone[sweep & 1], side->lo)) != cudaSuccess) return e;
-  }
-  if (side) {  // V complete before anything that follows on `s` reads it
-    if ((e = cudaEventRecord(side->ev_side, side->lo)) != cudaSuccess) return e;
-    if ((e = cudaStreamWaitEvent(s, side->ev_side, 0)) != cudaSuccess) return e;
   }
   note_launch();
   bj_diag_kernel<<<(m + 255) / 256, 256, 0, s>>>(A, mp, m, evals);

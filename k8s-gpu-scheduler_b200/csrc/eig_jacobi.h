@@ -6,13 +6,8 @@
 namespace gs {
 int eig_padded_size(int m);        // mp: row stride of the work matrices for an m x m problem
 size_t eig_work_doubles(int m);    // doubles of work space: A (mp*mp), V (mp*mp), rotations, norms
-struct EigSide;                    // a second stream + events: the eigenvector accumulation runs beside the sweep
-EigSide* eig_side_create();        // nullptr on failure
-void eig_side_destroy(EigSide* side);
-// V0 (optional, mp x mp): eigenvectors of an earlier, nearby matrix to start from; Vsave (optional): a copy of V;
-// side (optional): from eig_side_create(), used by one decomposition at a time
+// V0 (optional, mp x mp): eigenvectors of an earlier, nearby matrix to start from; Vsave (optional): a copy of V
 cudaError_t eig_block_jacobi(const double* G, int d, int j, double* work, double* evals, int* sweeps_host,
-                             cudaStream_t s, const double* V0 = nullptr, double* Vsave = nullptr,
-                             EigSide* side = nullptr);
+                             cudaStream_t s, const double* V0 = nullptr, double* Vsave = nullptr);
 void eig_stats(unsigned long long* fits, unsigned long long* sweeps);  // decompositions and sweeps so far (process-wide)
 }  // namespace gs
