@@ -62,6 +62,36 @@ def test_wide_tables_both_solvers(pkg, sched, monkeypatch, name):
     assert rel_err(tri, jac) < RTOL
 
 
+def test_config3_width_two_independent_solvers_agree(pkg, sched, monkeypatch):
+    """BASELINE configs[2]'s width (1 000 columns, rank 64 + noise, 30 % missing) is beyond what the reference's
+    Imputer finishes on a CPU in test time, so there is no golden at this width.  Pinned instead by two solvers
+    that share no code beyond the Gram matrix: the tridiagonal path and the block Jacobi eigendecomposition must
+    give the same completed table (one round: the first round's fits are the ill-conditioned ones — mean-imputed
+    columns — and one round bounds the Jacobi side's run time)."""
+    rng = np.random.default_rng(11)
+    n, d, rank = 1500, 1000, 64
+    truth = rng.normal(size=(n, rank)) @ rng.normal(size=(rank, d)) + rng.normal(scale=0.01, size=(n, d))
+    X = truth.copy()
+    mask = rng.random((n, d)) < 0.30
+    mask[rng.integers(0, n, size=d), np.arange(d)] = False
+    X[mask] = np.nan
+    monkeypatch.setenv("GS_COMPLETE_MAX_ROUNDS", "1")
+    fits0 = pkg.eig_stats()[0]
+    m, tri = pkg.complete_fit_transform(sched, X)
+    assert m.n_steps == d and pkg.eig_stats()[0] == fits0
+    m.close()
+    monkeypatch.setenv("GS_EIG_TRI", "0")
+    m, jac = pkg.complete_fit_transform(sched, X)
+    assert pkg.eig_stats()[0] == fits0 + d
+    m.close()
+    assert np.array_equal(tri[~mask], X[~mask]) and np.isfinite(tri).all()
+    assert rel_err(tri, jac) < RTOL
+    # one round already recovers the hidden entries far better than the column means it started from
+    rmse = float(np.sqrt(np.mean((tri - truth)[mask] ** 2)))
+    rmse_means = float(np.sqrt(np.mean((np.nanmean(X, axis=0)[None, :] - truth)[mask] ** 2)))
+    assert rmse < 0.2 * rmse_means
+
+
 def test_transform_is_row_independent_and_handles_complete_rows(pkg, sched):
     g = np.load([p for p in GOLD if "synth_200x12" in p][0])
     X = g["X"]
