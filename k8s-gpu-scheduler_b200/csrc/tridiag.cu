@@ -33,7 +33,6 @@
 namespace gs {
 
 constexpr int kTriThreads = 512;
-constexpr int kTriWarps = kTriThreads / 32;
 constexpr int kTriRowsPerCta = 4;   // target when fewer CTAs than SMs suffice
 constexpr int kBrMaxIterT = 300;    // BayesianRidge defaults (as complete.cu)
 constexpr double kBrTolT = 1e-3;
