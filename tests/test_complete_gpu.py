@@ -62,6 +62,28 @@ def test_wide_tables_both_solvers(pkg, sched, monkeypatch, name):
     assert rel_err(tri, jac) < RTOL
 
 
+def test_fewer_rows_than_features_on_the_tridiagonal_path(pkg, sched, monkeypatch):
+    """A singular Gram matrix (35 rows, 48 columns) through csrc/tridiag.cu: against the numpy oracle (pinned to
+    the reference's Imputer in tests/test_impute_oracle.py) and against the block Jacobi solver."""
+    from oracle import impute_oracle as io
+
+    rng = np.random.default_rng(21)
+    n, d = 35, 48
+    X = rng.normal(size=(n, 5)) @ rng.normal(size=(5, d)) + 0.05 * rng.normal(size=(n, d))
+    mask = rng.random((n, d)) < 0.25
+    mask[rng.integers(0, n, size=d), np.arange(d)] = False
+    X[mask] = np.nan
+    want = io.fit(X)[1]                                   # (model, completed training rows)
+    m = pkg.complete_fit(sched, X)
+    tri = m.transform(X)
+    m.close()
+    monkeypatch.setenv("GS_EIG_TRI", "0")
+    m = pkg.complete_fit(sched, X)
+    jac = m.transform(X)
+    m.close()
+    assert rel_err(tri, want) < RTOL and rel_err(jac, want) < RTOL
+
+
 def test_config3_width_two_independent_solvers_agree(pkg, sched, monkeypatch):
     """BASELINE configs[2]'s width (1 000 columns, rank 64 + noise, 30 % missing) is beyond what the reference's
     Imputer finishes on a CPU in test time, so there is no golden at this width.  Pinned instead by two solvers
