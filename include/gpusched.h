@@ -392,6 +392,11 @@ GS_API int gs_model_info(const gs_model* model, int32_t* n_features, int32_t* n_
 GS_API int gs_model_step(const gs_model* model, int32_t s, int32_t* feat, double* coef,
                   double* intercept);
 GS_API void gs_model_destroy(gs_model* model);
+/* Instrumentation (no counterpart in the reference): device time of the last fit on this context, measured with
+ * CUDA events on at most 64 of its estimator fits.  out4 = {fits sampled, ms per fit for the column moments, for the
+ * Gram matrix (kernels, all-reduce, recentring), for the estimator (reduction / decomposition + evidence
+ * iteration)}.  Used by bench.py's `completion` object. */
+GS_API int gs_complete_last_timing(gs_ctx* ctx, double* out4);
 /* Instrumentation (no counterpart in the reference): symmetric eigendecompositions the block Jacobi
  * solver has run in this process (return value) and the sweeps they took in total. */
 GS_API uint64_t gs_eig_stats(uint64_t* out_sweeps);

@@ -33,7 +33,7 @@ EXPORTS = [
     "gs_score_batch", "gs_score_decisions", "gs_decisions_dev", "gs_best_dev", "gs_create_multi", "gs_destroy_multi",
     "gs_multi_last_error", "gs_multi_device_count", "gs_mupload_predictions", "gs_mupload_cluster", "gs_mscore_batch",
     "gs_mscore_decisions", "gs_score_raw_dev", "gs_score_raw_dev_noalloc", "gs_normalize_dev", "gs_normalize_scores", "gs_select_mig",
-    "gs_set_profiling", "gs_last_score_kernel_ms", "gs_last_stage_a_ms", "gs_selftest", "gs_selftest_filter", "gs_launch_count", "gs_complete_fit", "gs_complete_fit_sharded", "gs_complete_fit_transform", "gs_complete_transform", "gs_model_info", "gs_model_step", "gs_model_destroy", "gs_eig_stats",
+    "gs_set_profiling", "gs_last_score_kernel_ms", "gs_last_stage_a_ms", "gs_selftest", "gs_selftest_filter", "gs_launch_count", "gs_complete_fit", "gs_complete_fit_sharded", "gs_complete_fit_transform", "gs_complete_transform", "gs_model_info", "gs_model_step", "gs_model_destroy", "gs_eig_stats", "gs_complete_last_timing",
 ]
 
 
@@ -114,6 +114,8 @@ def load_library():
     L.gs_model_step.argtypes = [vp, i32, C.POINTER(i32), vp, C.POINTER(C.c_double)]
     L.gs_model_destroy.argtypes = [vp]
     L.gs_model_destroy.restype = None
+    L.gs_complete_last_timing.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+    L.gs_complete_last_timing.restype = C.c_int
     L.gs_eig_stats.argtypes = [C.POINTER(C.c_uint64)]
     L.gs_eig_stats.restype = C.c_uint64
     _lib = L
@@ -266,6 +268,12 @@ class Scheduler:
         ms = C.c_float(0)
         self._check(self._L.gs_last_stage_a_ms(self._h, C.byref(ms)))
         return float(ms.value)
+
+    def complete_last_timing(self) -> dict:
+        """Device time of the last completion fit on this context, per estimator fit (sampled with CUDA events)."""
+        out = (C.c_double * 4)()
+        self._check(self._L.gs_complete_last_timing(self._h, out))
+        return {"fits_sampled": int(out[0]), "moments_ms": out[1], "gram_ms": out[2], "estimator_ms": out[3]}
 
     def selftest(self, seed: int = 1, n_million: int = 100) -> int:
         bad = C.c_uint64(0)

@@ -780,6 +780,48 @@ struct DevMem {
   }
 };
 
+// Device time of a fit's three parts, sampled on at most 64 estimator fits (events on the stream; read after the
+// fit's last synchronisation): moments (column sums over the observed rows), Gram (kernels, all-reduce,
+// recentring), estimator (decomposition / reduction and the evidence iteration).
+struct FitTimer {
+  std::vector<cudaEvent_t> ev;  // 4 per sample, created up front
+  size_t used = 0;
+  int stride = 1;
+  explicit FitTimer(int max_steps) : stride(max_steps > 64 ? (max_steps + 63) / 64 : 1) {
+    const size_t want = 4 * (size_t)((max_steps + stride - 1) / stride);
+    for (size_t k = 0; k < want; ++k) {
+      cudaEvent_t e = nullptr;
+      if (cudaEventCreate(&e) != cudaSuccess) {  // no timing then; the fit itself is unaffected
+        cudaGetLastError();
+        clear();
+        return;
+      }
+      ev.push_back(e);
+    }
+  }
+  ~FitTimer() { clear(); }
+  void clear() {
+    for (cudaEvent_t e : ev) cudaEventDestroy(e);
+    ev.clear();
+  }
+  bool sampled(int step) const { return !ev.empty() && step % stride == 0 && used + 4 <= ev.size(); }
+  void mark(cudaStream_t s) {
+    if (used < ev.size()) cudaEventRecord(ev[used++], s);
+  }
+  void summarise(double out[4]) const {
+    out[0] = out[1] = out[2] = out[3] = 0.0;
+    const size_t n = used / 4;
+    for (size_t k = 0; k < n; ++k)
+      for (int part = 0; part < 3; ++part) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, ev[4 * k + part], ev[4 * k + part + 1]) == cudaSuccess) out[1 + part] += ms;
+      }
+    out[0] = (double)n;
+    if (n)
+      for (int part = 1; part < 4; ++part) out[part] /= (double)n;
+  }
+};
+
 #define CK(call)                                              \
   do {                                                        \
     cudaError_t _e = (call);                                  \
@@ -992,6 +1034,7 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
     gram_reduce_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dPartial, d, parts, gtile, nullptr, dH);
   }
   int step = 0;
+  FitTimer timer(max_steps);
   std::vector<double> diff(256);
   CK(cudaMemcpyAsync(dPrev, dXt, sizeof(double) * total, cudaMemcpyDeviceToDevice, s));
   int max_rounds = kRounds;
@@ -1000,6 +1043,8 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
     m->n_rounds = rnd;
     for (int oi = 0; oi < d; ++oi, ++step) {
       const int j = order[oi];
+      const bool timed = timer.sampled(step);
+      if (timed) timer.mark(s);
       gs::note_launch();
       obs_sums_partial_kernel<<<sum_blocks, 256, 0, s>>>(dXt, dMask, n, d, j, dSumPart);
       gs::note_launch();
@@ -1009,6 +1054,7 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
       }
       gs::note_launch();
       finish_mu_kernel<<<(d + 255) / 256, 256, 0, s>>>(dSums, d, dMu, dNobs);
+      if (timed) timer.mark(s);
       if (big_gram) {
         const int n_dead = (int)(dead_off[j + 1] - dead_off[j]);
         if (2 * (size_t)n_dead < (size_t)n) {
@@ -1047,6 +1093,7 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
         gs::note_launch();
         recentre_kernel<<<(d * d + 255) / 256, 256, 0, s>>>(dG, d, dMu, dMeans, dNobs);
       }
+      if (timed) timer.mark(s);
       if (use_tri) {
         const cudaError_t ee = tri_bayes_ridge(dG, dMu, dNobs, d, j, dTriWork, n_sm, dCoef + (size_t)step * (d - 1),
                                                dIcpt + step, dIters + step, s);
@@ -1072,6 +1119,7 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
         bayes_ridge_kernel<<<1, 256, bayes_smem, s>>>(dG, dMu, dNobs, d, j, dV, mm, 1, dEv,
                                                       dCoef + (size_t)step * (d - 1), dIcpt + step, dIters + step);
       }
+      if (timed) timer.mark(s);
       if (missing[j] > 0) {
         gs::note_launch();
         predict_kernel<<<(n + 7) / 8, 256, 0, s>>>(dXt, dMask, n, d, j, dCoef + (size_t)step * (d - 1), dIcpt + step);
@@ -1112,6 +1160,7 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
   if (e != cudaSuccess) {
     return c->cuda_fail(e, "completion: model download");
   }
+  timer.summarise(c->fit_timing);
   if (use_block)
     for (int k = 0; k < step && k < (int)block_sweeps.size(); ++k) sweeps[k] = block_sweeps[k] >= 40 ? 60 : block_sweeps[k];
   for (int k = 0; k < step; ++k)
@@ -1124,6 +1173,14 @@ int gs_complete_fit_transform(gs_ctx* c, const double* X, int32_t n, int32_t d, 
     CK(cudaStreamSynchronize(s));
   }
   *out = owner.release();
+  return GS_OK;
+}
+
+int gs_complete_last_timing(gs_ctx* c, double* out4) {
+  if (!c) return GS_ERR_INVALID;
+  std::lock_guard<std::mutex> lk(c->mu);
+  if (!out4) return c->fail(GS_ERR_INVALID, "gs_complete_last_timing: null output");
+  for (int k = 0; k < 4; ++k) out4[k] = c->fit_timing[k];
   return GS_OK;
 }
 

@@ -15,6 +15,8 @@ struct DevBuf {
 };
 
 struct Ctx {
+  // gs_complete_last_timing: [fits sampled, moments ms, Gram ms, estimator ms] per fit, of the last completion fit
+  double fit_timing[4] = {0.0, 0.0, 0.0, 0.0};
   std::mutex mu;
   std::string err;
   int device = 0;
