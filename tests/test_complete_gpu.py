@@ -114,6 +114,16 @@ def test_config3_width_two_independent_solvers_agree(pkg, sched, monkeypatch):
     assert rmse < 0.2 * rmse_means
 
 
+def test_last_fit_timing_is_reported(pkg, sched):
+    g = np.load([p for p in GOLD if "synth_400x72" in p][0])
+    m = pkg.complete_fit(sched, g["X"])
+    t = sched.complete_last_timing()
+    assert 0 < t["fits_sampled"] <= 64 and t["fits_sampled"] <= m.n_steps
+    assert t["moments_ms"] > 0 and t["gram_ms"] > 0 and t["estimator_ms"] > 0
+    assert t["moments_ms"] + t["gram_ms"] + t["estimator_ms"] < 50.0    # per fit; this table takes well under a millisecond
+    m.close()
+
+
 def test_transform_is_row_independent_and_handles_complete_rows(pkg, sched):
     g = np.load([p for p in GOLD if "synth_200x12" in p][0])
     X = g["X"]
