@@ -6,11 +6,12 @@
 //   * per feature j the estimator needs only second moments of the rows where j is observed:
 //     the centred Gram matrix G of ALL d columns over those rows (gram_* kernels, float64).
 //     X^T X = G[others][others], X^T y = G[others][j], y^T y = G[j][j], var(y) = G[j][j]/n;
-//   * the SVD of X in BayesianRidge.fit becomes the symmetric eigendecomposition of X^T X
-//     (parallel cyclic Jacobi, one CTA): eigen_vals = S^2, Vh = V^T;
-//   * the alpha/lambda fixed-point iteration (<= 300 rounds) then costs O(d^2) per round in
-//     one CTA: coef~ = (V^T X^T y)/(s + lambda/alpha), coef = V coef~,
-//     sse = y^T y - 2 coef~.b~ + sum(coef~^2 s);
+//   * up to 24 features (the reference's own tables) the SVD of X in BayesianRidge.fit becomes the symmetric
+//     eigendecomposition of X^T X (parallel cyclic Jacobi, one CTA): eigen_vals = S^2, Vh = V^T, and the
+//     alpha/lambda fixed-point iteration (<= 300 rounds) costs O(d) per round in the eigenbasis:
+//     coef~ = (V^T X^T y)/(s + lambda/alpha), coef = V coef~, sse = y^T y - 2 coef~.b~ + sum(coef~^2 s);
+//   * wider tables need no eigendecomposition: tridiag.cu reduces X^T X to tridiagonal form and runs the same
+//     iteration there (eig_jacobi.cu, a block Jacobi eigendecomposition across CTAs, is the cross-check);
 //   * rows where j is missing get x.coef + intercept (predict_kernel).
 // Everything is float64; parity bar: 1e-5 relative against Imputer.predict (tests/golden).
 
