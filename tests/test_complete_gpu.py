@@ -114,6 +114,24 @@ def test_config3_width_two_independent_solvers_agree(pkg, sched, monkeypatch):
     assert rmse < 0.2 * rmse_means
 
 
+def test_tridiagonal_path_is_bitwise_repeatable(pkg, sched):
+    """The CTAs of the reduction exchange values through L2 without barriers, and the block sums use a scratch
+    area guarded by one barrier per sum: a lost update or a stale read would show as run-to-run variation.
+    Five fits of the same 264-column table must give identical bits in every coefficient."""
+    g = np.load([p for p in GOLD if "synth_320x264" in p][0])
+    X = g["X"]
+    first = None
+    for _ in range(5):
+        m = pkg.complete_fit(sched, X)
+        steps = m.steps()
+        m.close()
+        flat = np.concatenate([np.concatenate([np.asarray(c, dtype=np.float64).ravel(), [float(b)]]) for _, c, b in steps])
+        if first is None:
+            first = flat
+        else:
+            assert np.array_equal(first.view(np.uint64), flat.view(np.uint64))
+
+
 def test_last_fit_timing_is_reported(pkg, sched):
     g = np.load([p for p in GOLD if "synth_400x72" in p][0])
     m = pkg.complete_fit(sched, g["X"])
