@@ -39,6 +39,8 @@ def test_survey_known_answers_are_in_the_fixture():
 def test_oracle_matches_reference_imputer(path, via_gram):
     from oracle import impute_oracle as io
 
+    if not via_gram and "320x264" in path and not os.environ.get("GS_TEST_SLOW"):
+        pytest.skip("2 640 SVDs of 320 x 263 take minutes; the Gram form pins this golden (GS_TEST_SLOW=1 runs both)")
     g = np.load(path)
     X = g["X"]
     m, completed = io.fit(X, via_gram=via_gram)
